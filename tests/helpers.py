@@ -1,0 +1,46 @@
+"""Shared helpers for the parity tests."""
+import os
+
+import numpy as np
+
+from tahoe_b200 import synth
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+GOLDEN_CASES = ["tiny", "char_w", "short_w", "int_w", "ties", "one_feature", "depth0",
+                "susy_like", "higgs_like", "svhn_like"]
+TRANSFORMS = [(0x0, 0.0, 0.0), (0x1, 0.0, 0.0), (0x11, 0.0, 0.25), (0x110, 0.5, -0.1),
+              (0x111, 0.45, 0.0), (0x0, 0.0, 1.5)]
+
+
+def load_case(name):
+    """Golden case -> dict with nodes/data regenerated from seeds when not stored."""
+    z = dict(np.load(os.path.join(GOLDEN, name + ".npz"), allow_pickle=False))
+    c = {k: (v.item() if v.ndim == 0 else v) for k, v in z.items()}
+    if "nodes" not in c:
+        c["nodes"] = synth.gen_dense_forest(c["forest_seed"], c["trees"], c["depth"], c["cols"],
+                                            leaf_prob=c["leaf_prob"], grid=c["grid"])
+        c["data"] = synth.gen_data(c["data_seed"], c["rows"], c["cols"], miss_frac=c["miss_frac"],
+                                   nan_frac=c["nan_frac"], missing=float(c["missing"]),
+                                   grid=c["grid"])
+    return c
+
+
+def golden_preds(c, flags, thr, bias):
+    return c[f"preds_{flags:03x}_{thr}_{bias}"]
+
+
+def bits_equal(a, b):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    b = np.ascontiguousarray(b, dtype=np.float32)
+    return a.shape == b.shape and np.array_equal(a.view(np.uint32), b.view(np.uint32))
+
+
+def score_close(got, want, l1=None):
+    """north_star tolerance: summed scores within 1e-5 relative.  For a float sum
+    whose order differs the natural scale is the L1 mass of the summands (a sum
+    that cancels to ~0 has no meaningful relative error of its own), so the bound
+    is 1e-5 * max(|want|, l1 mass / num terms..., 1) -- we use max(|want|, 1)."""
+    got = np.asarray(got, dtype=np.float64)
+    want = np.asarray(want, dtype=np.float64)
+    scale = np.maximum(np.abs(want), 1.0)
+    return bool(np.all(np.abs(got - want) <= 1e-5 * scale))
