@@ -1,0 +1,176 @@
+/*
+ * tahoe_b200.h -- C ABI of the B200-native decision-forest batch-predict engine.
+ *
+ * Drop-in boundary for ONE path of sampathrg/Tahoe: forest load -> traversal
+ * strategies -> per-row summed score.  The reference has no FFI layer; its
+ * boundary is a header-only C++ class plus an abstract struct.
+ * Every entry point below names the reference interface it replaces.
+ *
+ * Plain pointers and sizes only; no torch / C++ types.  All functions return a
+ * tahoe_status_t (0 = ok) unless stated otherwise and never abort; the text of
+ * the last failure on the calling thread is available from tahoe_last_error().
+ * Every compute entry point runs on the GPU; there is no CPU fallback.
+ */
+#ifndef TAHOE_B200_H
+#define TAHOE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- status codes ------------------------------------------------------------
+ * The reference prints and continues (cuda_base.h:19-25) or assert(false)s
+ * (Struct.h:2012, 2057, 2114); here everything is a status. */
+typedef enum {
+  TAHOE_OK = 0,
+  TAHOE_ERR_INVALID = 1,        /* bad argument / malformed forest */
+  TAHOE_ERR_CUDA = 2,           /* CUDA runtime failure (text in tahoe_last_error) */
+  TAHOE_ERR_NOT_APPLICABLE = 3, /* strategy cannot run this forest/batch:
+                                   "Strategy %d is not suitable for this case."
+                                   (BaseTahoeTest.h:662-678) */
+  TAHOE_ERR_IO = 4,             /* unreadable file (reference: exit(1), BaseTahoeTest.h:273-277) */
+  TAHOE_ERR_NOMEM = 5
+} tahoe_status_t;
+
+/* ---- strategies (value = reference `selected_algorithm`,
+ * Struct.h:2168-2179; SetUp()'s printed id is value+1, BaseTahoeTest.h:93-109) */
+typedef enum {
+  TAHOE_STRATEGY_AUTO = -1,                  /* performance model picks (main.cu:22-82) */
+  TAHOE_STRATEGY_DIRECT = 0,                 /* K1  Struct.h:1196-1240 */
+  TAHOE_STRATEGY_SHARED_DATA_PER_THREAD = 1, /* K2  Struct.h:1610-1704 */
+  TAHOE_STRATEGY_SHARED_DATA = 2,            /* K3  Struct.h:992-1191  */
+  TAHOE_STRATEGY_SHARED_FOREST = 3,          /* K4  Struct.h:1245-1409 */
+  TAHOE_STRATEGY_SPLIT_SHARED_FOREST = 4,    /* K5  Struct.h:1414-1606 */
+  TAHOE_NUM_STRATEGIES = 5
+} tahoe_strategy_t;
+
+/* output_t flags, Struct.h:37-42 */
+enum { TAHOE_OUT_RAW = 0x0, TAHOE_OUT_AVG = 0x1, TAHOE_OUT_SIGMOID = 0x10, TAHOE_OUT_THRESHOLD = 0x100 };
+
+/* ---- POD layouts shared with the reference ------------------------------------
+ * dense_node_t, Struct.h:44-48.  bits = fid[0:29] | def_left<<30 | is_leaf<<31
+ * (Struct.h:57-59, encode_node :103-108).  Trees are complete heaps of
+ * 2^(depth+1)-1 nodes (root 0, children 2k+1 / 2k+2), tree-major. */
+typedef struct { float weight; float val; int32_t bits; } tahoe_dense_node_t;
+/* sparse_node_t, Struct.h:50-54.  Children are an adjacent pair at
+ * left_idx / left_idx+1 relative to the tree's first node (Struct.h:2244). */
+typedef struct { float val; int32_t bits; int32_t left_idx; } tahoe_sparse_node_t;
+
+/* forest_params_t, Struct.h:166-189 (same members, same order; enums as int). */
+typedef struct {
+  int num_nodes;     /* total nodes; sparse forests only */
+  int depth;         /* internal levels; dense forests only */
+  int num_trees;
+  int num_cols;
+  int algo;          /* algo_t, accepted and ignored (layouts are chosen per strategy) */
+  int output;        /* TAHOE_OUT_* flags */
+  float threshold;
+  float global_bias;
+  int strategy;      /* strategy_t of the FIL baseline, accepted and ignored */
+  float missing;     /* missing-value sentinel (data file header line 3) */
+} tahoe_forest_params_t;
+
+typedef struct tahoe_forest tahoe_forest_t; /* opaque handle; owns all device buffers */
+
+typedef struct {
+  int num_trees, depth, num_cols, is_sparse;
+  int64_t num_nodes;          /* real nodes */
+  int node_width_bytes;       /* reference width rule b in {1,2,4} (Struct.h:1831-1852), 0 if undefined */
+  int quantized;              /* 1 if the rank-quantised 4-byte layout exists */
+  int rank_bits, col_bits;
+  int trees_per_chunk;        /* shared-memory forest chunk (0 = a tree does not fit) */
+  int num_chunks;
+  int64_t bytes_heap;         /* packed bytes: 8-byte heap layout (DIRECT, PER_THREAD) */
+  int64_t bytes_interleaved;  /* node-major [node][tree] layout (SHARED_DATA) */
+  int64_t bytes_quantized;    /* 4-byte rank layout (SHARED_FOREST / SPLIT) */
+  int64_t exchanged_nodes;    /* nodes whose children were swapped by the probability reorder */
+  double mean_depth;          /* mean internal nodes on a root-to-leaf path, cover-weighted */
+  int device;
+  int sm_count;
+  int smem_optin_bytes;
+} tahoe_forest_info_t;
+
+/* ---- forest lifetime -------------------------------------------------------------
+ * Replaces dense_adaptive_forest::init(stream, nodes, params), Struct.h:1756, and
+ * init_dense_adaptive, BaseTahoeTest.h:605-611.  `nodes` is the host AoS array of
+ * num_trees * (2^(depth+1)-1) entries; it is copied.  The forest is built on the
+ * current CUDA device. */
+int tahoe_forest_create_dense(const tahoe_dense_node_t* nodes, const tahoe_forest_params_t* params,
+                              tahoe_forest_t** out);
+/* Replaces sparse_forest::init, Struct.h:2327-2345 (disabled in the reference).
+ * tree_offsets has num_trees+1 entries; weights (nullable) are per-node cover
+ * fractions used by the probability reorder. */
+int tahoe_forest_create_sparse(const tahoe_sparse_node_t* nodes, const float* weights,
+                               const int64_t* tree_offsets, const tahoe_forest_params_t* params,
+                               tahoe_forest_t** out);
+/* The reference leaks its forest (`delete forest`, BaseTahoeTest.h:709, no destructor). */
+void tahoe_forest_destroy(tahoe_forest_t* f);
+int tahoe_forest_info(const tahoe_forest_t* f, tahoe_forest_info_t* info);
+
+/* ---- predict -----------------------------------------------------------------------
+ * Replaces forest::predict(stream, preds, data, num_rows), Struct.h:245-269, with the
+ * strategy passed explicitly instead of through the global `selected_algorithm`
+ * (Struct.h:11).  d_data: device, row-major [num_rows][num_cols] float32.
+ * d_preds: device [num_rows].  d_leaf_ids: nullable device [num_rows][num_trees]
+ * int32 receiving the heap index (dense) / node index within the tree (sparse) of
+ * the leaf each row reaches in each tree, in the caller's original tree order.
+ * stream: a cudaStream_t (NULL = default stream).  Asynchronous. */
+int tahoe_predict(tahoe_forest_t* f, int strategy, const float* d_data, size_t num_rows,
+                  float* d_preds, int32_t* d_leaf_ids, void* stream);
+/* Same call with HOST buffers: slabs of rows are copied in, predicted and copied
+ * out on internal streams so that PCIe transfers overlap the traversal.  This is
+ * the harness path generate_data_from_file -> updateDevice -> predict -> updateHost
+ * (BaseTahoeTest.h:392, 691-692).  Synchronous. */
+int tahoe_predict_host(tahoe_forest_t* f, int strategy, const float* h_data, size_t num_rows,
+                       float* h_preds);
+
+/* TAHOE_OK if `strategy` can run this forest on `num_rows` rows, else
+ * TAHOE_ERR_NOT_APPLICABLE (harness gates, BaseTahoeTest.h:657-679). */
+int tahoe_strategy_applicable(const tahoe_forest_t* f, int strategy, size_t num_rows);
+/* Performance model (replaces main.cu:22-82): returns the strategy id it picks for
+ * this forest and batch size, and optionally the predicted seconds per strategy
+ * (array of TAHOE_NUM_STRATEGIES, +inf where not applicable). */
+int tahoe_select_strategy(const tahoe_forest_t* f, size_t num_rows, double* predicted_seconds);
+/* Number of kernel launches the last tahoe_predict on this handle issued. */
+int tahoe_last_launch_count(const tahoe_forest_t* f);
+
+/* ---- text loaders (host only) -------------------------------------------------------
+ * generate_forest_from_file, BaseTahoeTest.h:267-352 / generate_data_from_file,
+ * :354-402 (parse only; the caller uploads).  Buffers are released with
+ * tahoe_free_host. */
+int tahoe_load_model_text(const char* path, tahoe_dense_node_t** nodes, int* num_trees, int* depth);
+int tahoe_load_data_text(const char* path, float** data, int* num_rows, int* num_cols, float* missing);
+void tahoe_free_host(void* p);
+
+/* ---- synthetic inputs (device) -------------------------------------------------------
+ * Seeded U(-1,1) sample matrix written straight into device memory; bit-identical
+ * to tahoe_b200.synth.gen_data (replaces generate_data, BaseTahoeTest.h:404-438). */
+int tahoe_gen_data_device(uint64_t seed, size_t row0, size_t num_rows, int num_cols,
+                          float miss_frac, float missing, float* d_out, void* stream);
+
+/* ---- introspection for tests -----------------------------------------------------------
+ * Copies a packed host-side array out of the handle.  which: see TAHOE_EXPORT_*.
+ * Call with buf == NULL to get the size in bytes through *bytes. */
+enum {
+  TAHOE_EXPORT_HEAP_NODES = 0,    /* uint2 [T][2^(depth+1)] 1-based heap: {val bits, meta} */
+  TAHOE_EXPORT_INTERLEAVED = 1,   /* uint2 [nodes][Tpad] after reorder + tree permutation */
+  TAHOE_EXPORT_TREE_ORDER = 2,    /* int32 [Tpad] packed slot -> original tree (-1 = padding) */
+  TAHOE_EXPORT_ORIG_IDS = 3,      /* int32 [nodes][Tpad] packed position -> original heap id */
+  TAHOE_EXPORT_QUANT_WORDS = 4,   /* uint32 [T][2^(depth+1)] rank-quantised trees */
+  TAHOE_EXPORT_QUANT_TABLE = 5,   /* float [sum n_col] sorted distinct thresholds per column */
+  TAHOE_EXPORT_QUANT_OFFSETS = 6, /* int32 [num_cols+1] offsets into the table */
+  TAHOE_EXPORT_LEAF_ORIGIN = 7,   /* int32 [T][2^depth] padded bottom slot -> original leaf heap id */
+  TAHOE_EXPORT_SIMHASH = 8        /* uint64 [T] simhash per original tree */
+};
+int tahoe_forest_export(const tahoe_forest_t* f, int which, void* buf, size_t* bytes);
+
+const char* tahoe_last_error(void);
+const char* tahoe_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TAHOE_B200_H */

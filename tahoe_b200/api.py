@@ -1,0 +1,237 @@
+"""ctypes binding of include/tahoe_b200.h -- the host-side mirror used by tests and bench.
+
+The product is libtahoe_b200.so (hand-written sm_100a CUDA behind a C ABI).  This module
+only marshals pointers.  If the library is missing it raises: there is no Python, numpy
+or torch fallback for any compute entry point.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from .synth import DENSE_NODE, SPARSE_NODE
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "libtahoe_b200.so")
+
+OK, ERR_INVALID, ERR_CUDA, ERR_NOT_APPLICABLE, ERR_IO, ERR_NOMEM = range(6)
+AUTO, DIRECT, SHARED_DATA_PER_THREAD, SHARED_DATA, SHARED_FOREST, SPLIT_SHARED_FOREST = -1, 0, 1, 2, 3, 4
+STRATEGY_NAMES = {DIRECT: "direct", SHARED_DATA_PER_THREAD: "shared_data_per_thread",
+                  SHARED_DATA: "shared_data", SHARED_FOREST: "shared_forest",
+                  SPLIT_SHARED_FOREST: "split_shared_forest"}
+ALL_STRATEGIES = list(STRATEGY_NAMES)
+
+(EXPORT_HEAP_NODES, EXPORT_INTERLEAVED, EXPORT_TREE_ORDER, EXPORT_ORIG_IDS, EXPORT_QUANT_WORDS,
+ EXPORT_QUANT_TABLE, EXPORT_QUANT_OFFSETS, EXPORT_LEAF_ORIGIN, EXPORT_SIMHASH) = range(9)
+
+
+class TahoeError(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__(f"tahoe status {status}: {msg}")
+        self.status = status
+
+
+class NotApplicable(TahoeError):
+    pass
+
+
+class ForestParams(C.Structure):
+    _fields_ = [("num_nodes", C.c_int), ("depth", C.c_int), ("num_trees", C.c_int),
+                ("num_cols", C.c_int), ("algo", C.c_int), ("output", C.c_int),
+                ("threshold", C.c_float), ("global_bias", C.c_float), ("strategy", C.c_int),
+                ("missing", C.c_float)]
+
+
+class ForestInfo(C.Structure):
+    _fields_ = [("num_trees", C.c_int), ("depth", C.c_int), ("num_cols", C.c_int),
+                ("is_sparse", C.c_int), ("num_nodes", C.c_int64), ("node_width_bytes", C.c_int),
+                ("quantized", C.c_int), ("rank_bits", C.c_int), ("col_bits", C.c_int),
+                ("trees_per_chunk", C.c_int), ("num_chunks", C.c_int), ("bytes_heap", C.c_int64),
+                ("bytes_interleaved", C.c_int64), ("bytes_quantized", C.c_int64),
+                ("exchanged_nodes", C.c_int64), ("mean_depth", C.c_double), ("device", C.c_int),
+                ("sm_count", C.c_int), ("smem_optin_bytes", C.c_int)]
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load the CUDA library; fail loudly when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: run `python -m tahoe_b200.build` "
+                          "(there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp, sz = C.c_void_p, C.c_size_t
+    L.tahoe_forest_create_dense.argtypes = [vp, C.POINTER(ForestParams), C.POINTER(vp)]
+    L.tahoe_forest_create_sparse.argtypes = [vp, vp, vp, C.POINTER(ForestParams), C.POINTER(vp)]
+    L.tahoe_forest_destroy.argtypes = [vp]
+    L.tahoe_forest_destroy.restype = None
+    L.tahoe_forest_info.argtypes = [vp, C.POINTER(ForestInfo)]
+    L.tahoe_predict.argtypes = [vp, C.c_int, vp, sz, vp, vp, vp]
+    L.tahoe_predict_host.argtypes = [vp, C.c_int, vp, sz, vp]
+    L.tahoe_strategy_applicable.argtypes = [vp, C.c_int, sz]
+    L.tahoe_select_strategy.argtypes = [vp, sz, C.POINTER(C.c_double)]
+    L.tahoe_last_launch_count.argtypes = [vp]
+    L.tahoe_load_model_text.argtypes = [C.c_char_p, C.POINTER(vp), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.tahoe_load_data_text.argtypes = [C.c_char_p, C.POINTER(vp), C.POINTER(C.c_int),
+                                       C.POINTER(C.c_int), C.POINTER(C.c_float)]
+    L.tahoe_free_host.argtypes = [vp]
+    L.tahoe_free_host.restype = None
+    L.tahoe_gen_data_device.argtypes = [C.c_uint64, sz, sz, C.c_int, C.c_float, C.c_float, vp, vp]
+    L.tahoe_forest_export.argtypes = [vp, C.c_int, vp, C.POINTER(sz)]
+    L.tahoe_last_error.restype = C.c_char_p
+    L.tahoe_version.restype = C.c_char_p
+    _lib = L
+    return L
+
+
+def _check(rc: int):
+    if rc == OK:
+        return
+    msg = lib().tahoe_last_error().decode(errors="replace")
+    raise (NotApplicable if rc == ERR_NOT_APPLICABLE else TahoeError)(rc, msg)
+
+
+def _devptr(t):
+    """torch CUDA tensor / int / None -> void*"""
+    if t is None:
+        return None
+    if isinstance(t, int):
+        return C.c_void_p(t)
+    return C.c_void_p(t.data_ptr())
+
+
+def _stream_ptr(stream):
+    if stream is None:
+        try:
+            import torch
+            if torch.cuda.is_available():
+                return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        except ImportError:
+            pass
+        return None
+    return C.c_void_p(stream if isinstance(stream, int) else stream.cuda_stream)
+
+
+class Forest:
+    """Owns a tahoe_forest_t handle (mirror of dense_adaptive_forest, Struct.h:1710)."""
+
+    def __init__(self, handle, num_trees, num_cols):
+        self._h = handle
+        self.num_trees = num_trees
+        self.num_cols = num_cols
+
+    @classmethod
+    def from_dense(cls, nodes: np.ndarray, num_trees: int, depth: int, num_cols: int, *,
+                   missing: float = 0.0, output: int = 0, threshold: float = 0.0,
+                   global_bias: float = 0.0) -> "Forest":
+        nodes = np.ascontiguousarray(nodes, dtype=DENSE_NODE)
+        assert nodes.shape[0] == num_trees * ((1 << (depth + 1)) - 1), "node count != T*(2^(d+1)-1)"
+        ps = ForestParams(0, depth, num_trees, num_cols, 0, output, threshold, global_bias, 0, missing)
+        h = C.c_void_p()
+        _check(lib().tahoe_forest_create_dense(nodes.ctypes.data_as(C.c_void_p), C.byref(ps), C.byref(h)))
+        return cls(h, num_trees, num_cols)
+
+    @classmethod
+    def from_sparse(cls, nodes: np.ndarray, tree_offsets: np.ndarray, num_cols: int, *,
+                    weights=None, missing: float = 0.0, output: int = 0, threshold: float = 0.0,
+                    global_bias: float = 0.0) -> "Forest":
+        nodes = np.ascontiguousarray(nodes, dtype=SPARSE_NODE)
+        offs = np.ascontiguousarray(tree_offsets, dtype=np.int64)
+        T = offs.shape[0] - 1
+        w = None if weights is None else np.ascontiguousarray(weights, dtype=np.float32)
+        ps = ForestParams(int(offs[-1]), 0, T, num_cols, 0, output, threshold, global_bias, 0, missing)
+        h = C.c_void_p()
+        _check(lib().tahoe_forest_create_sparse(
+            nodes.ctypes.data_as(C.c_void_p), None if w is None else w.ctypes.data_as(C.c_void_p),
+            offs.ctypes.data_as(C.c_void_p), C.byref(ps), C.byref(h)))
+        return cls(h, T, num_cols)
+
+    def close(self):
+        if self._h:
+            lib().tahoe_forest_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self) -> ForestInfo:
+        inf = ForestInfo()
+        _check(lib().tahoe_forest_info(self._h, C.byref(inf)))
+        return inf
+
+    def applicable(self, strategy: int, rows: int) -> bool:
+        return lib().tahoe_strategy_applicable(self._h, strategy, rows) == OK
+
+    def select(self, rows: int):
+        t = (C.c_double * 5)()
+        s = lib().tahoe_select_strategy(self._h, rows, t)
+        return s, list(t)
+
+    def predict(self, data, preds=None, *, strategy: int = AUTO, leaf_ids=None, stream=None):
+        """data / preds / leaf_ids: torch CUDA tensors (float32 [R,C], float32 [R], int32 [R,T])."""
+        import torch
+        rows = int(data.shape[0])
+        assert data.is_cuda and data.dtype == torch.float32 and data.is_contiguous()
+        assert data.shape[1] == self.num_cols
+        if preds is None:
+            preds = torch.empty(rows, dtype=torch.float32, device=data.device)
+        _check(lib().tahoe_predict(self._h, strategy, _devptr(data), rows, _devptr(preds),
+                                   _devptr(leaf_ids), _stream_ptr(stream)))
+        return preds
+
+    def predict_host(self, data: np.ndarray, preds: np.ndarray | None = None, *, strategy: int = AUTO):
+        """Host buffers in, host buffers out (numpy or pinned torch CPU tensors)."""
+        rows = int(data.shape[0])
+        if preds is None:
+            preds = np.empty(rows, dtype=np.float32)
+        dp = data.ctypes.data if isinstance(data, np.ndarray) else data.data_ptr()
+        pp = preds.ctypes.data if isinstance(preds, np.ndarray) else preds.data_ptr()
+        _check(lib().tahoe_predict_host(self._h, strategy, C.c_void_p(dp), rows, C.c_void_p(pp)))
+        return preds
+
+    def launches(self) -> int:
+        return lib().tahoe_last_launch_count(self._h)
+
+    def export(self, which: int, dtype) -> np.ndarray:
+        n = C.c_size_t(0)
+        _check(lib().tahoe_forest_export(self._h, which, None, C.byref(n)))
+        buf = np.empty(n.value // np.dtype(dtype).itemsize, dtype=dtype)
+        _check(lib().tahoe_forest_export(self._h, which, buf.ctypes.data_as(C.c_void_p), C.byref(n)))
+        return buf
+
+
+def load_model_text(path: str):
+    p, t, d = C.c_void_p(), C.c_int(), C.c_int()
+    _check(lib().tahoe_load_model_text(path.encode(), C.byref(p), C.byref(t), C.byref(d)))
+    n = t.value * ((1 << (d.value + 1)) - 1)
+    arr = np.frombuffer((C.c_char * (n * 12)).from_address(p.value), dtype=DENSE_NODE).copy()
+    lib().tahoe_free_host(p)
+    return arr, t.value, d.value
+
+
+def load_data_text(path: str):
+    p, r, c, m = C.c_void_p(), C.c_int(), C.c_int(), C.c_float()
+    _check(lib().tahoe_load_data_text(path.encode(), C.byref(p), C.byref(r), C.byref(c), C.byref(m)))
+    n = r.value * c.value
+    arr = np.frombuffer((C.c_char * (n * 4)).from_address(p.value), dtype=np.float32).copy()
+    lib().tahoe_free_host(p)
+    return arr.reshape(r.value, c.value), m.value
+
+
+def gen_data_device(seed: int, rows: int, cols: int, *, row0: int = 0, miss_frac: float = 0.0,
+                    missing: float = -999.0, out=None, stream=None):
+    import torch
+    if out is None:
+        out = torch.empty((rows, cols), dtype=torch.float32, device="cuda")
+    _check(lib().tahoe_gen_data_device(seed, row0, rows, cols, miss_frac, missing, _devptr(out),
+                                       _stream_ptr(stream)))
+    return out

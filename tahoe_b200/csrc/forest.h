@@ -1,0 +1,134 @@
+// forest.h -- internal representation behind the opaque tahoe_forest_t handle.
+//
+// One forest is packed into up to four layouts, each built for the memory level
+// a strategy serves it from (DESIGN.md "Data layout in HBM"):
+//
+//   H8  heap layout, 8 B/node, tree-major, 1-based heap        DIRECT, PER_THREAD (L2 / HBM)
+//   S16 compact layout, 16 B/node, breadth-first per tree      sparse forests      (L2 / HBM)
+//   I8  node-major interleaved [node][tree], 8 B/node, children swapped by split
+//       probability (exchange bit) and trees grouped by simhash  SHARED_DATA       (L1 / L2)
+//   Q4  rank-quantised heap, 4 B/node, padded to full depth     SHARED_FOREST / SPLIT (shared memory)
+//
+// Reference counterparts: dense_adaptive_forest members bits_values_*/bits_*_reorg_*
+// (Struct.h:2186-2207) and the packer that fills them (Struct.h:1756-1986).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/tahoe_b200.h"
+
+namespace tahoe {
+
+constexpr int kMetaFidMask = (1 << 29) - 1;      // I8: fid in bits 0..28
+constexpr uint32_t kMetaExchange = 1u << 29;     // I8 only (reference EXCHANGE_MASK_INT is bit 31, Struct.h:64)
+constexpr uint32_t kMetaDefLeft = 1u << 30;      // same bit as the reference's DEF_LEFT_MASK, Struct.h:58
+constexpr uint32_t kMetaLeaf = 1u << 31;         // same bit as IS_LEAF_MASK, Struct.h:59
+
+constexpr int kQuantColShift = 7;                // Q4 word: column byte offset (col * 128) in bits 7..
+constexpr int kQuantMaxDepth = 14;               // 2^(d+1) words per tree must fit shared memory
+constexpr int kQuantMaxCols = 64;                // one warp tile = cols * 128 B of shared memory
+constexpr int kSmemWarps = 16;                   // warps per CTA of the shared-memory-forest kernel
+constexpr int kSmemTileBufs = 2;                 // double-buffered sample tiles per warp
+
+struct HostPack {
+  // H8 / S16
+  std::vector<uint2> heap;            // dense: [T][2^(d+1)]; entry 0 of each tree unused
+  std::vector<uint4> sparse;          // sparse: {val, bits, left_idx, 0}
+  std::vector<int64_t> tree_offsets;  // sparse: [T+1]
+  // I8
+  int tpad = 0;                       // trees padded to a multiple of 32
+  std::vector<uint2> inter;           // [N][tpad]
+  std::vector<int32_t> tree_order;    // [tpad] slot -> original tree, -1 padding
+  std::vector<int32_t> orig_ids;      // [N][tpad] position -> original heap id
+  std::vector<uint64_t> simhash;      // [T]
+  // Q4
+  std::vector<uint32_t> qwords;       // [T][2^(d+1)]
+  std::vector<float> qtable;          // sorted distinct thresholds, all columns back to back
+  std::vector<int32_t> qoffsets;      // [C+1]
+  std::vector<int32_t> leaf_origin;   // [T][2^d]
+};
+
+struct Workspace {                     // per-stream scratch, grow-only (no per-call malloc)
+  uint32_t* qtiles = nullptr;          // [tiles][C][32] rank words
+  uint32_t* tile_flags = nullptr;      // [tiles] bit0 = some feature of some row equals the sentinel
+  size_t cap_tiles = 0;
+  float* slab_data = nullptr;          // tahoe_predict_host staging
+  float* slab_preds = nullptr;
+  size_t cap_slab_rows = 0;
+  cudaStream_t stream = nullptr;       // owned (predict_host only)
+};
+
+constexpr int kHostSlots = 3;
+
+}  // namespace tahoe
+
+struct tahoe_forest {
+  tahoe_forest_params_t params{};
+  bool sparse = false;
+  int depth = 0;                 // dense: given; sparse: max level found
+  int64_t num_nodes = 0;         // real (reachable) nodes
+  int node_width = 0;            // reference width rule
+  int64_t exchanged = 0;
+  double mean_depth = 0.0;
+
+  // quantised layout parameters
+  bool quant = false;
+  int rank_bits = 0, col_bits = 0, rank_shift = 0;
+  uint32_t col_mask = 0, miss_code = 0;
+  int trees_per_chunk = 0, num_chunks = 0;
+  size_t smem_bytes = 0;
+
+  tahoe::HostPack host;
+
+  // device copies
+  uint2* d_heap = nullptr;
+  uint4* d_sparse = nullptr;
+  int64_t* d_tree_offsets = nullptr;
+  uint2* d_inter = nullptr;
+  int32_t* d_tree_order = nullptr;
+  int32_t* d_orig_ids = nullptr;
+  uint32_t* d_qwords = nullptr;
+  float* d_qtable = nullptr;
+  int32_t* d_qoffsets = nullptr;
+  int32_t* d_leaf_origin = nullptr;
+
+  int device = 0, sm_count = 0, smem_optin = 0, l2_bytes = 0;
+  tahoe::Workspace ws[1 + tahoe::kHostSlots];  // [0] = tahoe_predict, [1..] = predict_host slabs
+  int last_launches = 0;
+};
+
+namespace tahoe {
+
+void set_error(const std::string& msg);
+int cuda_fail(cudaError_t e, const char* what);
+#define TAHOE_CUDA(call)                                         \
+  do {                                                           \
+    cudaError_t e__ = (call);                                    \
+    if (e__ != cudaSuccess) return ::tahoe::cuda_fail(e__, #call); \
+  } while (0)
+
+// packer.cu
+int pack_dense(tahoe_forest* f, const tahoe_dense_node_t* nodes);
+int pack_sparse(tahoe_forest* f, const tahoe_sparse_node_t* nodes, const float* weights,
+                const int64_t* tree_offsets);
+int upload(tahoe_forest* f);
+void plan_chunks(tahoe_forest* f);
+
+// launchers (kernels_*.cu); each returns a status and adds to *launches
+struct PredictArgs {
+  const float* data;
+  size_t rows;
+  float* preds;
+  int32_t* leaf_ids;
+  cudaStream_t stream;
+  Workspace* ws;
+};
+int launch_direct(tahoe_forest* f, const PredictArgs& a, bool rows_in_smem, int* launches);
+int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches);
+int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches);
+int ensure_workspace(tahoe_forest* f, Workspace* ws, size_t rows);
+
+}  // namespace tahoe

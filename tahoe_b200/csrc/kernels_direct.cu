@@ -1,0 +1,120 @@
+// kernels_direct.cu -- thread = sample strategies with the forest read through L1/L2.
+//
+//   DIRECT                  (reference K1, Struct.h:1196-1240): features straight from global
+//   SHARED_DATA_PER_THREAD  (reference K2, Struct.h:1610-1704): the block's rows staged once in
+//                           shared memory, COLUMN-major ([col][thread]) so that lane i always
+//                           reads bank i -- no bank conflicts whatever feature each lane needs
+//                           (the reference copies each row serially, uncoalesced, row-major).
+// Both sum leaf values in tree order 0..T-1 exactly like predict_on_cpu
+// (BaseTahoeTest.h:462-466), so their raw scores are bit-identical to the CPU's.
+#include "device_utils.cuh"
+#include "forest.h"
+
+namespace tahoe {
+
+constexpr int kDirectThreads = 256;
+
+struct DirectParams {
+  const float* data;
+  size_t rows;
+  int cols;
+  int num_trees;
+  float missing;
+  const uint2* heap;            // dense: [T][2^(d+1)]
+  int64_t tree_stride;          // 2^(d+1)
+  const uint4* sparse;          // sparse nodes
+  const int64_t* tree_offsets;  // sparse
+  float* preds;
+  int32_t* leaf_ids;
+  Transform tf;
+};
+
+template <bool SPARSE, bool SMEM_ROWS>
+__global__ void __launch_bounds__(kDirectThreads) k_direct(DirectParams p) {
+  extern __shared__ float s_rows[];  // SMEM_ROWS: [cols][kDirectThreads]
+  const size_t block_row0 = (size_t)blockIdx.x * kDirectThreads;
+  const size_t row = block_row0 + threadIdx.x;
+  if (SMEM_ROWS) {
+    // the block's rows are one contiguous run of floats: coalesced read, transposed store
+    const size_t nrows = min((size_t)kDirectThreads, p.rows - block_row0);
+    const size_t total = nrows * (size_t)p.cols;
+    const float* src = p.data + block_row0 * (size_t)p.cols;
+    for (size_t w = threadIdx.x; w < total; w += kDirectThreads) {
+      const int r = (int)(w / p.cols), c = (int)(w % p.cols);
+      s_rows[c * kDirectThreads + r] = __ldg(src + w);
+    }
+    __syncthreads();
+  }
+  if (row >= p.rows) return;
+  const float* grow = p.data + row * (size_t)p.cols;
+  float acc = 0.0f;
+  for (int t = 0; t < p.num_trees; ++t) {
+    float leaf_val;
+    int32_t leaf_id;
+    if (!SPARSE) {
+      const uint2* tree = p.heap + (int64_t)t * p.tree_stride;
+      uint32_t n = 1;
+      uint2 e = __ldg(tree + 1);
+      while (!(e.y & kMetaLeaf)) {
+        const int fid = e.y & 0x3FFFFFFF;
+        const float v = SMEM_ROWS ? s_rows[fid * kDirectThreads + threadIdx.x] : __ldg(grow + fid);
+        n = 2 * n + (branch_right(v, __uint_as_float(e.x), e.y & kMetaDefLeft, p.missing) ? 1u : 0u);
+        e = __ldg(tree + n);
+      }
+      leaf_val = __uint_as_float(e.x);
+      leaf_id = (int32_t)n - 1;
+    } else {
+      const uint4* tree = p.sparse + p.tree_offsets[t];
+      uint32_t n = 0;
+      uint4 e = __ldg(tree);
+      while (!(e.y & kMetaLeaf)) {
+        const int fid = e.y & 0x3FFFFFFF;
+        const float v = SMEM_ROWS ? s_rows[fid * kDirectThreads + threadIdx.x] : __ldg(grow + fid);
+        n = e.z + (branch_right(v, __uint_as_float(e.x), e.y & kMetaDefLeft, p.missing) ? 1u : 0u);
+        e = __ldg(tree + n);
+      }
+      leaf_val = __uint_as_float(e.x);
+      leaf_id = (int32_t)n;
+    }
+    acc += leaf_val;
+    if (p.leaf_ids) p.leaf_ids[row * (size_t)p.num_trees + t] = leaf_id;
+  }
+  p.preds[row] = apply_transform(acc, p.tf);
+}
+
+int launch_direct(tahoe_forest* f, const PredictArgs& a, bool rows_in_smem, int* launches) {
+  if (a.rows == 0) return TAHOE_OK;
+  DirectParams p{};
+  p.data = a.data;
+  p.rows = a.rows;
+  p.cols = f->params.num_cols;
+  p.num_trees = f->params.num_trees;
+  p.missing = f->params.missing;
+  p.heap = f->d_heap;
+  p.tree_stride = (int64_t)1 << (f->depth + 1);
+  p.sparse = f->d_sparse;
+  p.tree_offsets = f->d_tree_offsets;
+  p.preds = a.preds;
+  p.leaf_ids = a.leaf_ids;
+  p.tf = Transform{f->params.output, (float)f->params.num_trees, f->params.threshold,
+                   f->params.global_bias};
+  const size_t blocks = (a.rows + kDirectThreads - 1) / kDirectThreads;
+  if (blocks > 0x7FFFFFFFull) { set_error("too many rows for one launch"); return TAHOE_ERR_INVALID; }
+  const size_t smem = rows_in_smem ? (size_t)p.cols * kDirectThreads * sizeof(float) : 0;
+  if (smem > (size_t)f->smem_optin) {
+    set_error("SHARED_DATA_PER_THREAD: a block's rows do not fit shared memory");
+    return TAHOE_ERR_NOT_APPLICABLE;
+  }
+  auto go = [&](auto kern) -> int {
+    if (smem > 48 * 1024)
+      TAHOE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)blocks, kDirectThreads, smem, a.stream>>>(p);
+    TAHOE_CUDA(cudaGetLastError());
+    ++*launches;
+    return TAHOE_OK;
+  };
+  if (f->sparse) return rows_in_smem ? go(k_direct<true, true>) : go(k_direct<true, false>);
+  return rows_in_smem ? go(k_direct<false, true>) : go(k_direct<false, false>);
+}
+
+}  // namespace tahoe

@@ -1,0 +1,378 @@
+// packer.cu -- forest loader / packer (host side).
+//
+// B200-first redesign of dense_adaptive_forest::init + swap_child
+// (Struct.h:1712-1986) and encode_node_adaptive (Struct.h:77-98):
+//   * probability reorder: a node whose right child is heavier gets its two
+//     subtrees swapped and an exchange bit (same rule, Struct.h:1781-1786),
+//   * a REAL simhash over (level, feature) tokens orders similar trees next to
+//     each other (the reference hashes uninitialised buffers, Struct.h:1854-1872),
+//   * node-major interleaved layout [node][tree] for the lane=tree kernel
+//     (Struct.h:1911-1923),
+//   * the reference's adaptive 1/2/4-byte feature-id width (Struct.h:1827-1852)
+//     becomes a rank-quantised 4-byte node: the float threshold is replaced by
+//     its rank among the forest's distinct thresholds on that column, so a whole
+//     node (rank, column, default direction) is one shared-memory word and the
+//     branch test is one unsigned compare.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <numeric>
+
+#include "forest.h"
+
+namespace tahoe {
+
+static inline uint32_t f2u(float x) { uint32_t u; std::memcpy(&u, &x, 4); return u; }
+
+static inline uint64_t mix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+
+static int ceil_log2(uint64_t v) { int b = 0; while ((1ull << b) < v) ++b; return b; }
+
+// Reference width rule, Struct.h:1831-1852: fid_len = (log2(max_fid)+3)/8.
+static int width_rule(int max_fid) {
+  if (max_fid <= 0) return 0;  // log(0): undefined in the reference
+  double len = (std::log((double)max_fid) / std::log(2.0) + 3.0) / 8.0;
+  if (len > 0.0 && len < 1.0) return 1;
+  if (len >= 1.0 && len < 2.0) return 2;
+  if (len >= 2.0 && len < 4.0) return 4;
+  return 0;
+}
+
+// ---- dense ---------------------------------------------------------------------
+struct TreeScratch {
+  std::vector<float> val, weight;
+  std::vector<uint32_t> meta;
+  std::vector<int32_t> orig;
+};
+
+static void swap_subtrees(TreeScratch& t, int64_t a, int64_t b, int64_t npt) {
+  // iterative level-by-level swap of the two complete subtrees rooted at a and b
+  int64_t width = 1;
+  while (a < npt) {
+    for (int64_t i = 0; i < width; ++i) {
+      std::swap(t.val[a + i], t.val[b + i]);
+      std::swap(t.weight[a + i], t.weight[b + i]);
+      std::swap(t.meta[a + i], t.meta[b + i]);
+      std::swap(t.orig[a + i], t.orig[b + i]);
+    }
+    a = 2 * a + 1;
+    b = 2 * b + 1;
+    width *= 2;
+  }
+}
+
+static int build_quant(tahoe_forest* f, const tahoe_dense_node_t* nodes);
+
+int pack_dense(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
+  const int T = f->params.num_trees, d = f->params.depth, C = f->params.num_cols;
+  if (T < 0 || d < 0 || d > 26 || C < 1) { set_error("invalid forest parameters"); return TAHOE_ERR_INVALID; }
+  const int64_t npt = ((int64_t)1 << (d + 1)) - 1;
+  const int64_t W = (int64_t)1 << (d + 1);
+  HostPack& h = f->host;
+  f->depth = d;
+
+  // ---- reachability, validation, statistics
+  std::vector<uint8_t> reach((size_t)npt);
+  int max_fid = 0;
+  int64_t real_nodes = 0;
+  double depth_acc = 0.0;
+  for (int t = 0; t < T; ++t) {
+    const tahoe_dense_node_t* tr = nodes + (int64_t)t * npt;
+    std::fill(reach.begin(), reach.end(), 0);
+    reach[0] = 1;
+    for (int64_t k = 0; k < npt; ++k) {
+      if (!reach[k]) continue;
+      ++real_nodes;
+      const bool leaf = tr[k].bits < 0;
+      if (leaf) continue;
+      const int fid = tr[k].bits & 0x3FFFFFFF;
+      if (2 * k + 2 >= npt) { set_error("reachable internal node on the bottom level"); return TAHOE_ERR_INVALID; }
+      if (fid >= C) { set_error("feature id >= num_cols"); return TAHOE_ERR_INVALID; }
+      if (fid >= (1 << 29)) { set_error("feature id needs more than 29 bits"); return TAHOE_ERR_INVALID; }
+      max_fid = std::max(max_fid, fid);
+      reach[2 * k + 1] = reach[2 * k + 2] = 1;
+      int level = 0; for (int64_t q = k + 1; q > 1; q >>= 1) ++level;
+      depth_acc += std::ldexp(1.0, -level);
+    }
+  }
+  f->num_nodes = real_nodes;
+  f->node_width = width_rule(max_fid);
+  f->mean_depth = T ? depth_acc / T : 0.0;
+
+  // ---- H8: 1-based heap, 8 B/node
+  h.heap.assign((size_t)T * W, make_uint2(0, kMetaLeaf));
+  for (int t = 0; t < T; ++t) {
+    const tahoe_dense_node_t* tr = nodes + (int64_t)t * npt;
+    uint2* out = h.heap.data() + (int64_t)t * W;
+    for (int64_t k = 0; k < npt; ++k) out[k + 1] = make_uint2(f2u(tr[k].val), (uint32_t)tr[k].bits);
+  }
+
+  // ---- I8: probability reorder + simhash order + node-major interleave
+  h.tpad = ((T + 31) / 32) * 32;
+  if (h.tpad == 0) h.tpad = 32;
+  const bool build_inter = (double)npt * h.tpad * 12.0 <= 6.0e9;
+  h.simhash.assign(T, 0);
+  std::vector<TreeScratch> trees(build_inter ? T : 0);
+  int64_t exchanged = 0;
+  for (int t = 0; t < T; ++t) {
+    const tahoe_dense_node_t* tr = nodes + (int64_t)t * npt;
+    // simhash over (level, fid) tokens of reachable internal nodes
+    int cnt[64] = {0};
+    std::fill(reach.begin(), reach.end(), 0);
+    reach[0] = 1;
+    for (int64_t k = 0; k < npt; ++k) {
+      if (!reach[k] || tr[k].bits < 0) continue;
+      reach[2 * k + 1] = reach[2 * k + 2] = 1;
+      int level = 0; for (int64_t q = k + 1; q > 1; q >>= 1) ++level;
+      uint64_t hsh = mix64(((uint64_t)level << 32) ^ (uint64_t)(tr[k].bits & 0x3FFFFFFF));
+      // shallow nodes decide more traffic: weight tokens by 2^-(level/2)
+      int wgt = std::max(1, 16 >> (level / 2));
+      for (int b = 0; b < 64; ++b) cnt[b] += ((hsh >> b) & 1) ? wgt : -wgt;
+    }
+    uint64_t sh = 0;
+    for (int b = 0; b < 64; ++b) if (cnt[b] > 0) sh |= 1ull << b;
+    h.simhash[t] = sh;
+    if (!build_inter) continue;
+    TreeScratch& s = trees[t];
+    s.val.resize(npt); s.weight.resize(npt); s.meta.resize(npt); s.orig.resize(npt);
+    for (int64_t k = 0; k < npt; ++k) {
+      s.val[k] = tr[k].val;
+      s.weight[k] = tr[k].weight;
+      uint32_t b = (uint32_t)tr[k].bits;
+      s.meta[k] = (b & kMetaFidMask) | (b & kMetaDefLeft) | (b & kMetaLeaf);
+      s.orig[k] = (int32_t)k;
+    }
+    // bottom-up child swap, Struct.h:1775-1825
+    for (int lv = d - 1; lv >= 0; --lv) {
+      for (int64_t k = ((int64_t)1 << lv) - 1; k < ((int64_t)1 << (lv + 1)) - 1; ++k) {
+        if (s.meta[k] & kMetaLeaf) continue;
+        if (s.weight[2 * k + 1] < s.weight[2 * k + 2]) {
+          s.meta[k] |= kMetaExchange;
+          swap_subtrees(s, 2 * k + 1, 2 * k + 2, npt);
+          ++exchanged;
+        }
+      }
+    }
+  }
+  f->exchanged = exchanged;
+  h.tree_order.assign(h.tpad, -1);
+  {
+    std::vector<int> order(T);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(),
+                     [&](int a, int b) { return h.simhash[a] < h.simhash[b]; });
+    for (int i = 0; i < T; ++i) h.tree_order[i] = order[i];
+  }
+  if (build_inter) {
+    h.inter.assign((size_t)npt * h.tpad, make_uint2(0, kMetaLeaf));  // padding slot = leaf 0.0
+    h.orig_ids.assign((size_t)npt * h.tpad, 0);
+    for (int slot = 0; slot < T; ++slot) {
+      const TreeScratch& s = trees[h.tree_order[slot]];
+      for (int64_t k = 0; k < npt; ++k) {
+        h.inter[(size_t)k * h.tpad + slot] = make_uint2(f2u(s.val[k]), s.meta[k]);
+        h.orig_ids[(size_t)k * h.tpad + slot] = s.orig[k];
+      }
+    }
+  }
+  return build_quant(f, nodes);
+}
+
+// ---- Q4: rank-quantised heap ------------------------------------------------------
+static int build_quant(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
+  const int T = f->params.num_trees, d = f->depth, C = f->params.num_cols;
+  HostPack& h = f->host;
+  f->quant = false;
+  if (d < 1 || d > kQuantMaxDepth || C > kQuantMaxCols || T < 1) return TAHOE_OK;
+  const int64_t npt = ((int64_t)1 << (d + 1)) - 1;
+  const int64_t W = (int64_t)1 << (d + 1);
+  const int64_t L = (int64_t)1 << d;
+
+  // state per 1-based heap position: 0 = reachable internal, >0 = under/at leaf (origin+1)
+  std::vector<int32_t> origin((size_t)W);
+  std::vector<std::vector<float>> thr(C);
+  for (int t = 0; t < T; ++t) {
+    const tahoe_dense_node_t* tr = nodes + (int64_t)t * npt;
+    origin[1] = (tr[0].bits < 0) ? 1 : 0;
+    for (int64_t i = 1; i < L; ++i) {
+      int32_t o = origin[i];
+      if (o == 0) {
+        float v = tr[i - 1].val;
+        if (!std::isnan(v)) thr[tr[i - 1].bits & 0x3FFFFFFF].push_back(v);
+        for (int c = 0; c < 2; ++c) origin[2 * i + c] = (tr[2 * i + c - 1].bits < 0) ? (int32_t)(2 * i + c) : 0;
+      } else {
+        origin[2 * i] = origin[2 * i + 1] = o;
+      }
+    }
+  }
+  h.qoffsets.assign(C + 1, 0);
+  size_t max_n = 0;
+  for (int c = 0; c < C; ++c) {
+    std::sort(thr[c].begin(), thr[c].end());
+    thr[c].erase(std::unique(thr[c].begin(), thr[c].end()), thr[c].end());  // == merges -0/+0
+    max_n = std::max(max_n, thr[c].size());
+    h.qoffsets[c + 1] = h.qoffsets[c] + (int32_t)thr[c].size();
+  }
+  const int rb = std::max(1, ceil_log2(max_n + 2));  // ranks 0..n, sentinel code 2^rb-1 > n
+  const int cb = std::max(1, ceil_log2((uint64_t)C));
+  if (rb + cb + kQuantColShift > 32) return TAHOE_OK;  // does not fit one word: no Q4 layout
+  h.qtable.clear();
+  h.qtable.reserve(h.qoffsets[C]);
+  for (int c = 0; c < C; ++c) h.qtable.insert(h.qtable.end(), thr[c].begin(), thr[c].end());
+  f->rank_bits = rb;
+  f->col_bits = cb;
+  f->rank_shift = 32 - rb;
+  f->col_mask = ((1u << cb) - 1u) << kQuantColShift;
+  f->miss_code = ((1u << rb) - 1u) << f->rank_shift;
+
+  h.qwords.assign((size_t)T * W, 0u);
+  h.leaf_origin.assign((size_t)T * L, 0);
+  for (int t = 0; t < T; ++t) {
+    const tahoe_dense_node_t* tr = nodes + (int64_t)t * npt;
+    uint32_t* out = h.qwords.data() + (int64_t)t * W;
+    int32_t* lo = h.leaf_origin.data() + (int64_t)t * L;
+    origin[1] = (tr[0].bits < 0) ? 1 : 0;
+    for (int64_t i = 1; i < W; ++i) {
+      int32_t o = origin[i];
+      if (i < L) {
+        if (o == 0) {
+          const int fid = tr[i - 1].bits & 0x3FFFFFFF;
+          const float v = tr[i - 1].val;
+          uint32_t k;
+          if (std::isnan(v)) k = (uint32_t)thr[fid].size();  // val >= NaN is never true
+          else k = (uint32_t)(std::lower_bound(thr[fid].begin(), thr[fid].end(), v) - thr[fid].begin());
+          out[i] = (k << f->rank_shift) | ((uint32_t)fid << kQuantColShift) |
+                   ((tr[i - 1].bits & 0x40000000) ? 1u : 0u);
+          for (int c = 0; c < 2; ++c) origin[2 * i + c] = (tr[2 * i + c - 1].bits < 0) ? (int32_t)(2 * i + c) : 0;
+        } else {
+          out[i] = 0u;  // below an early leaf: both children lead to the same value
+          origin[2 * i] = origin[2 * i + 1] = o;
+        }
+      } else {
+        // bottom slot: o > 0 always (validated: reachable bottom nodes are leaves)
+        out[i] = f2u(tr[o - 1].val);
+        lo[i - L] = o - 1;
+      }
+    }
+  }
+  f->quant = true;
+  return TAHOE_OK;
+}
+
+// ---- sparse (compact) forests --------------------------------------------------------
+// Replaces sparse_forest::init (Struct.h:2327-2345).  Nodes stay breadth-first per
+// tree with the two children adjacent, so both children of a node share one 32-byte
+// sector; the 12-byte reference node is padded to 16 B for one aligned 128-bit load.
+int pack_sparse(tahoe_forest* f, const tahoe_sparse_node_t* nodes, const float* weights,
+                const int64_t* tree_offsets) {
+  (void)weights;  // children are adjacent: the probability swap has nothing to win here
+  const int T = f->params.num_trees, C = f->params.num_cols;
+  if (T < 0 || C < 1 || !tree_offsets) { set_error("invalid sparse forest parameters"); return TAHOE_ERR_INVALID; }
+  HostPack& h = f->host;
+  h.tree_offsets.assign(tree_offsets, tree_offsets + T + 1);
+  const int64_t total = tree_offsets[T];
+  h.sparse.resize((size_t)total);
+  int max_fid = 0, max_level = 0;
+  double depth_acc = 0.0;
+  std::vector<int32_t> level;
+  for (int t = 0; t < T; ++t) {
+    const int64_t base = tree_offsets[t], n = tree_offsets[t + 1] - base;
+    if (n < 1) { set_error("empty tree"); return TAHOE_ERR_INVALID; }
+    level.assign((size_t)n, -1);
+    level[0] = 0;
+    for (int64_t k = 0; k < n; ++k) {
+      const tahoe_sparse_node_t& nd = nodes[base + k];
+      h.sparse[base + k] = make_uint4(f2u(nd.val), (uint32_t)nd.bits, (uint32_t)nd.left_idx, 0u);
+      if (nd.bits < 0 || level[k] < 0) continue;  // leaf, or unreachable
+      const int fid = nd.bits & 0x3FFFFFFF;
+      if (fid >= C) { set_error("feature id >= num_cols"); return TAHOE_ERR_INVALID; }
+      if (nd.left_idx <= k || (int64_t)nd.left_idx + 1 >= n) {
+        set_error("sparse child index out of range (children must follow their parent)");
+        return TAHOE_ERR_INVALID;
+      }
+      max_fid = std::max(max_fid, fid);
+      level[nd.left_idx] = level[nd.left_idx + 1] = level[k] + 1;
+      max_level = std::max(max_level, level[k] + 1);
+      depth_acc += std::ldexp(1.0, -level[k]);
+    }
+  }
+  f->sparse = true;
+  f->depth = max_level;
+  f->num_nodes = total;
+  f->node_width = width_rule(max_fid);
+  f->mean_depth = T ? depth_acc / T : 0.0;
+  f->quant = false;
+  return TAHOE_OK;
+}
+
+// ---- shared-memory chunk plan ------------------------------------------------------------
+// Shared memory of one persistent CTA (227 KB opt-in, vs the reference's 0.8 * 48 KB,
+// Struct.h:215-220): [warp tiles][forest chunk][mbarriers].
+void plan_chunks(tahoe_forest* f) {
+  f->trees_per_chunk = 0;
+  f->num_chunks = 0;
+  f->smem_bytes = 0;
+  if (!f->quant) return;
+  const size_t tile_bytes = (size_t)f->params.num_cols * 128;
+  const size_t tiles = (size_t)kSmemWarps * kSmemTileBufs * tile_bytes;
+  const size_t bars = 1024;
+  const size_t tree_bytes = ((size_t)1 << (f->depth + 1)) * 4;
+  if ((size_t)f->smem_optin < tiles + bars + tree_bytes) return;
+  size_t avail = (size_t)f->smem_optin - tiles - bars;
+  int tpc = (int)std::min<size_t>(avail / tree_bytes, (size_t)f->params.num_trees);
+  // balance the chunks: same chunk count, trees spread evenly
+  int chunks = (f->params.num_trees + tpc - 1) / tpc;
+  tpc = (f->params.num_trees + chunks - 1) / chunks;
+  f->trees_per_chunk = tpc;
+  f->num_chunks = chunks;
+  f->smem_bytes = tiles + bars + (size_t)tpc * tree_bytes;
+}
+
+template <typename T>
+static int to_device(T** dst, const std::vector<T>& src) {
+  *dst = nullptr;
+  if (src.empty()) return TAHOE_OK;
+  TAHOE_CUDA(cudaMalloc((void**)dst, src.size() * sizeof(T)));
+  TAHOE_CUDA(cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return TAHOE_OK;
+}
+
+int upload(tahoe_forest* f) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    // No GPU (authoring container): keep the host-side pack for inspection only.  Every
+    // predict call on such a handle fails with TAHOE_ERR_CUDA -- there is no CPU path.
+    cudaGetLastError();
+    f->device = -1;
+    f->sm_count = 148;
+    f->smem_optin = 232448;
+    plan_chunks(f);
+    return TAHOE_OK;
+  }
+  cudaDeviceProp prop;
+  TAHOE_CUDA(cudaGetDevice(&f->device));
+  TAHOE_CUDA(cudaGetDeviceProperties(&prop, f->device));
+  f->sm_count = prop.multiProcessorCount;
+  f->smem_optin = (int)prop.sharedMemPerBlockOptin;
+  f->l2_bytes = prop.l2CacheSize;
+  plan_chunks(f);
+  HostPack& h = f->host;
+  int rc;
+  if ((rc = to_device(&f->d_heap, h.heap))) return rc;
+  if ((rc = to_device(&f->d_sparse, h.sparse))) return rc;
+  if ((rc = to_device(&f->d_tree_offsets, h.tree_offsets))) return rc;
+  if ((rc = to_device(&f->d_inter, h.inter))) return rc;
+  if ((rc = to_device(&f->d_tree_order, h.tree_order))) return rc;
+  if ((rc = to_device(&f->d_orig_ids, h.orig_ids))) return rc;
+  if ((rc = to_device(&f->d_qwords, h.qwords))) return rc;
+  if ((rc = to_device(&f->d_qtable, h.qtable))) return rc;
+  if ((rc = to_device(&f->d_qoffsets, h.qoffsets))) return rc;
+  if ((rc = to_device(&f->d_leaf_origin, h.leaf_origin))) return rc;
+  return TAHOE_OK;
+}
+
+}  // namespace tahoe

@@ -1,0 +1,102 @@
+"""Test-only numpy emulators of what each kernel does with each PACKED layout.
+They let the CPU suite localise packer bugs without a GPU.  Not a product path."""
+import numpy as np
+
+LEAF, DEFLEFT, EXCH, FIDMASK = 1 << 31, 1 << 30, 1 << 29, (1 << 29) - 1
+
+
+def _right(v, thr, def_left, missing):
+    with np.errstate(invalid="ignore"):
+        miss = np.abs((v - np.float32(missing)).astype(np.float32)) <= np.float32(1e-6)
+        return np.where(miss, ~def_left, v >= thr)
+
+
+def heap_traverse(heap, T, depth, data, missing):
+    """H8: uint32 pairs [T][2^(d+1)][2], 1-based heap.  -> (leaf values [R,T], leaf ids [R,T])"""
+    W = 1 << (depth + 1)
+    h = heap.reshape(T, W, 2)
+    R = data.shape[0]
+    vals = np.zeros((R, T), np.float32)
+    ids = np.zeros((R, T), np.int32)
+    for t in range(T):
+        n = np.ones(R, np.int64)
+        for _ in range(depth + 1):
+            e = h[t, n]
+            leaf = (e[:, 1] & LEAF) != 0
+            fid = (e[:, 1] & 0x3FFFFFFF).astype(np.int64)
+            fid = np.where(leaf, 0, fid)
+            v = data[np.arange(R), fid]
+            c = _right(v, e[:, 0].view(np.float32), (e[:, 1] & DEFLEFT) != 0, missing)
+            n = np.where(leaf, n, 2 * n + c)
+        e = h[t, n]
+        assert np.all(e[:, 1] & LEAF)
+        vals[:, t] = e[:, 0].view(np.float32)
+        ids[:, t] = n - 1
+    return vals, ids
+
+
+def interleaved_traverse(inter, orig_ids, tree_order, tpad, depth, T, data, missing):
+    """I8: [N][tpad][2] with exchange bits.  -> (values [R,T], ids [R,T]) in ORIGINAL tree order"""
+    N = (1 << (depth + 1)) - 1
+    h = inter.reshape(N, tpad, 2)
+    oid = orig_ids.reshape(N, tpad)
+    R = data.shape[0]
+    vals = np.zeros((R, T), np.float32)
+    ids = np.zeros((R, T), np.int32)
+    for slot in range(tpad):
+        t = tree_order[slot]
+        n = np.zeros(R, np.int64)
+        for _ in range(depth + 1):
+            e = h[n, slot]
+            leaf = (e[:, 1] & LEAF) != 0
+            fid = np.where(leaf, 0, (e[:, 1] & FIDMASK).astype(np.int64))
+            v = data[np.arange(R), fid]
+            c = _right(v, e[:, 0].view(np.float32), (e[:, 1] & DEFLEFT) != 0, missing)
+            c = np.where((e[:, 1] & EXCH) != 0, ~c, c)
+            n = np.where(leaf, n, 2 * n + 1 + c)
+        e = h[n, slot]
+        assert np.all(e[:, 1] & LEAF)
+        if t < 0:
+            assert np.all(e[:, 0] == 0)
+            continue
+        vals[:, t] = e[:, 0].view(np.float32)
+        ids[:, t] = oid[n, slot]
+    return vals, ids
+
+
+def quantize_rows(data, table, offsets, rank_shift, miss_code, missing):
+    """k_quantize: float rows -> rank words [R,C] (uint32)."""
+    R, Ccols = data.shape
+    out = np.zeros((R, Ccols), np.uint32)
+    with np.errstate(invalid="ignore"):
+        miss = np.abs((data - np.float32(missing)).astype(np.float32)) <= np.float32(1e-6)
+    for c in range(Ccols):
+        tab = table[offsets[c]:offsets[c + 1]]
+        v = data[:, c]
+        rank = np.searchsorted(tab, v, side="right")      # #{thr <= v}
+        rank = np.where(np.isnan(v), 0, rank)
+        out[:, c] = (rank.astype(np.uint64) << np.uint64(rank_shift)).astype(np.uint32)
+    out[miss] = np.uint32(miss_code)
+    return out
+
+
+def quant_traverse(qwords, leaf_origin, T, depth, F, col_mask, miss_code):
+    """k_smem_forest: rank words + Q4 trees.  -> (values [R,T], ids [R,T])"""
+    W, L = 1 << (depth + 1), 1 << depth
+    q = qwords.reshape(T, W)
+    lo = leaf_origin.reshape(T, L)
+    R = F.shape[0]
+    vals = np.zeros((R, T), np.float32)
+    ids = np.zeros((R, T), np.int32)
+    for t in range(T):
+        n = np.ones(R, np.int64)
+        for _ in range(depth):
+            N = q[t, n]
+            col = ((N & np.uint32(col_mask)) >> np.uint32(7)).astype(np.int64)
+            Fv = F[np.arange(R), col]
+            c = Fv > N
+            c = np.where(Fv == np.uint32(miss_code), (N & np.uint32(1)) == 0, c)
+            n = 2 * n + c
+        vals[:, t] = q[t, n].view(np.float32)
+        ids[:, t] = lo[t, n - L]
+    return vals, ids

@@ -1,0 +1,118 @@
+"""GPU parity (B200): every strategy through the C ABI against the reference goldens and
+the oracle.  Leaf ids bit-exact; raw scores bit-exact for the strategies that sum in tree
+order (all thread=sample ones), within 1e-5 relative for SHARED_DATA (lane=tree order)."""
+import numpy as np
+import pytest
+
+from tahoe_b200 import api, synth
+from tests.helpers import GOLDEN_CASES, TRANSFORMS, bits_equal, golden_preds, load_case, score_close
+
+pytestmark = pytest.mark.gpu
+ORDERED = {api.DIRECT, api.SHARED_DATA_PER_THREAD, api.SHARED_FOREST, api.SPLIT_SHARED_FOREST}
+
+
+def _run(f, data_np, strategy, want_ids=True):
+    import torch
+    d = torch.from_numpy(np.ascontiguousarray(data_np)).cuda()
+    ids = torch.full((d.shape[0], f.num_trees), -7, dtype=torch.int32, device="cuda") if want_ids else None
+    p = f.predict(d, strategy=strategy, leaf_ids=ids)
+    torch.cuda.synchronize()
+    return p.cpu().numpy(), (ids.cpu().numpy() if want_ids else None)
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_all_strategies_match_reference(oracle, name):
+    c = load_case(name)
+    f = api.Forest.from_dense(c["nodes"], c["trees"], c["depth"], c["cols"], missing=float(c["missing"]))
+    want = golden_preds(c, 0, 0.0, 0.0)
+    _, wids = oracle.predict_dense(c["nodes"], c["trees"], c["depth"], c["data"],
+                                   float(c["missing"]), want_leaf_ids=True)
+    ran = 0
+    for s in api.ALL_STRATEGIES:
+        if not f.applicable(s, c["rows"]):
+            with pytest.raises(api.NotApplicable):
+                _run(f, c["data"], s)
+            continue
+        got, ids = _run(f, c["data"], s)
+        assert np.array_equal(ids, wids), (name, api.STRATEGY_NAMES[s])
+        if s in ORDERED:
+            assert bits_equal(got, want), (name, api.STRATEGY_NAMES[s])
+        else:
+            assert score_close(got, want), (name, api.STRATEGY_NAMES[s])
+        got2, _ = _run(f, c["data"], s, want_ids=False)     # perf instantiation, same scores
+        assert bits_equal(got, got2)
+        ran += 1
+    assert ran >= 2
+    got, _ = _run(f, c["data"], api.AUTO, want_ids=False)
+    assert score_close(got, want)
+
+
+@pytest.mark.parametrize("flags,thr,bias", TRANSFORMS[1:])
+def test_output_transforms(flags, thr, bias):
+    c = load_case("char_w")
+    f = api.Forest.from_dense(c["nodes"], c["trees"], c["depth"], c["cols"], missing=float(c["missing"]),
+                              output=flags, threshold=thr, global_bias=bias)
+    want = golden_preds(c, flags, thr, bias)
+    for s in api.ALL_STRATEGIES:
+        if not f.applicable(s, c["rows"]):
+            continue
+        got, _ = _run(f, c["data"], s, want_ids=False)
+        if flags & 0x100:      # thresholded 0/1: allow flips only where the score sits on the threshold
+            raw = golden_preds(c, flags & ~0x100, thr, bias)
+            bad = got != want
+            assert np.all(np.abs(raw[bad] - thr) < 1e-5)
+        else:
+            assert score_close(got, want), (hex(flags), api.STRATEGY_NAMES[s])
+
+
+def test_sparse_forest(oracle):
+    sp, offs, w, lv = synth.gen_sparse_forest(4242, 64, 12, 50)
+    data = synth.gen_data(4343, 3000, 50, miss_frac=0.01, nan_frac=0.005)
+    want, wids = oracle.predict_sparse(sp, offs, data, -999.0, want_leaf_ids=True)
+    f = api.Forest.from_sparse(sp, offs, 50, weights=w, missing=-999.0)
+    for s in (api.DIRECT, api.SHARED_DATA_PER_THREAD):
+        got, ids = _run(f, data, s)
+        assert np.array_equal(ids, wids) and bits_equal(got, want)
+    for s in (api.SHARED_DATA, api.SHARED_FOREST, api.SPLIT_SHARED_FOREST):
+        with pytest.raises(api.NotApplicable):
+            _run(f, data, s)
+
+
+@pytest.mark.parametrize("rows", [0, 1, 31, 32, 33, 2368 * 32 + 5])
+def test_ragged_batches(oracle, rows):
+    c = load_case("char_w")
+    f = api.Forest.from_dense(c["nodes"], c["trees"], c["depth"], c["cols"], missing=float(c["missing"]))
+    data = synth.gen_data(555, rows, c["cols"], miss_frac=0.01) if rows else np.zeros((0, c["cols"]), np.float32)
+    want = oracle.predict_dense(c["nodes"], c["trees"], c["depth"], data, float(c["missing"])) if rows else np.zeros(0, np.float32)
+    for s in api.ALL_STRATEGIES:
+        if f.applicable(s, rows):
+            got, _ = _run(f, data, s, want_ids=False)
+            assert got.shape == (rows,)
+            assert (bits_equal if s in ORDERED else score_close)(got, want), (rows, s)
+
+
+def test_multi_chunk_split_and_host_path(oracle):
+    """C2-shaped forest (500 x depth 10 x 18 cols): many shared-memory chunks; device generator
+    equals the host generator; tahoe_predict_host equals tahoe_predict."""
+    import torch
+    c = load_case("susy_like")
+    f = api.Forest.from_dense(c["nodes"], c["trees"], c["depth"], c["cols"], missing=-999.0)
+    assert f.info().num_chunks > 1
+    rows = 100_003
+    d = api.gen_data_device(777, rows, 18, miss_frac=0.001)
+    host = synth.gen_data(777, rows, 18, miss_frac=0.001)
+    assert np.array_equal(d.cpu().numpy().view(np.uint32), host.view(np.uint32))
+    p = f.predict(d, strategy=api.SPLIT_SHARED_FOREST)
+    torch.cuda.synchronize()
+    assert f.launches() == 2
+    sub = np.r_[0:4096, rows - 4096:rows]
+    want = oracle.predict_dense(c["nodes"], 500, 10, host[sub], -999.0)
+    assert bits_equal(p.cpu().numpy()[sub], want)
+    p2 = f.predict(d, strategy=api.DIRECT)
+    assert bits_equal(p2.cpu().numpy(), p.cpu().numpy())        # strategy vs strategy, all rows
+    p3 = f.predict(d, strategy=api.SHARED_DATA)
+    assert score_close(p3.cpu().numpy(), p.cpu().numpy())
+    ph = f.predict_host(host, strategy=api.SPLIT_SHARED_FOREST)
+    assert bits_equal(ph, p.cpu().numpy())
+    assert bits_equal(golden_preds(c, 0, 0.0, 0.0),
+                      f.predict_host(np.ascontiguousarray(c["data"]), strategy=api.SPLIT_SHARED_FOREST))

@@ -1,0 +1,161 @@
+"""Host-side packer checks (no GPU): every packed layout, traversed by a numpy emulation of
+its kernel, must land on the oracle's leaf ids; the probability reorder must match what the
+REFERENCE's own packer produced (golden pack_* arrays)."""
+import numpy as np
+import pytest
+
+from tahoe_b200 import api, synth
+from tests import emulate
+from tests.helpers import load_case
+
+PACK_CASES = ["tiny", "char_w", "short_w", "ties", "one_feature"]
+
+
+def _forest(c, **kw):
+    return api.Forest.from_dense(c["nodes"], c["trees"], c["depth"], c["cols"],
+                                 missing=float(c["missing"]), **kw)
+
+
+def _tree_order_sum(vals):
+    acc = np.zeros(vals.shape[0], np.float32)
+    for t in range(vals.shape[1]):
+        acc = (acc + vals[:, t]).astype(np.float32)
+    return acc
+
+
+@pytest.mark.parametrize("name", PACK_CASES + ["int_w"])
+def test_heap_layout(oracle, name):
+    c = load_case(name)
+    f = _forest(c)
+    want, wids = oracle.predict_dense(c["nodes"], c["trees"], c["depth"], c["data"],
+                                      float(c["missing"]), want_leaf_ids=True)
+    heap = f.export(api.EXPORT_HEAP_NODES, np.uint32)
+    vals, ids = emulate.heap_traverse(heap, c["trees"], c["depth"], c["data"], float(c["missing"]))
+    assert np.array_equal(ids, wids)
+    assert np.array_equal(_tree_order_sum(vals).view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.parametrize("name", PACK_CASES)
+def test_interleaved_layout_with_exchange_bits(oracle, name):
+    c = load_case(name)
+    f = _forest(c)
+    want, wids = oracle.predict_dense(c["nodes"], c["trees"], c["depth"], c["data"],
+                                      float(c["missing"]), want_leaf_ids=True)
+    inter = f.export(api.EXPORT_INTERLEAVED, np.uint32)
+    oid = f.export(api.EXPORT_ORIG_IDS, np.int32)
+    order = f.export(api.EXPORT_TREE_ORDER, np.int32)
+    tpad = order.shape[0]
+    assert tpad % 32 == 0 and sorted(order[order >= 0].tolist()) == list(range(c["trees"]))
+    vals, ids = emulate.interleaved_traverse(inter, oid, order, tpad, c["depth"], c["trees"],
+                                             c["data"], float(c["missing"]))
+    assert np.array_equal(ids, wids)
+    np.testing.assert_allclose(vals.sum(1, dtype=np.float64), want.astype(np.float64), rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("name", ["tiny", "char_w", "short_w", "ties"])
+def test_probability_reorder_matches_reference_packer(name):
+    """Our swapped trees, tree by tree, equal the reference packer's (Struct.h:1775-1825)."""
+    c = load_case(name)
+    if "pack_values" not in c:
+        pytest.skip("no reference pack in this golden")
+    f = _forest(c)
+    T, d = c["trees"], c["depth"]
+    N = (1 << (d + 1)) - 1
+    bl = int(c["pack_bits_length"])
+    assert bl == f.info().node_width_bytes
+    fid_bits = {1: 5, 2: 13, 4: 29}[bl]
+    inter = f.export(api.EXPORT_INTERLEAVED, np.uint32).reshape(N, -1, 2)
+    order = f.export(api.EXPORT_TREE_ORDER, np.int32)
+    ours = {}
+    for slot, t in enumerate(order):
+        if t < 0:
+            continue
+        meta = inter[:, slot, 1]
+        ref_style = ((meta & emulate.FIDMASK) & ((1 << fid_bits) - 1)) \
+            | np.where(meta & emulate.DEFLEFT, 1 << fid_bits, 0) \
+            | np.where(meta & emulate.LEAF, 1 << (fid_bits + 1), 0) \
+            | np.where(meta & emulate.EXCH, 1 << (fid_bits + 2), 0)
+        ours[inter[:, slot, 0].tobytes() + ref_style.astype(np.uint32).tobytes()] = t
+    rv = c["pack_values"].reshape(T, N)
+    rb = c["pack_bits"].reshape(T, N).astype(np.uint32)
+    seen = set()
+    for i in range(T):   # reference tree order is undefined: match as a set
+        key = rv[i].view(np.uint32).tobytes() + rb[i].tobytes()
+        assert key in ours, f"reference packed tree {i} has no equal in our pack"
+        seen.add(ours[key])
+    assert len(seen) == len(ours)
+
+
+def test_wide_forest_has_no_quantized_layout():
+    f = _forest(load_case("short_w"))       # 300 columns > 64: one warp tile would not fit
+    assert f.info().quantized == 0 and not f.applicable(api.SPLIT_SHARED_FOREST, 100)
+
+
+@pytest.mark.parametrize("name", ["tiny", "char_w", "ties", "one_feature"])
+def test_quantized_layout(oracle, name):
+    c = load_case(name)
+    f = _forest(c)
+    inf = f.info()
+    assert inf.quantized == 1 and inf.rank_bits + inf.col_bits + 7 <= 32
+    want, wids = oracle.predict_dense(c["nodes"], c["trees"], c["depth"], c["data"],
+                                      float(c["missing"]), want_leaf_ids=True)
+    table = f.export(api.EXPORT_QUANT_TABLE, np.float32)
+    offs = f.export(api.EXPORT_QUANT_OFFSETS, np.int32)
+    for col in range(c["cols"]):
+        seg = table[offs[col]:offs[col + 1]]
+        assert np.all(seg[1:] > seg[:-1])
+    shift = 32 - inf.rank_bits
+    miss_code = ((1 << inf.rank_bits) - 1) << shift
+    col_mask = ((1 << inf.col_bits) - 1) << 7
+    F = emulate.quantize_rows(c["data"], table, offs, shift, miss_code, float(c["missing"]))
+    vals, ids = emulate.quant_traverse(f.export(api.EXPORT_QUANT_WORDS, np.uint32),
+                                       f.export(api.EXPORT_LEAF_ORIGIN, np.int32),
+                                       c["trees"], c["depth"], F, col_mask, miss_code)
+    assert np.array_equal(ids, wids)
+    assert np.array_equal(_tree_order_sum(vals).view(np.uint32), want.view(np.uint32))
+
+
+def test_info_and_chunk_plan():
+    c = load_case("susy_like")
+    f = _forest(c)
+    inf = f.info()
+    assert (inf.num_trees, inf.depth, inf.num_cols, inf.is_sparse) == (500, 10, 18, 0)
+    assert inf.node_width_bytes == 1 and inf.quantized == 1
+    assert inf.num_nodes == 500 * 2047 and abs(inf.mean_depth - 10.0) < 1e-9
+    assert inf.trees_per_chunk * inf.num_chunks >= 500 and inf.trees_per_chunk * 8192 < 227 * 1024
+    assert not f.applicable(api.SHARED_FOREST, 1000) and f.applicable(api.SPLIT_SHARED_FOREST, 1000)
+    assert inf.bytes_quantized == 500 * 2048 * 4
+
+
+def test_invalid_forests_are_statuses_not_aborts():
+    nodes = synth.gen_dense_forest(1, 2, 2, 4)
+    with pytest.raises(api.TahoeError):       # fid >= num_cols
+        api.Forest.from_dense(nodes, 2, 2, 2)
+    bad = nodes.copy()
+    bad["bits"] &= 0x7FFFFFFF                  # no leaves at all -> internal node on the bottom level
+    with pytest.raises(api.TahoeError):
+        api.Forest.from_dense(bad, 2, 2, 4)
+
+
+def test_sparse_pack_validation():
+    nodes = synth.gen_dense_forest(3, 4, 3, 6, leaf_prob=0.3)
+    sp, offs, w, ids = synth.dense_to_sparse(nodes, 4, 3)
+    f = api.Forest.from_sparse(sp, offs, 6, weights=w, missing=-999.0)
+    inf = f.info()
+    assert inf.is_sparse == 1 and inf.num_nodes == sp.shape[0] and inf.quantized == 0
+    assert not f.applicable(api.SPLIT_SHARED_FOREST, 10) and f.applicable(api.DIRECT, 10)
+    bad = sp.copy()
+    bad["left_idx"][0] = 0
+    with pytest.raises(api.TahoeError):
+        api.Forest.from_sparse(bad, offs, 6)
+
+
+def test_predict_without_gpu_fails_loudly():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    c = load_case("tiny")
+    f = _forest(c)
+    out = np.zeros(c["rows"], np.float32)
+    with pytest.raises(api.TahoeError):
+        f.predict_host(np.ascontiguousarray(c["data"]), out, strategy=api.DIRECT)
