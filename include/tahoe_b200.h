@@ -137,6 +137,14 @@ int tahoe_select_strategy(const tahoe_forest_t* f, size_t num_rows, double* pred
 /* Number of kernel launches the last tahoe_predict on this handle issued. */
 int tahoe_last_launch_count(const tahoe_forest_t* f);
 
+/* Per-kernel timing for the roofline report.  While on, every tahoe_predict on the
+ * shared-memory-forest strategies records CUDA events on the launch stream around its two
+ * kernels (the reference times whole predict calls with gettimeofday, BaseTahoeTest.h:687-698).
+ * tahoe_profile_read synchronises on them and returns the summed milliseconds and the number
+ * of predicts covered since profiling was switched on. */
+int tahoe_set_profiling(tahoe_forest_t* f, int on);
+int tahoe_profile_read(tahoe_forest_t* f, double* quantize_ms, double* traverse_ms, int* count);
+
 /* ---- text loaders (host only) -------------------------------------------------------
  * generate_forest_from_file, BaseTahoeTest.h:267-352 / generate_data_from_file,
  * :354-402 (parse only; the caller uploads).  Buffers are released with

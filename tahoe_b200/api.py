@@ -77,6 +77,8 @@ def lib() -> C.CDLL:
     L.tahoe_strategy_applicable.argtypes = [vp, C.c_int, sz]
     L.tahoe_select_strategy.argtypes = [vp, sz, C.POINTER(C.c_double)]
     L.tahoe_last_launch_count.argtypes = [vp]
+    L.tahoe_set_profiling.argtypes = [vp, C.c_int]
+    L.tahoe_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int)]
     L.tahoe_load_model_text.argtypes = [C.c_char_p, C.POINTER(vp), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.tahoe_load_data_text.argtypes = [C.c_char_p, C.POINTER(vp), C.POINTER(C.c_int),
                                        C.POINTER(C.c_int), C.POINTER(C.c_float)]
@@ -197,6 +199,15 @@ class Forest:
         pp = preds.ctypes.data if isinstance(preds, np.ndarray) else preds.data_ptr()
         _check(lib().tahoe_predict_host(self._h, strategy, C.c_void_p(dp), rows, C.c_void_p(pp)))
         return preds
+
+    def set_profiling(self, on: bool):
+        _check(lib().tahoe_set_profiling(self._h, int(on)))
+
+    def profile_read(self):
+        """-> (quantize_ms_sum, traverse_ms_sum, predicts_covered)"""
+        q, t, n = C.c_double(), C.c_double(), C.c_int()
+        _check(lib().tahoe_profile_read(self._h, C.byref(q), C.byref(t), C.byref(n)))
+        return q.value, t.value, n.value
 
     def launches(self) -> int:
         return lib().tahoe_last_launch_count(self._h)

@@ -164,6 +164,7 @@ void tahoe_forest_destroy(tahoe_forest_t* f) {
   cudaFree(f->d_tree_order); cudaFree(f->d_orig_ids); cudaFree(f->d_qwords); cudaFree(f->d_qtable);
   cudaFree(f->d_qoffsets); cudaFree(f->d_leaf_origin);
   for (auto& w : f->ws) free_workspace(w);
+  for (auto& e : f->prof_events) cudaEventDestroy(e);
   cudaGetLastError();
   delete f;
 }
@@ -236,6 +237,32 @@ int tahoe_strategy_applicable(const tahoe_forest_t* f, int strategy, size_t num_
 int tahoe_select_strategy(const tahoe_forest_t* f, size_t num_rows, double* predicted_seconds) {
   if (!f) { set_error("null argument"); return TAHOE_STRATEGY_DIRECT; }
   return select_strategy(f, num_rows, predicted_seconds);
+}
+
+int tahoe_set_profiling(tahoe_forest_t* f, int on) {
+  if (!f) { set_error("null argument"); return TAHOE_ERR_INVALID; }
+  if (on && f->prof_events.empty()) {
+    f->prof_events.resize((size_t)kProfRing * 3);
+    for (auto& e : f->prof_events) TAHOE_CUDA(cudaEventCreate(&e));
+  }
+  f->profile = on != 0;
+  f->prof_count = 0;
+  return TAHOE_OK;
+}
+
+int tahoe_profile_read(tahoe_forest_t* f, double* quantize_ms, double* traverse_ms, int* count) {
+  if (!f || !quantize_ms || !traverse_ms || !count) { set_error("null argument"); return TAHOE_ERR_INVALID; }
+  double q = 0.0, t = 0.0;
+  for (int i = 0; i < f->prof_count; ++i) {
+    cudaEvent_t* ev = &f->prof_events[(size_t)i * 3];
+    TAHOE_CUDA(cudaEventSynchronize(ev[2]));
+    float a = 0.f, b = 0.f;
+    TAHOE_CUDA(cudaEventElapsedTime(&a, ev[0], ev[1]));
+    TAHOE_CUDA(cudaEventElapsedTime(&b, ev[1], ev[2]));
+    q += a; t += b;
+  }
+  *quantize_ms = q; *traverse_ms = t; *count = f->prof_count;
+  return TAHOE_OK;
 }
 
 int tahoe_last_launch_count(const tahoe_forest_t* f) { return f ? f->last_launches : 0; }

@@ -62,6 +62,7 @@ struct Workspace {                     // per-stream scratch, grow-only (no per-
 };
 
 constexpr int kHostSlots = 3;
+constexpr int kProfRing = 512;         // per-kernel CUDA-event triples kept while profiling is on
 
 }  // namespace tahoe
 
@@ -98,6 +99,11 @@ struct tahoe_forest {
   int device = 0, sm_count = 0, smem_optin = 0, l2_bytes = 0;
   tahoe::Workspace ws[1 + tahoe::kHostSlots];  // [0] = tahoe_predict, [1..] = predict_host slabs
   int last_launches = 0;
+
+  // optional per-kernel timing (tahoe_set_profiling): events recorded on the launch stream
+  bool profile = false;
+  int prof_count = 0;
+  std::vector<cudaEvent_t> prof_events;  // 3 per entry: before quantise, between, after traverse
 };
 
 namespace tahoe {

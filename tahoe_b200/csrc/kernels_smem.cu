@@ -277,7 +277,14 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   const size_t qwarps_per_block = 256 / 32;
   unsigned qgrid = (unsigned)std::min<size_t>((tiles + qwarps_per_block - 1) / qwarps_per_block,
                                               (size_t)f->sm_count * 16);
+  cudaEvent_t* ev = nullptr;
+  if (f->profile && a.ws == &f->ws[0] && f->prof_count < kProfRing) {
+    ev = &f->prof_events[(size_t)f->prof_count * 3];
+    ++f->prof_count;
+    TAHOE_CUDA(cudaEventRecord(ev[0], a.stream));
+  }
   k_quantize<<<qgrid, 256, (q.cols + 1) * sizeof(int32_t), a.stream>>>(q);
+  if (ev) TAHOE_CUDA(cudaEventRecord(ev[1], a.stream));
   TAHOE_CUDA(cudaGetLastError());
   ++*launches;
 
@@ -301,6 +308,7 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
     default: set_error("unsupported depth"); return TAHOE_ERR_NOT_APPLICABLE;
   }
   if (rc) return rc;
+  if (ev) TAHOE_CUDA(cudaEventRecord(ev[2], a.stream));
   ++*launches;
   return TAHOE_OK;
 }

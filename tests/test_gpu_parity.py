@@ -48,7 +48,7 @@ def test_all_strategies_match_reference(oracle, name):
 
 
 @pytest.mark.parametrize("flags,thr,bias", TRANSFORMS[1:])
-def test_output_transforms(flags, thr, bias):
+def test_output_transforms(oracle, flags, thr, bias):
     c = load_case("char_w")
     f = api.Forest.from_dense(c["nodes"], c["trees"], c["depth"], c["cols"], missing=float(c["missing"]),
                               output=flags, threshold=thr, global_bias=bias)
