@@ -91,6 +91,7 @@ typedef struct {
   int device;
   int sm_count;
   int smem_optin_bytes;
+  int col_shift;              /* bit position of the column field in a quantised node word (7 or 12) */
 } tahoe_forest_info_t;
 
 /* ---- forest lifetime -------------------------------------------------------------
@@ -171,7 +172,10 @@ enum {
   TAHOE_EXPORT_QUANT_TABLE = 5,   /* float [sum n_col] sorted distinct thresholds per column */
   TAHOE_EXPORT_QUANT_OFFSETS = 6, /* int32 [num_cols+1] offsets into the table */
   TAHOE_EXPORT_LEAF_ORIGIN = 7,   /* int32 [T][2^depth] padded bottom slot -> original leaf heap id */
-  TAHOE_EXPORT_SIMHASH = 8        /* uint64 [T] simhash per original tree */
+  TAHOE_EXPORT_SIMHASH = 8,       /* uint64 [T] simhash per original tree */
+  TAHOE_EXPORT_QUANT_LUT = 9,     /* int32 [C][B+1] bucket index: thresholds of the column in lower buckets */
+  TAHOE_EXPORT_QUANT_LUT_MIN = 10,  /* float [C] */
+  TAHOE_EXPORT_QUANT_LUT_SCALE = 11 /* float [C] */
 };
 int tahoe_forest_export(const tahoe_forest_t* f, int which, void* buf, size_t* bytes);
 

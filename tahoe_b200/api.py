@@ -14,7 +14,7 @@ import numpy as np
 from .synth import DENSE_NODE, SPARSE_NODE
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libtahoe_b200.so")
+LIB_PATH = os.environ.get("TAHOE_B200_LIB") or os.path.join(HERE, "lib", "libtahoe_b200.so")
 
 OK, ERR_INVALID, ERR_CUDA, ERR_NOT_APPLICABLE, ERR_IO, ERR_NOMEM = range(6)
 AUTO, DIRECT, SHARED_DATA_PER_THREAD, SHARED_DATA, SHARED_FOREST, SPLIT_SHARED_FOREST = -1, 0, 1, 2, 3, 4
@@ -24,7 +24,8 @@ STRATEGY_NAMES = {DIRECT: "direct", SHARED_DATA_PER_THREAD: "shared_data_per_thr
 ALL_STRATEGIES = list(STRATEGY_NAMES)
 
 (EXPORT_HEAP_NODES, EXPORT_INTERLEAVED, EXPORT_TREE_ORDER, EXPORT_ORIG_IDS, EXPORT_QUANT_WORDS,
- EXPORT_QUANT_TABLE, EXPORT_QUANT_OFFSETS, EXPORT_LEAF_ORIGIN, EXPORT_SIMHASH) = range(9)
+ EXPORT_QUANT_TABLE, EXPORT_QUANT_OFFSETS, EXPORT_LEAF_ORIGIN, EXPORT_SIMHASH, EXPORT_QUANT_LUT,
+ EXPORT_QUANT_LUT_MIN, EXPORT_QUANT_LUT_SCALE) = range(12)
 
 
 class TahoeError(RuntimeError):
@@ -51,7 +52,7 @@ class ForestInfo(C.Structure):
                 ("trees_per_chunk", C.c_int), ("num_chunks", C.c_int), ("bytes_heap", C.c_int64),
                 ("bytes_interleaved", C.c_int64), ("bytes_quantized", C.c_int64),
                 ("exchanged_nodes", C.c_int64), ("mean_depth", C.c_double), ("device", C.c_int),
-                ("sm_count", C.c_int), ("smem_optin_bytes", C.c_int)]
+                ("sm_count", C.c_int), ("smem_optin_bytes", C.c_int), ("col_shift", C.c_int)]
 
 
 _lib = None

@@ -163,6 +163,7 @@ void tahoe_forest_destroy(tahoe_forest_t* f) {
   cudaFree(f->d_heap); cudaFree(f->d_sparse); cudaFree(f->d_tree_offsets); cudaFree(f->d_inter);
   cudaFree(f->d_tree_order); cudaFree(f->d_orig_ids); cudaFree(f->d_qwords); cudaFree(f->d_qtable);
   cudaFree(f->d_qoffsets); cudaFree(f->d_leaf_origin);
+  cudaFree(f->d_qlut_min); cudaFree(f->d_qlut_scale); cudaFree(f->d_qlut);
   for (auto& w : f->ws) free_workspace(w);
   for (auto& e : f->prof_events) cudaEventDestroy(e);
   cudaGetLastError();
@@ -180,7 +181,7 @@ int tahoe_forest_info(const tahoe_forest_t* f, tahoe_forest_info_t* info) {
   info->bytes_interleaved = (int64_t)(f->host.inter.size() * sizeof(uint2));
   info->bytes_quantized = (int64_t)(f->host.qwords.size() * sizeof(uint32_t));
   info->exchanged_nodes = f->exchanged; info->mean_depth = f->mean_depth; info->device = f->device;
-  info->sm_count = f->sm_count; info->smem_optin_bytes = f->smem_optin;
+  info->sm_count = f->sm_count; info->smem_optin_bytes = f->smem_optin; info->col_shift = f->col_shift;
   return TAHOE_OK;
 }
 
@@ -282,6 +283,9 @@ int tahoe_forest_export(const tahoe_forest_t* f, int which, void* buf, size_t* b
     case TAHOE_EXPORT_QUANT_OFFSETS: src = h.qoffsets.data(); n = h.qoffsets.size() * 4; break;
     case TAHOE_EXPORT_LEAF_ORIGIN: src = h.leaf_origin.data(); n = h.leaf_origin.size() * 4; break;
     case TAHOE_EXPORT_SIMHASH: src = h.simhash.data(); n = h.simhash.size() * 8; break;
+    case TAHOE_EXPORT_QUANT_LUT: src = h.qlut.data(); n = h.qlut.size() * 4; break;
+    case TAHOE_EXPORT_QUANT_LUT_MIN: src = h.qlut_min.data(); n = h.qlut_min.size() * 4; break;
+    case TAHOE_EXPORT_QUANT_LUT_SCALE: src = h.qlut_scale.data(); n = h.qlut_scale.size() * 4; break;
     default: set_error("unknown export id"); return TAHOE_ERR_INVALID;
   }
   if (buf) {

@@ -27,7 +27,9 @@ constexpr uint32_t kMetaExchange = 1u << 29;     // I8 only (reference EXCHANGE_
 constexpr uint32_t kMetaDefLeft = 1u << 30;      // same bit as the reference's DEF_LEFT_MASK, Struct.h:58
 constexpr uint32_t kMetaLeaf = 1u << 31;         // same bit as IS_LEAF_MASK, Struct.h:59
 
-constexpr int kQuantColShift = 7;                // Q4 word: column byte offset (col * 128) in bits 7..
+constexpr int kQuantColShift = 7;                // Q4 word, compact form: column index in bits 7..
+constexpr int kQuantColShiftWide = 12;           // Q4 word, wide form: column * 4096 = its byte offset in the
+                                                 // tile region (32 interleaved warp buffers of 128 B per column)
 constexpr int kQuantMaxDepth = 14;               // 2^(d+1) words per tree must fit shared memory
 constexpr int kQuantMaxCols = 64;                // one warp tile = cols * 128 B of shared memory
 constexpr int kSmemWarps = 16;                   // warps per CTA of the shared-memory-forest kernel
@@ -49,6 +51,11 @@ struct HostPack {
   std::vector<float> qtable;          // sorted distinct thresholds, all columns back to back
   std::vector<int32_t> qoffsets;      // [C+1]
   std::vector<int32_t> leaf_origin;   // [T][2^d]
+  // bucket index over each column's threshold range: rank(v) is searched only inside v's bucket
+  int qbuckets = 0;                   // B (power of two)
+  std::vector<float> qlut_min;        // [C] smallest threshold of the column
+  std::vector<float> qlut_scale;      // [C] B / (max - min)  (0 when the range is empty or infinite)
+  std::vector<int32_t> qlut;          // [C][B+1] thresholds of the column whose bucket is < b
 };
 
 struct Workspace {                     // per-stream scratch, grow-only (no per-call malloc)
@@ -77,7 +84,7 @@ struct tahoe_forest {
 
   // quantised layout parameters
   bool quant = false;
-  int rank_bits = 0, col_bits = 0, rank_shift = 0;
+  int rank_bits = 0, col_bits = 0, rank_shift = 0, col_shift = 0;
   uint32_t col_mask = 0, miss_code = 0;
   int trees_per_chunk = 0, num_chunks = 0;
   size_t smem_bytes = 0;
@@ -95,6 +102,9 @@ struct tahoe_forest {
   float* d_qtable = nullptr;
   int32_t* d_qoffsets = nullptr;
   int32_t* d_leaf_origin = nullptr;
+  float* d_qlut_min = nullptr;
+  float* d_qlut_scale = nullptr;
+  int32_t* d_qlut = nullptr;
 
   int device = 0, sm_count = 0, smem_optin = 0, l2_bytes = 0;
   tahoe::Workspace ws[1 + tahoe::kHostSlots];  // [0] = tahoe_predict, [1..] = predict_host slabs

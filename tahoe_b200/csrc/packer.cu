@@ -223,10 +223,45 @@ static int build_quant(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
   h.qtable.clear();
   h.qtable.reserve(h.qoffsets[C]);
   for (int c = 0; c < C; ++c) h.qtable.insert(h.qtable.end(), thr[c].begin(), thr[c].end());
+  // bucket LUT (k_quantize): bucket(x) = clamp(int((x - min) * scale), 0, B-1) is monotone in x, so
+  // thresholds in lower buckets are < v and thresholds in higher buckets are > v; only v's own
+  // bucket needs a search.  Host and device evaluate bucket() with the same IEEE float ops.
+  {
+    int B = 1024;
+    while (B > 16 && (size_t)C * (B + 1) * 4 > 96 * 1024) B >>= 1;
+    h.qbuckets = B;
+    h.qlut_min.assign(C, 0.0f);
+    h.qlut_scale.assign(C, 0.0f);
+    h.qlut.assign((size_t)C * (B + 1), 0);
+    for (int c = 0; c < C; ++c) {
+      const std::vector<float>& tv = thr[c];
+      int32_t* lut = h.qlut.data() + (size_t)c * (B + 1);
+      if (tv.empty()) continue;
+      const float mn = tv.front(), range = tv.back() - tv.front();
+      float scale = 0.0f;
+      if (range > 0.0f && std::isfinite(range)) {
+        scale = (float)B / range;
+        if (!std::isfinite(scale)) scale = 0.0f;
+      }
+      h.qlut_min[c] = mn;
+      h.qlut_scale[c] = scale;
+      for (float t : tv) {
+        const float x = (t - mn) * scale;
+        int b = x >= (float)B ? B - 1 : (int)x;   // tv is sorted, so x >= 0
+        if (b < 0) b = 0;
+        if (b > B - 1) b = B - 1;
+        lut[b + 1] += 1;
+      }
+      for (int b = 0; b < B; ++b) lut[b + 1] += lut[b];
+    }
+  }
   f->rank_bits = rb;
   f->col_bits = cb;
   f->rank_shift = 32 - rb;
-  f->col_mask = ((1u << cb) - 1u) << kQuantColShift;
+  // wide form when it fits: the column field is then already the byte offset of the column
+  // row in the shared-memory tile region, saving one instruction per node visit
+  f->col_shift = (rb + cb + kQuantColShiftWide <= 32) ? kQuantColShiftWide : kQuantColShift;
+  f->col_mask = ((1u << cb) - 1u) << f->col_shift;
   f->miss_code = ((1u << rb) - 1u) << f->rank_shift;
 
   h.qwords.assign((size_t)T * W, 0u);
@@ -245,7 +280,7 @@ static int build_quant(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
           uint32_t k;
           if (std::isnan(v)) k = (uint32_t)thr[fid].size();  // val >= NaN is never true
           else k = (uint32_t)(std::lower_bound(thr[fid].begin(), thr[fid].end(), v) - thr[fid].begin());
-          out[i] = (k << f->rank_shift) | ((uint32_t)fid << kQuantColShift) |
+          out[i] = (k << f->rank_shift) | ((uint32_t)fid << f->col_shift) |
                    ((tr[i - 1].bits & 0x40000000) ? 1u : 0u);
           for (int c = 0; c < 2; ++c) origin[2 * i + c] = (tr[2 * i + c - 1].bits < 0) ? (int32_t)(2 * i + c) : 0;
         } else {
@@ -372,6 +407,9 @@ int upload(tahoe_forest* f) {
   if ((rc = to_device(&f->d_qtable, h.qtable))) return rc;
   if ((rc = to_device(&f->d_qoffsets, h.qoffsets))) return rc;
   if ((rc = to_device(&f->d_leaf_origin, h.leaf_origin))) return rc;
+  if ((rc = to_device(&f->d_qlut_min, h.qlut_min))) return rc;
+  if ((rc = to_device(&f->d_qlut_scale, h.qlut_scale))) return rc;
+  if ((rc = to_device(&f->d_qlut, h.qlut))) return rc;
   return TAHOE_OK;
 }
 

@@ -80,7 +80,31 @@ def quantize_rows(data, table, offsets, rank_shift, miss_code, missing):
     return out
 
 
-def quant_traverse(qwords, leaf_origin, T, depth, F, col_mask, miss_code):
+def quantize_rows_lut(data, table, offsets, lut, lut_min, lut_scale, rank_shift, miss_code, missing):
+    """k_quantize exactly as the device does it: bucket LUT + search inside the bucket."""
+    R, Ccols = data.shape
+    B = lut.shape[0] // Ccols - 1
+    lut = lut.reshape(Ccols, B + 1)
+    out = np.zeros((R, Ccols), np.uint32)
+    with np.errstate(invalid="ignore", over="ignore"):
+        miss = np.abs((data - np.float32(missing)).astype(np.float32)) <= np.float32(1e-6)
+        for c in range(Ccols):
+            tab = table[offsets[c]:offsets[c + 1]]
+            v = data[:, c]
+            x = ((v - lut_min[c]).astype(np.float32) * lut_scale[c]).astype(np.float32)
+            b = np.where(x >= np.float32(B), B - 1, np.trunc(np.nan_to_num(x, nan=0.0, posinf=B, neginf=-1)).astype(np.int64))
+            b = np.clip(b, 0, B - 1)
+            lo, hi = lut[c, b], lut[c, b + 1]
+            rank = np.zeros(R, np.int64)
+            for i in range(R):
+                if v[i] == v[i]:
+                    rank[i] = lo[i] + np.searchsorted(tab[lo[i]:hi[i]], v[i], side="right")
+            out[:, c] = (rank.astype(np.uint64) << np.uint64(rank_shift)).astype(np.uint32)
+    out[miss] = np.uint32(miss_code)
+    return out
+
+
+def quant_traverse(qwords, leaf_origin, T, depth, F, col_mask, miss_code, col_shift=7):
     """k_smem_forest: rank words + Q4 trees.  -> (values [R,T], ids [R,T])"""
     W, L = 1 << (depth + 1), 1 << depth
     q = qwords.reshape(T, W)
@@ -92,7 +116,7 @@ def quant_traverse(qwords, leaf_origin, T, depth, F, col_mask, miss_code):
         n = np.ones(R, np.int64)
         for _ in range(depth):
             N = q[t, n]
-            col = ((N & np.uint32(col_mask)) >> np.uint32(7)).astype(np.int64)
+            col = ((N & np.uint32(col_mask)) >> np.uint32(col_shift)).astype(np.int64)
             Fv = F[np.arange(R), col]
             c = Fv > N
             c = np.where(Fv == np.uint32(miss_code), (N & np.uint32(1)) == 0, c)

@@ -106,11 +106,17 @@ def test_quantized_layout(oracle, name):
         assert np.all(seg[1:] > seg[:-1])
     shift = 32 - inf.rank_bits
     miss_code = ((1 << inf.rank_bits) - 1) << shift
-    col_mask = ((1 << inf.col_bits) - 1) << 7
+    assert inf.col_shift in (7, 12) and inf.rank_bits + inf.col_bits + inf.col_shift <= 32
+    col_mask = ((1 << inf.col_bits) - 1) << inf.col_shift
     F = emulate.quantize_rows(c["data"], table, offs, shift, miss_code, float(c["missing"]))
+    F2 = emulate.quantize_rows_lut(c["data"], table, offs, f.export(api.EXPORT_QUANT_LUT, np.int32),
+                                   f.export(api.EXPORT_QUANT_LUT_MIN, np.float32),
+                                   f.export(api.EXPORT_QUANT_LUT_SCALE, np.float32), shift, miss_code,
+                                   float(c["missing"]))
+    assert np.array_equal(F, F2)          # the bucket index never changes a rank
     vals, ids = emulate.quant_traverse(f.export(api.EXPORT_QUANT_WORDS, np.uint32),
                                        f.export(api.EXPORT_LEAF_ORIGIN, np.int32),
-                                       c["trees"], c["depth"], F, col_mask, miss_code)
+                                       c["trees"], c["depth"], F, col_mask, miss_code, inf.col_shift)
     assert np.array_equal(ids, wids)
     assert np.array_equal(_tree_order_sum(vals).view(np.uint32), want.view(np.uint32))
 
