@@ -171,6 +171,7 @@ def main():
     ap.add_argument("--strategy", type=int, default=-1, help="force a strategy id (default: model picks)")
     ap.add_argument("--rows", type=int, default=0, help="override rows per GPU (debug only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs only)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -244,24 +245,28 @@ def main():
     value = world * rows / (ms_step * 1e-3)
 
     # ---- end to end: pinned host rows in, host scores out, every step
-    h_data = torch.empty((rows, cfg["cols"]), dtype=torch.float32, pin_memory=True)
-    h_data.copy_(data)
-    h_preds = torch.empty(rows, dtype=torch.float32, pin_memory=True)
-    e2e_steps = max(3, min(args.steps, 10))
-    for _ in range(2):
-        forest.predict_host(h_data, h_preds, strategy=strategy)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        forest.predict_host(h_data, h_preds, strategy=strategy)
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    if distributed:
-        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    e2e_value = world * rows * e2e_steps / e2e_s
-    same = bool(torch.equal(h_preds.cuda(), preds))
+    e2e = None
+    if not args.no_e2e:
+        h_data = torch.empty((rows, cfg["cols"]), dtype=torch.float32, pin_memory=True)
+        h_data.copy_(data)
+        h_preds = torch.empty(rows, dtype=torch.float32, pin_memory=True)
+        e2e_steps = max(3, min(args.steps, 10))
+        for _ in range(2):
+            forest.predict_host(h_data, h_preds, strategy=strategy)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            forest.predict_host(h_data, h_preds, strategy=strategy)
+        torch.cuda.synchronize()
+        e2e_s = time.perf_counter() - t0
+        if distributed:
+            t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_s = float(t.item())
+        same = bool(torch.equal(h_preds.cuda(), preds))
+        e2e = {"value": world * rows * e2e_steps / e2e_s, "unit": "samples/s",
+               "h2d_bytes_per_step": rows * cfg["cols"] * 4, "d2h_bytes_per_step": rows * 4,
+               "steps": e2e_steps, "matches_device_path": same}
 
     if rank == 0:
         peak, peak_src = _peaks()
@@ -284,9 +289,7 @@ def main():
                          "kernel_ms": trav_ms, "quantize_ms": (q_ms / n_prof if n_prof else None),
                          "algorithmic_bytes_per_launch": abytes, "peak_source": peak_src,
                          "note": "node bytes are served from shared memory, so achieved may exceed the HBM peak"},
-            "e2e": {"value": e2e_value, "unit": "samples/s",
-                    "h2d_bytes_per_step": rows * cfg["cols"] * 4, "d2h_bytes_per_step": rows * 4,
-                    "steps": e2e_steps, "matches_device_path": same},
+            "e2e": e2e,
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks,
         }

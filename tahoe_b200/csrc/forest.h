@@ -27,13 +27,31 @@ constexpr uint32_t kMetaExchange = 1u << 29;     // I8 only (reference EXCHANGE_
 constexpr uint32_t kMetaDefLeft = 1u << 30;      // same bit as the reference's DEF_LEFT_MASK, Struct.h:58
 constexpr uint32_t kMetaLeaf = 1u << 31;         // same bit as IS_LEAF_MASK, Struct.h:59
 
+// Tunables of the shared-memory-forest kernel (variant builds override them with -D, see
+// tools/build_variant.sh; every translation unit must see the same values).
+#ifndef TAHOE_WARPS
+#define TAHOE_WARPS 16
+#endif
+#ifndef TAHOE_BUFS
+#define TAHOE_BUFS 2
+#endif
+#ifndef TAHOE_GROUP
+#define TAHOE_GROUP 6
+#endif
+constexpr int kSmemWarps = TAHOE_WARPS;          // warps per CTA of the shared-memory-forest kernel
+constexpr int kSmemTileBufs = TAHOE_BUFS;        // sample-tile buffers per warp
+constexpr int kSlots = kSmemWarps * kSmemTileBufs;  // tile buffers per CTA (a power of two)
+constexpr int kGroup = TAHOE_GROUP;              // trees traversed together by one thread (ILP)
+static_assert((kSlots & (kSlots - 1)) == 0 && kSlots >= 1 && kSlots <= 64, "tile slots must be a power of two");
+constexpr int ilog2_c(int v) { return v <= 1 ? 0 : 1 + ilog2_c(v >> 1); }
+
 constexpr int kQuantColShift = 7;                // Q4 word, compact form: column index in bits 7..
-constexpr int kQuantColShiftWide = 12;           // Q4 word, wide form: column * 4096 = its byte offset in the
-                                                 // tile region (32 interleaved warp buffers of 128 B per column)
+constexpr int kQuantColShiftWide = 7 + ilog2_c(kSlots);  // Q4 word, wide form: column * (128 * kSlots) = its
+                                                 // byte offset in the tile region (all kSlots warp buffers of a
+                                                 // column interleaved, 128 B each)
 constexpr int kQuantMaxDepth = 14;               // 2^(d+1) words per tree must fit shared memory
 constexpr int kQuantMaxCols = 64;                // one warp tile = cols * 128 B of shared memory
-constexpr int kSmemWarps = 16;                   // warps per CTA of the shared-memory-forest kernel
-constexpr int kSmemTileBufs = 2;                 // double-buffered sample tiles per warp
+constexpr int kQuantMaxBuckets = 8192;           // bucket index of one column: (B+1) ints of shared memory
 
 struct HostPack {
   // H8 / S16
@@ -87,7 +105,11 @@ struct tahoe_forest {
   int rank_bits = 0, col_bits = 0, rank_shift = 0, col_shift = 0;
   uint32_t col_mask = 0, miss_code = 0;
   int trees_per_chunk = 0, num_chunks = 0;
+  int group = 1;                 // trees per traversal group (1, 2, 4 or kGroup); qwords_trees is a multiple
+  int qwords_trees = 0;          // trees in d_qwords: num_trees padded with all-zero trees (leaf value +0.0f)
   size_t smem_bytes = 0;
+  int quant_stride = 1;          // k_quantize keeps every quant_stride-th threshold of a column in shared memory
+  size_t quant_smem = 0;
 
   tahoe::HostPack host;
 

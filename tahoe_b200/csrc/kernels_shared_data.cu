@@ -48,7 +48,7 @@ __global__ void k_shared_data(SharedDataParams p) {
       for (int i = lane; i < p.cols; i += 32) my[i] = __ldg(g + i);
     }
     __syncwarp();
-    float acc = 0.0f;
+    double acc = 0.0;   // lane = tree changes the summation order; double keeps the result within half an ulp of exact
     for (int slot = lane; slot < p.tpad; slot += 32) {
       uint32_t n = 0;
       uint2 e = __ldg(p.inter + slot);
@@ -59,14 +59,15 @@ __global__ void k_shared_data(SharedDataParams p) {
         n = 2 * n + 1 + (c ? 1u : 0u);
         e = __ldg(p.inter + (size_t)n * p.tpad + slot);
       }
-      acc += __uint_as_float(e.x);            // padding slots are leaves holding 0.0f
+      acc += (double)__uint_as_float(e.x);    // padding slots are leaves holding 0.0f
       if (p.leaf_ids) {
         const int t = p.tree_order[slot];
         if (t >= 0) p.leaf_ids[row * (size_t)p.num_trees + t] = p.orig_ids[(size_t)n * p.tpad + slot];
       }
     }
-    acc = warp_sum(acc);
-    if (lane == 0) p.preds[row] = apply_transform(acc, p.tf);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) p.preds[row] = apply_transform((float)acc, p.tf);
   }
 }
 

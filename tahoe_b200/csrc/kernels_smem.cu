@@ -22,10 +22,6 @@
 namespace tahoe {
 
 constexpr int kSmemThreads = kSmemWarps * 32;
-#ifndef TAHOE_GROUP
-#define TAHOE_GROUP 4
-#endif
-constexpr int kGroup = TAHOE_GROUP;  // trees traversed together by one thread (ILP)
 
 // ---------------------------------------------------------------------------------------------
 struct QuantParams {
@@ -39,70 +35,89 @@ struct QuantParams {
   const float* lut_min;    // [cols]
   const float* lut_scale;  // [cols]
   const int32_t* lut;      // [cols][B+1]
+  int stride_log2;         // shared memory keeps every 2^stride_log2-th threshold of the column
   int rank_shift;
   uint32_t miss_code;
   uint32_t* qtiles;        // [tiles][cols][32]
-  uint32_t* tile_flags;    // [tiles]
+  uint32_t* tile_flags;    // [tiles], zeroed before the launch
   size_t num_tiles;
+  int splits;              // CTAs per column
 };
 
-constexpr int kQuantThreads = 256;
+constexpr int kQuantThreads = 1024;
+constexpr int kQuantUnroll = 4;   // tiles in flight per warp (independent strided loads)
 
-// Persistent blocks; each keeps the bucket LUT of every column in shared memory.  A warp owns a
-// 32-row tile: its input is one contiguous run of 32*cols floats (coalesced reads), its output the
-// column-major tile [col][32].  rank(v) = #{thr <= v}: one LUT lookup picks v's bucket, a short
-// binary search over that bucket's thresholds (one or two cache lines) finishes it.
-__global__ void __launch_bounds__(kQuantThreads) k_quantize(QuantParams p) {
+// One CTA = one COLUMN of the sample matrix over a range of 32-row tiles.  The column's sorted
+// threshold table (112 KB for the SUSY-shaped forest) and its bucket index sit in shared memory, so
+// rank(v) = #{thr <= v} is one index lookup plus a two-or-three-probe search that never leaves the
+// SM.  The CTAs of all columns walk the same rows at the same pace: a 32-byte sector of the
+// row-major input is fetched from HBM once and served to the other columns' CTAs by L2.  Output is
+// the column-major tile [tile][col][32 lanes]: one coalesced 128-byte store per warp.
+// Columns longer than shared memory keep every 2^k-th threshold there and finish with <= 2^k - 1
+// probes of one or two sectors of the full table.
+__global__ void __launch_bounds__(kQuantThreads, 1) k_quantize(QuantParams p) {
   extern __shared__ __align__(16) uint8_t qsm[];
-  const int B1 = p.buckets + 1;
-  int32_t* s_lut = reinterpret_cast<int32_t*>(qsm);                    // [cols][B+1]
-  float* s_min = reinterpret_cast<float*>(s_lut + (size_t)p.cols * B1);  // [cols]
-  float* s_scale = s_min + p.cols;                                     // [cols]
-  int32_t* s_off = reinterpret_cast<int32_t*>(s_scale + p.cols);       // [cols+1]
-  for (int i = threadIdx.x; i < p.cols * B1; i += kQuantThreads) s_lut[i] = p.lut[i];
-  for (int i = threadIdx.x; i < p.cols; i += kQuantThreads) { s_min[i] = p.lut_min[i]; s_scale[i] = p.lut_scale[i]; }
-  for (int i = threadIdx.x; i <= p.cols; i += kQuantThreads) s_off[i] = p.offsets[i];
+  const int c = blockIdx.x % p.cols;
+  const int split = blockIdx.x / p.cols;
+  const int B = p.buckets;
+  const int S = 1 << p.stride_log2;
+  const int off = p.offsets[c];
+  const int n = p.offsets[c + 1] - off;
+  const int ns = n >> p.stride_log2;                 // whole blocks of S thresholds
+  int32_t* s_lut = reinterpret_cast<int32_t*>(qsm);  // [B+1], in units of blocks, clamped to ns
+  float* s_tab = reinterpret_cast<float*>(s_lut + (B + 1));   // [ns] last threshold of each block
+  const float* tab = p.table + off;
+  for (int i = threadIdx.x; i <= B; i += kQuantThreads)
+    s_lut[i] = min(ns, p.lut[(size_t)c * (B + 1) + i] >> p.stride_log2);
+  for (int i = threadIdx.x; i < ns; i += kQuantThreads) s_tab[i] = __ldg(tab + (size_t)i * S + (S - 1));
   __syncthreads();
-  const int lane = threadIdx.x & 31;
-  const size_t warp = ((size_t)blockIdx.x * kQuantThreads + threadIdx.x) >> 5;
-  const size_t nwarps = ((size_t)gridDim.x * kQuantThreads) >> 5;
-  const int step_r = 32 / p.cols, step_c = 32 % p.cols;   // advance of (row, col) per 32 words
-  const float fB = (float)p.buckets;
-  for (size_t tile = warp; tile < p.num_tiles; tile += nwarps) {
-    const size_t row0 = tile * 32;
-    const size_t nrows = min((size_t)32, p.rows - row0);
-    const int total = (int)nrows * p.cols;
-    const float* src = p.data + row0 * (size_t)p.cols;
-    uint32_t* dst = p.qtiles + tile * (size_t)p.cols * 32;
-    bool any_missing = false;
-    int r = lane / p.cols, c = lane - r * p.cols;
-    for (int w = lane; w < 32 * p.cols; w += 32) {
-      uint32_t code = 0;
-      if (w < total) {
-        const float v = __ldg(src + w);
-        if (fabsf(v - p.missing) <= 1.0e-6f) {      // BaseTahoeTest.h:451-452
-          code = p.miss_code;
-          any_missing = true;
-        } else if (v == v) {                         // NaN: val >= thr is never true -> rank 0
-          const float x = (v - s_min[c]) * s_scale[c];
-          int b = x >= fB ? p.buckets - 1 : (int)x;  // float->int truncation is monotone
-          b = max(b, 0);
-          const int32_t* lut = s_lut + c * B1;
-          const float* tab = p.table + s_off[c];
-          int lo = lut[b], hi = lut[b + 1];
-          while (lo < hi) {                          // rank = #{thr <= v}
-            const int mid = (lo + hi) >> 1;
-            if (__ldg(tab + mid) <= v) lo = mid + 1; else hi = mid;
-          }
-          code = (uint32_t)lo << p.rank_shift;
-        }
-      }
-      dst[c * 32 + r] = code;
-      r += step_r; c += step_c;
-      if (c >= p.cols) { c -= p.cols; ++r; }
+  const float mn = p.lut_min[c], scale = p.lut_scale[c], fB = (float)B;
+
+  auto rank_code = [&](float v, bool& any_missing) -> uint32_t {
+    if (fabsf(v - p.missing) <= 1.0e-6f) {      // BaseTahoeTest.h:451-452
+      any_missing = true;
+      return p.miss_code;
     }
-    any_missing = __any_sync(0xffffffffu, any_missing);
-    if (lane == 0) p.tile_flags[tile] = any_missing ? 1u : 0u;
+    if (!(v == v)) return 0u;                    // NaN: val >= thr is never true -> rank 0
+    const float x = (v - mn) * scale;
+    int b = x >= fB ? B - 1 : (int)x;            // float->int truncation is monotone
+    b = max(b, 0);
+    int lo = s_lut[b], hi = s_lut[b + 1];
+    while (lo < hi) {                            // first block whose last threshold is > v
+      const int mid = (lo + hi) >> 1;
+      if (s_tab[mid] <= v) lo = mid + 1; else hi = mid;
+    }
+    int r = lo << p.stride_log2;
+    if (S > 1) {                                 // count inside that block (sorted: stop at the first > v)
+      const int end = min(n, r + S);
+      while (r < end && __ldg(tab + r) <= v) ++r;
+    }
+    return (uint32_t)r << p.rank_shift;
+  };
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int kWarps = kQuantThreads / 32;
+  const size_t per = (p.num_tiles + p.splits - 1) / p.splits;
+  const size_t t0 = (size_t)split * per, t1 = min(p.num_tiles, t0 + per);
+  for (size_t base = t0 + warp; base < t1; base += (size_t)kWarps * kQuantUnroll) {
+    float v[kQuantUnroll];
+    bool live[kQuantUnroll];
+#pragma unroll
+    for (int u = 0; u < kQuantUnroll; ++u) {
+      const size_t tile = base + (size_t)u * kWarps;
+      const size_t row = tile * 32 + lane;
+      live[u] = tile < t1 && row < p.rows;
+      v[u] = live[u] ? __ldg(p.data + row * (size_t)p.cols + c) : 0.0f;
+    }
+#pragma unroll
+    for (int u = 0; u < kQuantUnroll; ++u) {
+      const size_t tile = base + (size_t)u * kWarps;
+      if (tile >= t1) break;                     // warp-uniform
+      bool miss = false;
+      const uint32_t code = live[u] ? rank_code(v[u], miss) : 0u;
+      p.qtiles[(tile * p.cols + c) * 32 + lane] = code;
+      if (__any_sync(0xffffffffu, miss) && lane == 0) atomicOr(p.tile_flags + tile, 1u);
+    }
   }
 }
 
@@ -114,7 +129,9 @@ struct SmemParams {
   size_t rows;
   int cols;
   const uint32_t* qwords;   // [T][2^(d+1)]
-  int num_trees, trees_per_chunk, num_chunks;
+  int num_trees;            // real trees (leaf ids are written for these only)
+  int padded_trees;         // trees in qwords: whole traversal groups, the extra ones all zero
+  int trees_per_chunk, num_chunks;
   uint32_t col_mask, miss_code;
   float* preds;
   int32_t* leaf_ids;
@@ -122,7 +139,6 @@ struct SmemParams {
   Transform tf;
 };
 
-constexpr int kSlots = kSmemWarps * kSmemTileBufs;     // tile buffers per CTA (32)
 constexpr uint32_t kColStride = 128u * kSlots;          // bytes between column rows in the tile region
 static_assert(kColStride == (1u << kQuantColShiftWide), "wide column field must equal the region stride");
 
@@ -176,7 +192,7 @@ __device__ __forceinline__ void traverse_group(uint32_t tree_abs, uint32_t s_bas
   }
 }
 
-template <int DEPTH, bool LEAF_IDS, bool WIDE>
+template <int DEPTH, int G, bool LEAF_IDS, bool WIDE>
 __global__ void __launch_bounds__(kSmemThreads, 1) k_smem_forest(SmemParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr uint32_t W = 1u << (DEPTH + 1);      // words per tree
@@ -216,7 +232,7 @@ __global__ void __launch_bounds__(kSmemThreads, 1) k_smem_forest(SmemParams p) {
 
   for (int chunk = 0; chunk < p.num_chunks; ++chunk) {
     const int tree0 = chunk * p.trees_per_chunk;
-    const int ntrees = min(p.trees_per_chunk, p.num_trees - tree0);
+    const int ntrees = min(p.trees_per_chunk, p.padded_trees - tree0);   // a multiple of G
     // ---- stage this chunk of trees (everyone is done reading the previous one)
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -239,43 +255,46 @@ __global__ void __launch_bounds__(kSmemThreads, 1) k_smem_forest(SmemParams p) {
 
     const bool first = (chunk == 0), last = (chunk == p.num_chunks - 1);
     int buf = 0;
+    // the tile's missing flag and this lane's partial sum are fetched one tile ahead, so that their
+    // global-memory latency hides behind the traversal of the tile before
+    uint32_t flag_next = 0;
+    float acc_next = 0.0f;
+    if (tile < p.num_tiles) {
+      flag_next = __ldg(p.tile_flags + tile);
+      const size_t r0 = tile * 32 + lane;
+      if (!first && r0 < p.rows) acc_next = p.preds[r0];
+    }
     for (; tile < p.num_tiles; tile += warp_stride) {
       // prefetch the next tile into the other buffer (all lanes finished reading it)
       const size_t next = tile + warp_stride;
       __syncwarp();
-      if (next < p.num_tiles) load_tile(next, buf ^ 1);
-      const bool has_missing = __ldg(p.tile_flags + tile) != 0;
+      const bool has_missing = flag_next != 0;
+      float acc = acc_next;
+      if (next < p.num_tiles) {
+        load_tile(next, buf ^ 1);
+        flag_next = __ldg(p.tile_flags + next);
+        const size_t rn = next * 32 + lane;
+        acc_next = (!first && rn < p.rows) ? p.preds[rn] : 0.0f;
+      }
       mbar_wait(bar_tile0 + buf * 8, (tile_phase >> buf) & 1u);
       tile_phase ^= 1u << buf;
 
       const size_t row = tile * 32 + lane;
       const bool live = row < p.rows;
-      float acc = (first || !live) ? 0.0f : p.preds[row];
       const uint32_t slot_lane = (uint32_t)(warp * kSmemTileBufs + buf) * 128u + lane * 4u;
 
-      int t = 0;
-      for (; t + kGroup <= ntrees; t += kGroup) {
-        uint32_t a[kGroup];
+      for (int t = 0; t < ntrees; t += G) {
+        uint32_t a[G];
         const uint32_t tree_abs = s_base + forest_off + (uint32_t)t * W * 4u;
-        if (has_missing) traverse_group<DEPTH, kGroup, true, WIDE>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a);
-        else traverse_group<DEPTH, kGroup, false, WIDE>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a);
+        if (has_missing) traverse_group<DEPTH, G, true, WIDE>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a);
+        else traverse_group<DEPTH, G, false, WIDE>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a);
 #pragma unroll
-        for (int g = 0; g < kGroup; ++g) {
-          acc += __uint_as_float(lds_u32(a[g]));
-          if (LEAF_IDS && live)
+        for (int g = 0; g < G; ++g) {
+          acc += __uint_as_float(lds_u32(a[g]));   // a padding tree adds +0.0f: the sum keeps its bits
+          if (LEAF_IDS && live && tree0 + t + g < p.num_trees)
             p.leaf_ids[row * (size_t)p.num_trees + tree0 + t + g] =
                 __ldg(p.leaf_origin + (size_t)(tree0 + t + g) * L + ((a[g] - tree_abs - g * W * 4u) / 4 - L));
         }
-      }
-      for (; t < ntrees; ++t) {
-        uint32_t a[1];
-        const uint32_t tree_abs = s_base + forest_off + (uint32_t)t * W * 4u;
-        if (has_missing) traverse_group<DEPTH, 1, true, WIDE>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a);
-        else traverse_group<DEPTH, 1, false, WIDE>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a);
-        acc += __uint_as_float(lds_u32(a[0]));
-        if (LEAF_IDS && live)
-          p.leaf_ids[row * (size_t)p.num_trees + tree0 + t] =
-              __ldg(p.leaf_origin + (size_t)(tree0 + t) * L + ((a[0] - tree_abs) / 4 - L));
       }
       if (live) p.preds[row] = last ? apply_transform(acc, p.tf) : acc;
       buf ^= 1;
@@ -305,8 +324,11 @@ static int launch_depth(tahoe_forest* f, const SmemParams& p, unsigned grid, cud
     return TAHOE_OK;
   };
   const bool wide = f->col_shift == kQuantColShiftWide;
-  if (p.leaf_ids) return wide ? go(k_smem_forest<DEPTH, true, true>) : go(k_smem_forest<DEPTH, true, false>);
-  return wide ? go(k_smem_forest<DEPTH, false, true>) : go(k_smem_forest<DEPTH, false, false>);
+  // the leaf-id instantiation is the checking path: one tree at a time keeps the build small
+  if (p.leaf_ids) return wide ? go(k_smem_forest<DEPTH, 1, true, true>) : go(k_smem_forest<DEPTH, 1, true, false>);
+  if (f->group == kGroup) return wide ? go(k_smem_forest<DEPTH, kGroup, false, true>) : go(k_smem_forest<DEPTH, kGroup, false, false>);
+  if (f->group >= 2) return wide ? go(k_smem_forest<DEPTH, 2, false, true>) : go(k_smem_forest<DEPTH, 2, false, false>);
+  return wide ? go(k_smem_forest<DEPTH, 1, false, true>) : go(k_smem_forest<DEPTH, 1, false, false>);
 }
 
 int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
@@ -324,22 +346,25 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   q.data = a.data; q.rows = a.rows; q.cols = f->params.num_cols; q.missing = f->params.missing;
   q.table = f->d_qtable; q.offsets = f->d_qoffsets; q.buckets = f->host.qbuckets;
   q.lut_min = f->d_qlut_min; q.lut_scale = f->d_qlut_scale; q.lut = f->d_qlut;
+  q.stride_log2 = ilog2_c(f->quant_stride);
   q.rank_shift = f->rank_shift; q.miss_code = f->miss_code; q.qtiles = a.ws->qtiles;
   q.tile_flags = a.ws->tile_flags; q.num_tiles = tiles;
-  const size_t qsmem = ((size_t)q.cols * (q.buckets + 1) + 3 * (size_t)q.cols + 1) * 4;
-  if (qsmem > 48 * 1024)
-    TAHOE_CUDA(cudaFuncSetAttribute(k_quantize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qsmem));
-  const size_t qwarps_per_block = kQuantThreads / 32;
-  const int qblocks_per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, ((size_t)f->smem_optin - 1024) / (qsmem + 1024)));
-  unsigned qgrid = (unsigned)std::min<size_t>((tiles + qwarps_per_block - 1) / qwarps_per_block,
-                                              (size_t)f->sm_count * qblocks_per_sm);
+  // CTAs = columns x splits; every split is a contiguous range of tiles, at least one pass of the
+  // CTA's warps long, and the grid fills the SMs once (one CTA per SM: its table owns shared memory)
+  const size_t tiles_per_pass = (size_t)(kQuantThreads / 32) * kQuantUnroll;
+  q.splits = (int)std::max<size_t>(1, std::min<size_t>((tiles + tiles_per_pass - 1) / tiles_per_pass,
+                                                        (size_t)std::max(1, f->sm_count / q.cols)));
+  const unsigned qgrid = (unsigned)(q.cols * q.splits);
+  if (f->quant_smem > 48 * 1024)
+    TAHOE_CUDA(cudaFuncSetAttribute(k_quantize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->quant_smem));
   cudaEvent_t* ev = nullptr;
   if (f->profile && a.ws == &f->ws[0] && f->prof_count < kProfRing) {
     ev = &f->prof_events[(size_t)f->prof_count * 3];
     ++f->prof_count;
     TAHOE_CUDA(cudaEventRecord(ev[0], a.stream));
   }
-  k_quantize<<<qgrid, kQuantThreads, qsmem, a.stream>>>(q);
+  TAHOE_CUDA(cudaMemsetAsync(a.ws->tile_flags, 0, tiles * sizeof(uint32_t), a.stream));
+  k_quantize<<<qgrid, kQuantThreads, f->quant_smem, a.stream>>>(q);
   if (ev) TAHOE_CUDA(cudaEventRecord(ev[1], a.stream));
   TAHOE_CUDA(cudaGetLastError());
   ++*launches;
@@ -347,6 +372,7 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   SmemParams p{};
   p.qtiles = a.ws->qtiles; p.tile_flags = a.ws->tile_flags; p.num_tiles = tiles; p.rows = a.rows;
   p.cols = f->params.num_cols; p.qwords = f->d_qwords; p.num_trees = f->params.num_trees;
+  p.padded_trees = f->qwords_trees;
   p.trees_per_chunk = f->trees_per_chunk; p.num_chunks = f->num_chunks;
   p.col_mask = f->col_mask; p.miss_code = f->miss_code; p.preds = a.preds; p.leaf_ids = a.leaf_ids;
   p.leaf_origin = f->d_leaf_origin;

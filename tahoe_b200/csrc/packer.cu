@@ -227,8 +227,10 @@ static int build_quant(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
   // thresholds in lower buckets are < v and thresholds in higher buckets are > v; only v's own
   // bucket needs a search.  Host and device evaluate bucket() with the same IEEE float ops.
   {
-    int B = 1024;
-    while (B > 16 && (size_t)C * (B + 1) * 4 > 96 * 1024) B >>= 1;
+    // about two buckets per threshold of the busiest column; k_quantize keeps ONE column's index in
+    // shared memory at a time, so the bound is per column
+    int B = 16;
+    while (B < kQuantMaxBuckets && (size_t)B < 2 * max_n) B <<= 1;
     h.qbuckets = B;
     h.qlut_min.assign(C, 0.0f);
     h.qlut_scale.assign(C, 0.0f);
@@ -351,20 +353,41 @@ void plan_chunks(tahoe_forest* f) {
   f->trees_per_chunk = 0;
   f->num_chunks = 0;
   f->smem_bytes = 0;
+  f->group = 1;
+  f->qwords_trees = f->params.num_trees;
   if (!f->quant) return;
+  const int T = f->params.num_trees;
   const size_t tile_bytes = (size_t)f->params.num_cols * 128;
-  const size_t tiles = (size_t)kSmemWarps * kSmemTileBufs * tile_bytes;
+  const size_t tiles = (size_t)kSlots * tile_bytes;
   const size_t bars = 1024;
   const size_t tree_bytes = ((size_t)1 << (f->depth + 1)) * 4;
-  if ((size_t)f->smem_optin < tiles + bars + tree_bytes) return;
-  size_t avail = (size_t)f->smem_optin - tiles - bars;
-  int tpc = (int)std::min<size_t>(avail / tree_bytes, (size_t)f->params.num_trees);
-  // balance the chunks: same chunk count, trees spread evenly
-  int chunks = (f->params.num_trees + tpc - 1) / tpc;
-  tpc = (f->params.num_trees + chunks - 1) / chunks;
+  if ((size_t)f->smem_optin < tiles + bars + tree_bytes) { f->quant_stride = 1; f->quant_smem = 0; return; }
+  const size_t avail = (size_t)f->smem_optin - tiles - bars;
+  const int max_tpc = (int)std::min<size_t>(avail / tree_bytes, (size_t)T);
+  // traversal group: kGroup trees in flight per thread when a chunk holds that many, else 2 or 1
+  const int G = kGroup <= max_tpc ? kGroup : (max_tpc >= 2 ? 2 : 1);
+  const int tpad = (T + G - 1) / G * G;            // all-zero trees pad the forest to whole groups
+  int tpc = std::min(max_tpc / G * G, tpad);
+  // balance the chunks: same chunk count, trees spread evenly in whole groups
+  const int chunks = (tpad + tpc - 1) / tpc;
+  tpc = ((tpad + chunks - 1) / chunks + G - 1) / G * G;
+  f->group = G;
+  f->qwords_trees = tpad;
   f->trees_per_chunk = tpc;
-  f->num_chunks = chunks;
+  f->num_chunks = (tpad + tpc - 1) / tpc;
   f->smem_bytes = tiles + bars + (size_t)tpc * tree_bytes;
+
+  // k_quantize: one column's sorted thresholds (every quant_stride-th of them when the column is
+  // too long) + its bucket index live in shared memory
+  size_t max_n = 0;
+  for (int c = 0; c < f->params.num_cols; ++c)
+    max_n = std::max<size_t>(max_n, (size_t)(f->host.qoffsets[c + 1] - f->host.qoffsets[c]));
+  const size_t lut_bytes = ((size_t)f->host.qbuckets + 1) * 4;
+  const size_t budget = (size_t)f->smem_optin - 2048 - lut_bytes;
+  int S = 1;
+  while ((max_n / S + 1) * 4 > budget) S <<= 1;
+  f->quant_stride = S;
+  f->quant_smem = lut_bytes + (max_n / S + 1) * 4 + 16;
 }
 
 template <typename T>
@@ -403,7 +426,13 @@ int upload(tahoe_forest* f) {
   if ((rc = to_device(&f->d_inter, h.inter))) return rc;
   if ((rc = to_device(&f->d_tree_order, h.tree_order))) return rc;
   if ((rc = to_device(&f->d_orig_ids, h.orig_ids))) return rc;
-  if ((rc = to_device(&f->d_qwords, h.qwords))) return rc;
+  if (!h.qwords.empty()) {   // padded with all-zero trees to whole traversal groups
+    const size_t W = (size_t)1 << (f->depth + 1);
+    const size_t words = (size_t)f->qwords_trees * W;
+    TAHOE_CUDA(cudaMalloc((void**)&f->d_qwords, words * 4));
+    TAHOE_CUDA(cudaMemset(f->d_qwords, 0, words * 4));
+    TAHOE_CUDA(cudaMemcpy(f->d_qwords, h.qwords.data(), h.qwords.size() * 4, cudaMemcpyHostToDevice));
+  }
   if ((rc = to_device(&f->d_qtable, h.qtable))) return rc;
   if ((rc = to_device(&f->d_qoffsets, h.qoffsets))) return rc;
   if ((rc = to_device(&f->d_leaf_origin, h.leaf_origin))) return rc;
