@@ -1,0 +1,301 @@
+// BaseTahoeTest.h -- host-side mirror of the reference harness class, written against the C ABI.
+//
+// Drop-in for the reference's `BaseTahoeTest` (BaseTahoeTest.h:45-907): same constructor
+// signature (:49), `int SetUp(float& speedup)` (:71-115), the README's zero-argument `SetUp()`
+// (README.md:80-84), `Free()` (:873-882), `TearDown()` (:117-121), the public members the
+// reference exposes (`ps`, `nodes`, `data_h`, `data_d`, `preds_d`, `want_preds_d`, `stream`,
+// :889-906) and its console strings.  Nothing below is copied from the
+// reference: every GPU step goes through include/tahoe_b200.h; the CPU "standard results"
+// (predict_on_cpu, :458-487) are the harness's checker, as they are in the reference -- they are
+// never returned as a prediction.
+//
+// Differences, on purpose:
+//   * the five strategies are the sm_100a kernels of libtahoe_b200.so, selected by a named enum
+//     instead of the global `selected_algorithm` (Struct.h:11);
+//   * the "FIL (baseline)" line (:577) times the library's SHARED_DATA strategy, which is the
+//     strategy the reference's FIL baseline runs (Struct.h:410-491); the FIL kernels themselves
+//     are out of scope;
+//   * timing uses CUDA events on the launch stream, not gettimeofday (:687-698);
+//   * a CUDA failure ends SetUp with a message instead of printing and carrying on
+//     (cuda_base.h:19-25).
+#ifndef TAHOE_B200_BASETAHOETEST_H
+#define TAHOE_B200_BASETAHOETEST_H
+
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "tahoe_b200.h"
+
+// ---- enums and parameter block, same names and values as Struct.h:23-42, 118-142 ----------------
+enum algo_t { NAIVE, TREE_REORG, BATCH_TREE_REORG };
+enum strategy_t { SHARED_DATA, SHARED_FOREST, SPLIT_FOREST, SPLIT_FOREST_SHARED_DATA };
+enum output_t { RAW = 0x0, AVG = 0x1, SIGMOID = 0x10, THRESHOLD = 0x100 };
+typedef tahoe_dense_node_t dense_node_t;   // {float weight; float val; int bits;}  Struct.h:44-48
+
+struct TahoeTestParams {
+  int num_rows;
+  int num_cols;
+  float nan_prob;
+  int depth;
+  int num_trees;
+  float leaf_prob;
+  output_t output;
+  float threshold;
+  float global_bias;
+  algo_t algo;
+  int seed;
+  float tolerance;
+  strategy_t strategy;
+  char input_model_file[1024];
+  char input_data_file[1024];
+  float missing;
+};
+
+static int epoch_new = 50;   // timed predicts per strategy (BaseTahoeTest.h:43)
+
+class BaseTahoeTest {
+ public:
+  BaseTahoeTest(std::string input_model_file, std::string input_data_file, int algorithm = 0,
+                int num_rows = 1000, int num_cols = 500, float nan_prob = 0.0, int depth = 20,
+                int num_trees = 10, float leaf_prob = 0.0, output_t output = RAW,
+                float threshold = 0.0, float global_bias = 0.0, algo_t algo = NAIVE, int seed = 0,
+                float tolerance = 1e-3f, strategy_t strategy = SHARED_DATA) {
+    std::memset(&ps, 0, sizeof(ps));
+    ps.num_rows = num_rows; ps.num_cols = num_cols; ps.nan_prob = nan_prob;
+    ps.depth = depth; ps.num_trees = num_trees; ps.leaf_prob = leaf_prob;
+    ps.output = output; ps.threshold = threshold; ps.global_bias = global_bias;
+    ps.algo = algo; ps.seed = seed; ps.tolerance = tolerance; ps.strategy = strategy;
+    std::snprintf(ps.input_model_file, sizeof(ps.input_model_file), "%s", input_model_file.c_str());
+    std::snprintf(ps.input_data_file, sizeof(ps.input_data_file), "%s", input_data_file.c_str());
+    selected_algorithm = algorithm;
+  }
+  ~BaseTahoeTest() { Free(); }
+
+  // ---- SetUp: load, CPU standard results, time every strategy, pick the fastest -----------------
+  // Returns the best strategy id 1..5 (BaseTahoeTest.h:93-109); speedup = baseline / best (:111).
+  int SetUp(float& speedup) {
+    float acc[5];
+    speedup = 0.0f;
+    if (!ok(cudaStreamCreate(&stream), "cudaStreamCreate")) return 0;
+    std::printf("Loading model...\n");
+    generate_forest_from_file();
+    std::printf("Loading data...\n");
+    generate_data_from_file();
+    std::printf("Predict on CPU to get standard results...\n");
+    predict_on_cpu();
+    std::printf("Test on GPU...\n");
+    if (!init_forest()) return 0;
+    const float baseline = predict_on_gpu_dense();
+    predict_on_gpu_dense_adaptive(acc);
+    int algorithm = 0;
+    float time = FLT_MAX;
+    for (int s = 0; s < 5; ++s)
+      if (acc[s] < time) { algorithm = s + 1; time = acc[s]; }
+    if (algorithm) speedup = baseline / time;
+    best_algorithm = algorithm;
+    return algorithm;
+  }
+  int SetUp() { float s; return SetUp(s); }   // README.md:80-84
+
+  void TearDown() {                            // BaseTahoeTest.h:117-121
+    if (preds_d) cudaFree(preds_d);
+    if (want_preds_d) cudaFree(want_preds_d);
+    if (data_d) cudaFree(data_d);
+    preds_d = want_preds_d = data_d = nullptr;
+  }
+
+  void Free() {                                // BaseTahoeTest.h:873-882
+    TearDown();
+    if (forest) { tahoe_forest_destroy(forest); forest = nullptr; }
+    if (stream) { cudaStreamDestroy(stream); stream = nullptr; }
+  }
+
+  size_t tree_num_nodes() const { return ((size_t)1 << (ps.depth + 1)) - 1; }   // Struct.h:15-17
+
+  // ---- loaders: the reference's text grammar, parsed by the library ---------
+  void generate_forest_from_file() {           // BaseTahoeTest.h:267-352
+    tahoe_dense_node_t* p = nullptr;
+    int T = 0, d = 0;
+    if (tahoe_load_model_text(ps.input_model_file, &p, &T, &d) != TAHOE_OK) {
+      std::printf("Cannot open file %s : %s\n", ps.input_model_file, tahoe_last_error());
+      std::exit(1);                            // as the reference does (:273-277)
+    }
+    ps.num_trees = T;
+    ps.depth = d;
+    nodes.assign(p, p + (size_t)T * tree_num_nodes());
+    tahoe_free_host(p);
+  }
+
+  void generate_data_from_file() {             // BaseTahoeTest.h:354-402 (parse + upload)
+    float* p = nullptr;
+    int R = 0, C = 0;
+    float missing = 0.0f;
+    if (tahoe_load_data_text(ps.input_data_file, &p, &R, &C, &missing) != TAHOE_OK) {
+      std::printf("Cannot open file %s : %s\n", ps.input_data_file, tahoe_last_error());
+      std::exit(1);
+    }
+    ps.num_rows = R; ps.num_cols = C; ps.missing = missing;
+    data_h.assign(p, p + (size_t)R * C);
+    tahoe_free_host(p);
+    const size_t bytes = data_h.size() * sizeof(float);
+    if (data_d) cudaFree(data_d);
+    data_d = nullptr;
+    if (bytes && ok(cudaMalloc((void**)&data_d, bytes), "cudaMalloc(data)"))
+      ok(cudaMemcpyAsync(data_d, data_h.data(), bytes, cudaMemcpyHostToDevice, stream), "upload data");
+  }
+
+  // ---- CPU "standard results": the harness's checker (BaseTahoeTest.h:440-487) -------------------
+  float infer_one_tree(dense_node_t* root, float* data) {
+    int curr = 0;
+    for (;;) {
+      const dense_node_t& n = root[curr];
+      if (n.bits < 0) return n.val;                                   // is_leaf = bit 31
+      const float v = data[n.bits & 0x3FFFFFFF];
+      const bool def_left = (n.bits & 0x40000000) != 0;
+      const bool right = (std::fabs(v - ps.missing) <= 1.0e-6f) ? !def_left : (v >= n.val);
+      curr = 2 * curr + 1 + (right ? 1 : 0);
+    }
+  }
+
+  void predict_on_cpu() {
+    const size_t npt = tree_num_nodes();
+    want_preds_h.assign((size_t)ps.num_rows, 0.0f);
+    for (int i = 0; i < ps.num_rows; ++i) {
+      float pred = 0.0f;
+      for (int j = 0; j < ps.num_trees; ++j)
+        pred += infer_one_tree(&nodes[(size_t)j * npt], &data_h[(size_t)i * ps.num_cols]);
+      if (ps.output & AVG) pred = pred / ps.num_trees;
+      pred += ps.global_bias;
+      if (ps.output & SIGMOID) pred = 1.0f / (1.0f + std::exp(-pred));
+      if (ps.output & THRESHOLD) pred = pred > ps.threshold ? 1.0f : 0.0f;
+      want_preds_h[i] = pred;
+    }
+    const size_t bytes = want_preds_h.size() * sizeof(float);
+    if (want_preds_d) cudaFree(want_preds_d);
+    if (preds_d) cudaFree(preds_d);
+    want_preds_d = preds_d = nullptr;
+    if (bytes) {
+      if (ok(cudaMalloc((void**)&want_preds_d, bytes), "cudaMalloc(want_preds)"))
+        ok(cudaMemcpyAsync(want_preds_d, want_preds_h.data(), bytes, cudaMemcpyHostToDevice, stream), "upload");
+      ok(cudaMalloc((void**)&preds_d, bytes), "cudaMalloc(preds)");
+    }
+  }
+
+  // ---- GPU side: everything below goes through the C ABI ----------------------------------------
+  bool init_forest() {                         // init_forest_dense_adaptive, BaseTahoeTest.h:605-631
+    tahoe_forest_params_t fp;
+    std::memset(&fp, 0, sizeof(fp));
+    fp.depth = ps.depth; fp.num_trees = ps.num_trees; fp.num_cols = ps.num_cols;
+    fp.algo = (int)ps.algo; fp.output = (int)ps.output; fp.threshold = ps.threshold;
+    fp.global_bias = ps.global_bias; fp.strategy = (int)ps.strategy; fp.missing = ps.missing;
+    if (forest) { tahoe_forest_destroy(forest); forest = nullptr; }
+    if (tahoe_forest_create_dense(nodes.data(), &fp, &forest) != TAHOE_OK) {
+      std::printf("FAIL: forest creation: %s\n", tahoe_last_error());
+      return false;
+    }
+    return true;
+  }
+
+  // The performance model's pick, as a SetUp-style id 1..5 (replaces main.cu:22-82).
+  int model_choice() {
+    if (!forest && !(nodes.size() && init_forest())) return 0;
+    return tahoe_select_strategy(forest, (size_t)ps.num_rows, nullptr) + 1;
+  }
+
+  // One strategy: 5 warm-ups, epoch_new timed predicts, microseconds per sample; FLT_MAX when the
+  // strategy cannot run this forest (the reference prints the same sentence, :662-678).
+  float time_strategy(int strategy, bool announce) {
+    if (tahoe_strategy_applicable(forest, strategy, (size_t)ps.num_rows) != TAHOE_OK) {
+      if (announce) std::printf("Strategy %d is not suitable for this case.\n", strategy + 1);
+      return FLT_MAX;
+    }
+    if (announce) std::printf("Using strategy %d\n", strategy + 1);
+    for (int i = 0; i < 5; ++i)
+      if (!predict(strategy)) return FLT_MAX;
+    cudaEvent_t e0, e1;
+    if (!ok(cudaEventCreate(&e0), "event") || !ok(cudaEventCreate(&e1), "event")) return FLT_MAX;
+    cudaEventRecord(e0, stream);
+    for (int i = 0; i < epoch_new; ++i)
+      if (!predict(strategy)) return FLT_MAX;
+    cudaEventRecord(e1, stream);
+    if (!ok(cudaEventSynchronize(e1), "predict")) return FLT_MAX;
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return ms * 1000.0f / ((float)epoch_new * (float)(ps.num_rows > 0 ? ps.num_rows : 1));
+  }
+
+  float predict_on_gpu_dense() {               // the "FIL (baseline)" line, BaseTahoeTest.h:549-596
+    const int s = tahoe_strategy_applicable(forest, TAHOE_STRATEGY_SHARED_DATA, (size_t)ps.num_rows) == TAHOE_OK
+                      ? TAHOE_STRATEGY_SHARED_DATA : TAHOE_STRATEGY_DIRECT;
+    const float us = time_strategy(s, false);
+    std::printf("Exec.Time/Sample on FIL (baseline) is %f us\n", us);
+    compare();
+    return us;
+  }
+
+  void predict_on_gpu_dense_adaptive(float* acc) {   // the five-strategy loop, BaseTahoeTest.h:633-710
+    for (int s = 0; s < TAHOE_NUM_STRATEGIES; ++s) {
+      acc[s] = time_strategy(s, true);
+      if (acc[s] == FLT_MAX) continue;
+      std::printf("Exec.Time/Sample on strategy %d is %f us\n", s + 1, acc[s]);
+      compare();
+    }
+  }
+
+  bool predict(int strategy) {                 // forest::predict, Struct.h:245-269
+    if (tahoe_predict(forest, strategy, data_d, (size_t)ps.num_rows, preds_d, nullptr, stream) != TAHOE_OK) {
+      std::printf("FAIL: predict: %s\n", tahoe_last_error());
+      return false;
+    }
+    return true;
+  }
+
+  // compare_GPU, cuda_base.h:98-111: absolute difference against the CPU results, tolerance
+  // ps.tolerance (1e-3), verdict printed.  Done on the host here (one D2H copy) instead of a
+  // single-thread kernel.  Returns the verdict as well.
+  bool compare() {
+    std::vector<float> got((size_t)ps.num_rows);
+    if (!got.empty()) {
+      if (!ok(cudaMemcpyAsync(got.data(), preds_d, got.size() * sizeof(float), cudaMemcpyDeviceToHost, stream), "download") ||
+          !ok(cudaStreamSynchronize(stream), "sync"))
+        return false;
+    }
+    bool same = true;
+    for (size_t i = 0; i < got.size() && same; ++i)
+      same = std::fabs(got[i] - want_preds_h[i]) <= ps.tolerance;   // NaN fails, as it should
+    std::printf(same ? "Results are correct\n" : "Results are incorrect\n");
+    last_compare_ok = same;
+    return same;
+  }
+
+  // ---- public state, as in the reference (BaseTahoeTest.h:889-906) -------------------------------
+  float* preds_d = nullptr;
+  float* want_preds_d = nullptr;
+  float* data_d = nullptr;
+  cudaStream_t stream = nullptr;
+  TahoeTestParams ps;
+  std::vector<float> data_h;
+  std::vector<float> want_preds_h;             // the reference keeps these in a local (:460)
+  std::vector<dense_node_t> nodes;
+  tahoe_forest_t* forest = nullptr;            // replaces `forest* forest` / dense_adaptive_forest
+  int selected_algorithm = 0;                  // a member here; a mutable global there (Struct.h:11)
+  int best_algorithm = 0;
+  bool last_compare_ok = false;
+
+ private:
+  static bool ok(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return true;
+    std::printf("FAIL: %s: %s\n", what, cudaGetErrorString(e));
+    return false;
+  }
+};
+
+#endif  // TAHOE_B200_BASETAHOETEST_H

@@ -91,7 +91,10 @@ typedef struct {
   int device;
   int sm_count;
   int smem_optin_bytes;
-  int col_shift;              /* bit position of the column field in a quantised node word (7 or 12) */
+  int col_shift;              /* bit position of the column field in a quantised node word (7 = compact, else wide) */
+  int smem_warps;             /* shared-memory-forest plan: warps per CTA, */
+  int smem_staged;            /*   1 = one tile buffer per warp + register staging, 0 = two by TMA, */
+  int smem_group;             /*   trees traversed together by one thread */
 } tahoe_forest_info_t;
 
 /* ---- forest lifetime -------------------------------------------------------------

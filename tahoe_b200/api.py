@@ -52,7 +52,8 @@ class ForestInfo(C.Structure):
                 ("trees_per_chunk", C.c_int), ("num_chunks", C.c_int), ("bytes_heap", C.c_int64),
                 ("bytes_interleaved", C.c_int64), ("bytes_quantized", C.c_int64),
                 ("exchanged_nodes", C.c_int64), ("mean_depth", C.c_double), ("device", C.c_int),
-                ("sm_count", C.c_int), ("smem_optin_bytes", C.c_int), ("col_shift", C.c_int)]
+                ("sm_count", C.c_int), ("smem_optin_bytes", C.c_int), ("col_shift", C.c_int),
+                ("smem_warps", C.c_int), ("smem_staged", C.c_int), ("smem_group", C.c_int)]
 
 
 _lib = None

@@ -15,6 +15,7 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "lib", "libtahoe_b200.so")
 SOURCES = ["abi.cu", "packer.cu", "textio.cu", "gen.cu", "kernels_direct.cu",
            "kernels_shared_data.cu", "kernels_smem.cu"]
+MAX_DEPTH = 14
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-O2,-fno-fast-math", "--fmad=true", "-prec-div=true",
               "-prec-sqrt=true", "-ftz=false"]
@@ -31,19 +32,28 @@ def build(force: bool = False, verbose: bool = False) -> str:
     headers.append(os.path.join(HERE, "..", "include", "tahoe_b200.h"))
     hdr_time = max(os.path.getmtime(h) for h in headers)
     jobs = []
+    objs = []
     for s in SOURCES:
         src, obj = os.path.join(CSRC, s), os.path.join(OBJ, s + ".o")
+        objs.append(obj)
         if force or _newer(src, obj) or hdr_time > os.path.getmtime(obj):
             jobs.append(["nvcc", *NVCC_FLAGS, "-c", src, "-o", obj])
+    # k_smem_forest: one object per tree depth, so the instantiations compile in parallel
+    src = os.path.join(CSRC, "kernels_smem_depth.cu")
+    for d in range(1, MAX_DEPTH + 1):
+        obj = os.path.join(OBJ, f"kernels_smem_depth_{d}.o")
+        objs.append(obj)
+        if force or _newer(src, obj) or hdr_time > os.path.getmtime(obj):
+            jobs.insert(0, ["nvcc", *NVCC_FLAGS, f"-DTAHOE_DEPTH={d}", "-c", src, "-o", obj])
+    jobs.sort(key=lambda j: 0 if any(a.startswith("-DTAHOE_DEPTH=") for a in j) else 1)
 
     def run(cmd):
         if verbose:
             print(" ".join(cmd), flush=True)
         subprocess.run(cmd, check=True)
 
-    with ThreadPoolExecutor(max_workers=min(8, max(1, len(jobs)))) as ex:
+    with ThreadPoolExecutor(max_workers=min(os.cpu_count() or 4, max(1, len(jobs)))) as ex:
         list(ex.map(run, jobs))
-    objs = [os.path.join(OBJ, s + ".o") for s in SOURCES]
     if jobs or not os.path.exists(LIB):
         run(["nvcc", "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs,
              "-cudart", "static"])

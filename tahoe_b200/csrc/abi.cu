@@ -126,9 +126,9 @@ int tahoe_forest_create_dense(const tahoe_dense_node_t* nodes, const tahoe_fores
   tahoe_forest* f = new (std::nothrow) tahoe_forest;
   if (!f) return TAHOE_ERR_NOMEM;
   f->params = *params;
-  int rc;
+  int rc = query_device(f);
   try {
-    rc = pack_dense(f, nodes);
+    if (rc == TAHOE_OK) rc = pack_dense(f, nodes);
   } catch (const std::bad_alloc&) {
     set_error("out of host memory while packing"); rc = TAHOE_ERR_NOMEM;
   }
@@ -146,9 +146,9 @@ int tahoe_forest_create_sparse(const tahoe_sparse_node_t* nodes, const float* we
   tahoe_forest* f = new (std::nothrow) tahoe_forest;
   if (!f) return TAHOE_ERR_NOMEM;
   f->params = *params;
-  int rc;
+  int rc = query_device(f);
   try {
-    rc = pack_sparse(f, nodes, weights, tree_offsets);
+    if (rc == TAHOE_OK) rc = pack_sparse(f, nodes, weights, tree_offsets);
   } catch (const std::bad_alloc&) {
     set_error("out of host memory while packing"); rc = TAHOE_ERR_NOMEM;
   }
@@ -182,6 +182,7 @@ int tahoe_forest_info(const tahoe_forest_t* f, tahoe_forest_info_t* info) {
   info->bytes_quantized = (int64_t)(f->host.qwords.size() * sizeof(uint32_t));
   info->exchanged_nodes = f->exchanged; info->mean_depth = f->mean_depth; info->device = f->device;
   info->sm_count = f->sm_count; info->smem_optin_bytes = f->smem_optin; info->col_shift = f->col_shift;
+  info->smem_warps = f->warps; info->smem_staged = f->staged; info->smem_group = f->group;
   return TAHOE_OK;
 }
 

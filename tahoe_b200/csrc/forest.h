@@ -27,28 +27,17 @@ constexpr uint32_t kMetaExchange = 1u << 29;     // I8 only (reference EXCHANGE_
 constexpr uint32_t kMetaDefLeft = 1u << 30;      // same bit as the reference's DEF_LEFT_MASK, Struct.h:58
 constexpr uint32_t kMetaLeaf = 1u << 31;         // same bit as IS_LEAF_MASK, Struct.h:59
 
-// Tunables of the shared-memory-forest kernel (variant builds override them with -D, see
-// tools/build_variant.sh; every translation unit must see the same values).
-#ifndef TAHOE_WARPS
-#define TAHOE_WARPS 16
-#endif
-#ifndef TAHOE_BUFS
-#define TAHOE_BUFS 2
-#endif
-#ifndef TAHOE_GROUP
-#define TAHOE_GROUP 6
-#endif
-constexpr int kSmemWarps = TAHOE_WARPS;          // warps per CTA of the shared-memory-forest kernel
-constexpr int kSmemTileBufs = TAHOE_BUFS;        // sample-tile buffers per warp
-constexpr int kSlots = kSmemWarps * kSmemTileBufs;  // tile buffers per CTA (a power of two)
-constexpr int kGroup = TAHOE_GROUP;              // trees traversed together by one thread (ILP)
-static_assert((kSlots & (kSlots - 1)) == 0 && kSlots >= 1 && kSlots <= 64, "tile slots must be a power of two");
+// Shared-memory-forest kernel: the plan (warps per CTA, tile buffering, trees per traversal group)
+// is chosen per forest at pack time (plan_chunks) and is all run-time state of the handle; the
+// environment variable TAHOE_SMEM_PLAN="warps,staged,group" overrides it for tuning runs.
+constexpr int kSmemMaxWarps = 16;                // 512 threads, one persistent CTA per SM
+constexpr int kMaxGroup = 6;                     // trees traversed together by one thread (ILP): 1..6
+constexpr int kStagedMaxCols = 32;               // register-staged tiles keep one word per column per lane
 constexpr int ilog2_c(int v) { return v <= 1 ? 0 : 1 + ilog2_c(v >> 1); }
 
-constexpr int kQuantColShift = 7;                // Q4 word, compact form: column index in bits 7..
-constexpr int kQuantColShiftWide = 7 + ilog2_c(kSlots);  // Q4 word, wide form: column * (128 * kSlots) = its
-                                                 // byte offset in the tile region (all kSlots warp buffers of a
-                                                 // column interleaved, 128 B each)
+constexpr int kQuantColShift = 7;                // Q4 word, compact form: column index in bits 7.. (the wide
+                                                 // form puts it at log2(128 * tile slots): the field is then
+                                                 // the byte offset of the column row in the tile region)
 constexpr int kQuantMaxDepth = 14;               // 2^(d+1) words per tree must fit shared memory
 constexpr int kQuantMaxCols = 64;                // one warp tile = cols * 128 B of shared memory
 constexpr int kQuantMaxBuckets = 8192;           // bucket index of one column: (B+1) ints of shared memory
@@ -105,7 +94,10 @@ struct tahoe_forest {
   int rank_bits = 0, col_bits = 0, rank_shift = 0, col_shift = 0;
   uint32_t col_mask = 0, miss_code = 0;
   int trees_per_chunk = 0, num_chunks = 0;
-  int group = 1;                 // trees per traversal group (1, 2, 4 or kGroup); qwords_trees is a multiple
+  int group = 1;                 // trees per traversal group (1..kMaxGroup); qwords_trees is a multiple
+  int warps = tahoe::kSmemMaxWarps;  // warps per CTA of k_smem_forest
+  bool staged = false;           // one tile buffer per warp, next tile staged in registers (else 2, by TMA)
+  int slots = 0;                 // tile buffers per CTA = warps * (staged ? 1 : 2), a power of two
   int qwords_trees = 0;          // trees in d_qwords: num_trees padded with all-zero trees (leaf value +0.0f)
   size_t smem_bytes = 0;
   int quant_stride = 1;          // k_quantize keeps every quant_stride-th threshold of a column in shared memory
@@ -167,6 +159,7 @@ struct PredictArgs {
 int launch_direct(tahoe_forest* f, const PredictArgs& a, bool rows_in_smem, int* launches);
 int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches);
 int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches);
+int query_device(tahoe_forest* f);
 int ensure_workspace(tahoe_forest* f, Workspace* ws, size_t rows);
 
 }  // namespace tahoe

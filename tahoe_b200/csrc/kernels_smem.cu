@@ -16,12 +16,9 @@
 //                  Partial sums are carried in preds[] between chunks by the same thread,
 //                  in tree order, so the float sum is the CPU's sum bit for bit -- no
 //                  [rows x blocks] temp and no segmented reduce.
-#include "device_utils.cuh"
-#include "forest.h"
+#include "kernels_smem_traverse.cuh"   // SmemParams; the kernel itself is instantiated per depth
 
 namespace tahoe {
-
-constexpr int kSmemThreads = kSmemWarps * 32;
 
 // ---------------------------------------------------------------------------------------------
 struct QuantParams {
@@ -121,186 +118,6 @@ __global__ void __launch_bounds__(kQuantThreads, 1) k_quantize(QuantParams p) {
   }
 }
 
-// ---------------------------------------------------------------------------------------------
-struct SmemParams {
-  const uint32_t* qtiles;
-  const uint32_t* tile_flags;
-  size_t num_tiles;
-  size_t rows;
-  int cols;
-  const uint32_t* qwords;   // [T][2^(d+1)]
-  int num_trees;            // real trees (leaf ids are written for these only)
-  int padded_trees;         // trees in qwords: whole traversal groups, the extra ones all zero
-  int trees_per_chunk, num_chunks;
-  uint32_t col_mask, miss_code;
-  float* preds;
-  int32_t* leaf_ids;
-  const int32_t* leaf_origin;  // [T][2^d]
-  Transform tf;
-};
-
-constexpr uint32_t kColStride = 128u * kSlots;          // bytes between column rows in the tile region
-static_assert(kColStride == (1u << kQuantColShiftWide), "wide column field must equal the region stride");
-
-// Shared-memory map of k_smem_forest (byte offsets from smem[]):
-//   [0, cols*kColStride)           tile region: word (col, slot, lane) at col*4096 + slot*128 + lane*4
-//                                  -- all 32 warp buffers interleaved, so the region base is one
-//                                  CTA-uniform constant and a lane's address is a pure bit-field OR
-//   [.., + trees_per_chunk*W*4)    the resident chunk of rank-quantised trees
-//   [.., + (1 + kSlots)*8)         mbarriers: chunk, then one per tile buffer
-
-// One group of G trees for this lane's sample, on absolute shared-memory addresses.
-//   tree_abs   shared address of word 0 of the group's first tree (warp-uniform)
-//   s_base     shared address of smem[0] = base of the tile region (CTA-uniform)
-//   slot_lane  slot*128 + lane*4 : this lane's bank inside this warp's current tile buffer
-// a[g] is the shared ADDRESS of the current node, so one visit is six instructions:
-//   LDS  node  [a]
-//   LOP3 (node & col_mask) | slot_lane           (WIDE; the compact form adds one shift)
-//   LDS  rank  [that + s_base]                   (uniform-register base, folded into the LDS)
-//   ISETP rank > node ; SEL k = right ? 4-B : -B ; IADD3 a = a + a + k      (B = tree address)
-// i.e. a' - B = 2(a - B) + 4*right, the heap step on byte offsets, with no separate address add.
-// Loads are asm so the address arithmetic stays exactly this; ptxas still interleaves the G chains.
-template <int DEPTH, int G, bool MISSING, bool WIDE>
-__device__ __forceinline__ void traverse_group(uint32_t tree_abs, uint32_t s_base, uint32_t slot_lane,
-                                               uint32_t col_mask, uint32_t miss_code, uint32_t (&a)[G]) {
-  constexpr uint32_t W4 = 4u << (DEPTH + 1);  // bytes per tree
-  uint32_t k0[G];
-#pragma unroll
-  for (int g = 0; g < G; ++g) {
-    k0[g] = 0u - (tree_abs + g * W4);
-    a[g] = tree_abs + g * W4 + 4;
-  }
-#pragma unroll
-  for (int l = 0; l < DEPTH; ++l) {
-    uint32_t N[G], F[G];
-#pragma unroll
-    for (int g = 0; g < G; ++g) N[g] = lds_u32(a[g]);
-#pragma unroll
-    for (int g = 0; g < G; ++g) {
-      const uint32_t col_off = WIDE ? (N[g] & col_mask)
-                                    : ((N[g] & col_mask) << (kQuantColShiftWide - kQuantColShift));
-      F[g] = lds_u32(s_base + (col_off | slot_lane));
-    }
-#pragma unroll
-    for (int g = 0; g < G; ++g) {
-      bool c = F[g] > N[g];
-      if (MISSING) {
-        if (F[g] == miss_code) c = !(N[g] & 1u);  // sentinel: !def_left (BaseTahoeTest.h:452)
-      }
-      a[g] = a[g] + a[g] + (c ? k0[g] + 4u : k0[g]);
-    }
-  }
-}
-
-template <int DEPTH, int G, bool LEAF_IDS, bool WIDE>
-__global__ void __launch_bounds__(kSmemThreads, 1) k_smem_forest(SmemParams p) {
-  extern __shared__ __align__(128) uint8_t smem[];
-  constexpr uint32_t W = 1u << (DEPTH + 1);      // words per tree
-  constexpr uint32_t L = 1u << DEPTH;            // bottom slots per tree
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t tile_bytes = (uint32_t)p.cols * 128u;
-  const uint32_t forest_off = (uint32_t)p.cols * kColStride;
-  const uint32_t bars_off = forest_off + (uint32_t)p.trees_per_chunk * W * 4u;
-  const uint32_t s_base = smem_u32(smem);
-  const uint32_t bar_chunk = s_base + bars_off;
-  const uint32_t bar_tile0 = bar_chunk + 8 + warp * (8 * kSmemTileBufs);
-
-  if (threadIdx.x == 0) {
-    mbar_init(bar_chunk, 1);
-    for (int i = 0; i < kSlots; ++i) mbar_init(bar_chunk + 8 + i * 8, 1);
-    fence_mbar_init();
-  }
-  __syncthreads();
-
-  const size_t warp_global = (size_t)blockIdx.x * kSmemWarps + warp;
-  const size_t warp_stride = (size_t)gridDim.x * kSmemWarps;
-  uint32_t tile_phase = 0;   // bit b = parity to wait for on this warp's buffer b
-  uint32_t chunk_phase = 0;
-
-  // bring tile `tile` into this warp's buffer `b`: one 128-byte bulk copy per column row
-  auto load_tile = [&](size_t tile, int b) {
-    const uint32_t bar = bar_tile0 + b * 8;
-    if (lane == 0) mbar_expect_tx(bar, tile_bytes);
-    __syncwarp();
-    const uint32_t slot_off = (uint32_t)(warp * kSmemTileBufs + b) * 128u;
-    const uint32_t* src = p.qtiles + tile * (size_t)p.cols * 32;
-    for (int c = lane; c < p.cols; c += 32) {
-      fence_proxy_async();
-      bulk_g2s(s_base + c * kColStride + slot_off, src + c * 32, 128u, bar);
-    }
-  };
-
-  for (int chunk = 0; chunk < p.num_chunks; ++chunk) {
-    const int tree0 = chunk * p.trees_per_chunk;
-    const int ntrees = min(p.trees_per_chunk, p.padded_trees - tree0);   // a multiple of G
-    // ---- stage this chunk of trees (everyone is done reading the previous one)
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      fence_proxy_async();
-      const uint32_t bytes = (uint32_t)ntrees * W * 4u;
-      mbar_expect_tx(bar_chunk, bytes);
-      const uint8_t* src = (const uint8_t*)(p.qwords + (size_t)tree0 * W);
-      uint32_t done = 0;
-      while (done < bytes) {               // pieces of <= 64 KB
-        const uint32_t piece = min(bytes - done, 65536u);
-        bulk_g2s(s_base + forest_off + done, src + done, piece, bar_chunk);
-        done += piece;
-      }
-    }
-    // the first tile of this pass flies while the chunk lands
-    size_t tile = warp_global;
-    if (tile < p.num_tiles) load_tile(tile, 0);
-    mbar_wait(bar_chunk, chunk_phase);
-    chunk_phase ^= 1;
-
-    const bool first = (chunk == 0), last = (chunk == p.num_chunks - 1);
-    int buf = 0;
-    // the tile's missing flag and this lane's partial sum are fetched one tile ahead, so that their
-    // global-memory latency hides behind the traversal of the tile before
-    uint32_t flag_next = 0;
-    float acc_next = 0.0f;
-    if (tile < p.num_tiles) {
-      flag_next = __ldg(p.tile_flags + tile);
-      const size_t r0 = tile * 32 + lane;
-      if (!first && r0 < p.rows) acc_next = p.preds[r0];
-    }
-    for (; tile < p.num_tiles; tile += warp_stride) {
-      // prefetch the next tile into the other buffer (all lanes finished reading it)
-      const size_t next = tile + warp_stride;
-      __syncwarp();
-      const bool has_missing = flag_next != 0;
-      float acc = acc_next;
-      if (next < p.num_tiles) {
-        load_tile(next, buf ^ 1);
-        flag_next = __ldg(p.tile_flags + next);
-        const size_t rn = next * 32 + lane;
-        acc_next = (!first && rn < p.rows) ? p.preds[rn] : 0.0f;
-      }
-      mbar_wait(bar_tile0 + buf * 8, (tile_phase >> buf) & 1u);
-      tile_phase ^= 1u << buf;
-
-      const size_t row = tile * 32 + lane;
-      const bool live = row < p.rows;
-      const uint32_t slot_lane = (uint32_t)(warp * kSmemTileBufs + buf) * 128u + lane * 4u;
-
-      for (int t = 0; t < ntrees; t += G) {
-        uint32_t a[G];
-        const uint32_t tree_abs = s_base + forest_off + (uint32_t)t * W * 4u;
-        if (has_missing) traverse_group<DEPTH, G, true, WIDE>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a);
-        else traverse_group<DEPTH, G, false, WIDE>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a);
-#pragma unroll
-        for (int g = 0; g < G; ++g) {
-          acc += __uint_as_float(lds_u32(a[g]));   // a padding tree adds +0.0f: the sum keeps its bits
-          if (LEAF_IDS && live && tree0 + t + g < p.num_trees)
-            p.leaf_ids[row * (size_t)p.num_trees + tree0 + t + g] =
-                __ldg(p.leaf_origin + (size_t)(tree0 + t + g) * L + ((a[g] - tree_abs - g * W * 4u) / 4 - L));
-        }
-      }
-      if (live) p.preds[row] = last ? apply_transform(acc, p.tf) : acc;
-      buf ^= 1;
-    }
-  }
-}
 
 // ---------------------------------------------------------------------------------------------
 int ensure_workspace(tahoe_forest* f, Workspace* ws, size_t rows) {
@@ -315,21 +132,13 @@ int ensure_workspace(tahoe_forest* f, Workspace* ws, size_t rows) {
   return TAHOE_OK;
 }
 
-template <int DEPTH>
-static int launch_depth(tahoe_forest* f, const SmemParams& p, unsigned grid, cudaStream_t stream) {
-  auto go = [&](auto kern) -> int {
-    TAHOE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->smem_bytes));
-    kern<<<grid, kSmemThreads, f->smem_bytes, stream>>>(p);
-    TAHOE_CUDA(cudaGetLastError());
-    return TAHOE_OK;
-  };
-  const bool wide = f->col_shift == kQuantColShiftWide;
-  // the leaf-id instantiation is the checking path: one tree at a time keeps the build small
-  if (p.leaf_ids) return wide ? go(k_smem_forest<DEPTH, 1, true, true>) : go(k_smem_forest<DEPTH, 1, true, false>);
-  if (f->group == kGroup) return wide ? go(k_smem_forest<DEPTH, kGroup, false, true>) : go(k_smem_forest<DEPTH, kGroup, false, false>);
-  if (f->group >= 2) return wide ? go(k_smem_forest<DEPTH, 2, false, true>) : go(k_smem_forest<DEPTH, 2, false, false>);
-  return wide ? go(k_smem_forest<DEPTH, 1, false, true>) : go(k_smem_forest<DEPTH, 1, false, false>);
-}
+// one translation unit per depth (kernels_smem_depth.cu)
+#define TAHOE_DEPTH_DECL(D) \
+  int launch_smem_depth_##D(tahoe_forest* f, const SmemParams& p, unsigned grid, cudaStream_t stream);
+TAHOE_DEPTH_DECL(1) TAHOE_DEPTH_DECL(2) TAHOE_DEPTH_DECL(3) TAHOE_DEPTH_DECL(4) TAHOE_DEPTH_DECL(5)
+TAHOE_DEPTH_DECL(6) TAHOE_DEPTH_DECL(7) TAHOE_DEPTH_DECL(8) TAHOE_DEPTH_DECL(9) TAHOE_DEPTH_DECL(10)
+TAHOE_DEPTH_DECL(11) TAHOE_DEPTH_DECL(12) TAHOE_DEPTH_DECL(13) TAHOE_DEPTH_DECL(14)
+#undef TAHOE_DEPTH_DECL
 
 int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   if (!f->quant || f->trees_per_chunk < 1) {
@@ -374,14 +183,17 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.cols = f->params.num_cols; p.qwords = f->d_qwords; p.num_trees = f->params.num_trees;
   p.padded_trees = f->qwords_trees;
   p.trees_per_chunk = f->trees_per_chunk; p.num_chunks = f->num_chunks;
-  p.col_mask = f->col_mask; p.miss_code = f->miss_code; p.preds = a.preds; p.leaf_ids = a.leaf_ids;
+  p.col_mask = f->col_mask; p.miss_code = f->miss_code;
+  p.col_stride = 128u * (uint32_t)f->slots;
+  p.col_lshift = ilog2_c(f->slots);
+  p.preds = a.preds; p.leaf_ids = a.leaf_ids;
   p.leaf_origin = f->d_leaf_origin;
   p.tf = Transform{f->params.output, (float)f->params.num_trees, f->params.threshold,
                    f->params.global_bias};
   const unsigned grid = (unsigned)std::min<size_t>((size_t)f->sm_count,
-                                                   (tiles + kSmemWarps - 1) / kSmemWarps);
+                                                   (tiles + f->warps - 1) / f->warps);
   switch (f->depth) {
-#define TAHOE_DEPTH_CASE(D) case D: rc = launch_depth<D>(f, p, grid, a.stream); break;
+#define TAHOE_DEPTH_CASE(D) case D: rc = launch_smem_depth_##D(f, p, grid, a.stream); break;
     TAHOE_DEPTH_CASE(1) TAHOE_DEPTH_CASE(2) TAHOE_DEPTH_CASE(3) TAHOE_DEPTH_CASE(4)
     TAHOE_DEPTH_CASE(5) TAHOE_DEPTH_CASE(6) TAHOE_DEPTH_CASE(7) TAHOE_DEPTH_CASE(8)
     TAHOE_DEPTH_CASE(9) TAHOE_DEPTH_CASE(10) TAHOE_DEPTH_CASE(11) TAHOE_DEPTH_CASE(12)

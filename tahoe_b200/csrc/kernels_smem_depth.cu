@@ -1,0 +1,52 @@
+// kernels_smem_depth.cu -- the instantiations of k_smem_forest for ONE tree depth.
+// Compiled 14 times (-DTAHOE_DEPTH=1..14, tahoe_b200/build.py) so the builds run in parallel; each
+// object exports launch_smem_depth_<N>(), which picks the instantiation the handle's plan names:
+// trees per group (1..6), wide/compact column field, TMA double-buffered or register-staged tiles.
+#include "kernels_smem_traverse.cuh"
+
+#ifndef TAHOE_DEPTH
+#error "compile with -DTAHOE_DEPTH=<1..14>"
+#endif
+#define TAHOE_CAT2(a, b) a##b
+#define TAHOE_CAT(a, b) TAHOE_CAT2(a, b)
+
+namespace tahoe {
+
+int TAHOE_CAT(launch_smem_depth_, TAHOE_DEPTH)(tahoe_forest* f, const SmemParams& p, unsigned grid,
+                                              cudaStream_t stream) {
+  constexpr int D = TAHOE_DEPTH;
+  auto go = [&](auto kern) -> int {
+    TAHOE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->smem_bytes));
+    kern<<<grid, (unsigned)f->warps * 32u, f->smem_bytes, stream>>>(p);
+    TAHOE_CUDA(cudaGetLastError());
+    return TAHOE_OK;
+  };
+  const bool wide = f->col_shift != kQuantColShift;
+  const int sel = (wide ? 1 : 0) | (f->staged ? 2 : 0);
+  // the leaf-id instantiation is the checking path: one tree at a time keeps the build small
+  if (p.leaf_ids) {
+    switch (sel) {
+      case 0: return go(k_smem_forest<D, 1, true, false, false>);
+      case 1: return go(k_smem_forest<D, 1, true, true, false>);
+      case 2: return go(k_smem_forest<D, 1, true, false, true>);
+      default: return go(k_smem_forest<D, 1, true, true, true>);
+    }
+  }
+#define TAHOE_G_CASE(G)                                                   \
+  case G:                                                                 \
+    switch (sel) {                                                        \
+      case 0: return go(k_smem_forest<D, G, false, false, false>);        \
+      case 1: return go(k_smem_forest<D, G, false, true, false>);         \
+      case 2: return go(k_smem_forest<D, G, false, false, true>);         \
+      default: return go(k_smem_forest<D, G, false, true, true>);         \
+    }
+  switch (f->group) {
+    TAHOE_G_CASE(1) TAHOE_G_CASE(2) TAHOE_G_CASE(3) TAHOE_G_CASE(4) TAHOE_G_CASE(5) TAHOE_G_CASE(6)
+    default: break;
+  }
+#undef TAHOE_G_CASE
+  set_error("unsupported traversal group size");
+  return TAHOE_ERR_INVALID;
+}
+
+}  // namespace tahoe

@@ -1,0 +1,225 @@
+// kernels_smem_traverse.cuh -- k_smem_forest: SHARED_FOREST / SPLIT_SHARED_FOREST traversal
+// (reference K4/K5, Struct.h:1245-1409 and 1414-1606).  Included by kernels_smem_depth.cu, which is
+// compiled once per tree depth (-DTAHOE_DEPTH=N) so that the 14 x 28 instantiations build in parallel.
+#pragma once
+#include "device_utils.cuh"
+#include "forest.h"
+
+namespace tahoe {
+
+// ---------------------------------------------------------------------------------------------
+struct SmemParams {
+  const uint32_t* qtiles;
+  const uint32_t* tile_flags;
+  size_t num_tiles;
+  size_t rows;
+  int cols;
+  const uint32_t* qwords;   // [padded_trees][2^(d+1)]
+  int num_trees;            // real trees (leaf ids are written for these only)
+  int padded_trees;         // trees in qwords: whole traversal groups, the extra ones all zero
+  int trees_per_chunk, num_chunks;
+  uint32_t col_mask, miss_code;
+  uint32_t col_stride;      // bytes between column rows of the tile region = 128 * tile slots
+  int col_lshift;           // compact node form: (node & col_mask) << col_lshift = column row offset
+  float* preds;
+  int32_t* leaf_ids;
+  const int32_t* leaf_origin;  // [T][2^d]
+  Transform tf;
+};
+
+constexpr int kSmemMaxThreads = kSmemMaxWarps * 32;
+
+// Shared-memory map of k_smem_forest (byte offsets from smem[]):
+//   [0, cols*col_stride)           tile region: word (col, slot, lane) at col*col_stride + slot*128 + lane*4
+//                                  -- all warp buffers of a column interleaved, so the region base is
+//                                  one CTA-uniform constant and a lane's address is a pure bit-field OR
+//   [.., + trees_per_chunk*W*4)    the resident chunk of rank-quantised trees
+//   [.., + (1 + slots)*8)          mbarriers: chunk, then one per tile buffer
+// slots = warps * 2 (tiles double-buffered by TMA bulk copies) or warps * 1 (STAGED: the next tile
+// waits in registers while the current one is traversed -- half the tile memory, so deep trees get
+// more of them per chunk).
+
+// One group of G trees for this lane's sample, on absolute shared-memory addresses.
+//   tree_abs   shared address of word 0 of the group's first tree (warp-uniform)
+//   s_base     shared address of smem[0] = base of the tile region (CTA-uniform)
+//   slot_lane  slot*128 + lane*4 : this lane's bank inside this warp's current tile buffer
+// a[g] is the shared ADDRESS of the current node, so one visit is six instructions:
+//   LDS  node  [a]
+//   LOP3 (node & col_mask) | slot_lane           (WIDE; the compact form adds one shift)
+//   LDS  rank  [that + s_base]                   (uniform-register base, folded into the LDS)
+//   ISETP rank > node ; SEL k = right ? 4-B : -B ; IADD3 a = a + a + k      (B = tree address)
+// i.e. a' - B = 2(a - B) + 4*right, the heap step on byte offsets, with no separate address add.
+// Loads are asm so the address arithmetic stays exactly this; ptxas still interleaves the G chains.
+template <int DEPTH, int G, bool MISSING, bool WIDE>
+__device__ __forceinline__ void traverse_group(uint32_t tree_abs, uint32_t s_base, uint32_t slot_lane,
+                                               uint32_t col_mask, int col_lshift, uint32_t miss_code,
+                                               uint32_t (&a)[G]) {
+  constexpr uint32_t W4 = 4u << (DEPTH + 1);  // bytes per tree
+  uint32_t k0[G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    k0[g] = 0u - (tree_abs + g * W4);
+    a[g] = tree_abs + g * W4 + 4;
+  }
+#pragma unroll
+  for (int l = 0; l < DEPTH; ++l) {
+    uint32_t N[G], F[G];
+#pragma unroll
+    for (int g = 0; g < G; ++g) N[g] = lds_u32(a[g]);
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const uint32_t col_off = WIDE ? (N[g] & col_mask) : ((N[g] & col_mask) << col_lshift);
+      F[g] = lds_u32(s_base + (col_off | slot_lane));
+    }
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      bool c = F[g] > N[g];
+      if (MISSING) {
+        if (F[g] == miss_code) c = !(N[g] & 1u);  // sentinel: !def_left (BaseTahoeTest.h:452)
+      }
+      a[g] = a[g] + a[g] + (c ? k0[g] + 4u : k0[g]);
+    }
+  }
+}
+
+__device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+template <int DEPTH, int G, bool LEAF_IDS, bool WIDE, bool STAGED>
+__global__ void __launch_bounds__(kSmemMaxThreads, 1) k_smem_forest(SmemParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  constexpr uint32_t W = 1u << (DEPTH + 1);      // words per tree
+  constexpr uint32_t L = 1u << DEPTH;            // bottom slots per tree
+  constexpr int kBufs = STAGED ? 1 : 2;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nwarps = blockDim.x >> 5;
+  const int slots = nwarps * kBufs;
+  const uint32_t tile_bytes = (uint32_t)p.cols * 128u;
+  const uint32_t forest_off = (uint32_t)p.cols * p.col_stride;
+  const uint32_t bars_off = forest_off + (uint32_t)p.trees_per_chunk * W * 4u;
+  const uint32_t s_base = smem_u32(smem);
+  const uint32_t bar_chunk = s_base + bars_off;
+  const uint32_t bar_tile0 = bar_chunk + 8 + warp * (8 * kBufs);
+
+  if (threadIdx.x == 0) {
+    mbar_init(bar_chunk, 1);
+    for (int i = 0; i < slots; ++i) mbar_init(bar_chunk + 8 + i * 8, 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  const size_t warp_global = (size_t)blockIdx.x * nwarps + warp;
+  const size_t warp_stride = (size_t)gridDim.x * nwarps;
+  uint32_t tile_phase = 0;   // bit b = parity to wait for on this warp's buffer b
+  uint32_t chunk_phase = 0;
+
+  // TMA path: bring tile `tile` into this warp's buffer `b`, one 128-byte bulk copy per column row
+  auto load_tile = [&](size_t tile, int b) {
+    const uint32_t bar = bar_tile0 + b * 8;
+    if (lane == 0) mbar_expect_tx(bar, tile_bytes);
+    __syncwarp();
+    const uint32_t slot_off = (uint32_t)(warp * kBufs + b) * 128u;
+    const uint32_t* src = p.qtiles + tile * (size_t)p.cols * 32;
+    for (int c = lane; c < p.cols; c += 32) {
+      fence_proxy_async();
+      bulk_g2s(s_base + c * p.col_stride + slot_off, src + c * 32, 128u, bar);
+    }
+  };
+  // STAGED path: the tile's words for this lane ([col][lane]: one coalesced 128-byte row per column)
+  uint32_t st[STAGED ? kStagedMaxCols : 1];
+  auto fetch_tile = [&](size_t tile) {
+    const uint32_t* src = p.qtiles + tile * (size_t)p.cols * 32 + lane;
+#pragma unroll
+    for (int c = 0; c < (STAGED ? kStagedMaxCols : 0); ++c)
+      if (c < p.cols) st[c] = __ldg(src + c * 32);
+  };
+  auto commit_tile = [&]() {
+    const uint32_t dst = s_base + (uint32_t)warp * 128u + lane * 4u;
+#pragma unroll
+    for (int c = 0; c < (STAGED ? kStagedMaxCols : 0); ++c)
+      if (c < p.cols) sts_u32(dst + c * p.col_stride, st[c]);
+  };
+
+  for (int chunk = 0; chunk < p.num_chunks; ++chunk) {
+    const int tree0 = chunk * p.trees_per_chunk;
+    const int ntrees = min(p.trees_per_chunk, p.padded_trees - tree0);   // a multiple of G
+    // ---- stage this chunk of trees (everyone is done reading the previous one)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      fence_proxy_async();
+      const uint32_t bytes = (uint32_t)ntrees * W * 4u;
+      mbar_expect_tx(bar_chunk, bytes);
+      const uint8_t* src = (const uint8_t*)(p.qwords + (size_t)tree0 * W);
+      uint32_t done = 0;
+      while (done < bytes) {               // pieces of <= 64 KB
+        const uint32_t piece = min(bytes - done, 65536u);
+        bulk_g2s(s_base + forest_off + done, src + done, piece, bar_chunk);
+        done += piece;
+      }
+    }
+    // the first tile of this pass flies while the chunk lands
+    size_t tile = warp_global;
+    if (tile < p.num_tiles) {
+      if (STAGED) fetch_tile(tile); else load_tile(tile, 0);
+    }
+    mbar_wait(bar_chunk, chunk_phase);
+    chunk_phase ^= 1;
+
+    const bool first = (chunk == 0), last = (chunk == p.num_chunks - 1);
+    int buf = 0;
+    // the tile's missing flag and this lane's partial sum are fetched one tile ahead, so that their
+    // global-memory latency hides behind the traversal of the tile before
+    uint32_t flag_next = 0;
+    float acc_next = 0.0f;
+    if (tile < p.num_tiles) {
+      flag_next = __ldg(p.tile_flags + tile);
+      const size_t r0 = tile * 32 + lane;
+      if (!first && r0 < p.rows) acc_next = p.preds[r0];
+    }
+    for (; tile < p.num_tiles; tile += warp_stride) {
+      const size_t next = tile + warp_stride;
+      __syncwarp();                          // all lanes finished reading the buffer about to be refilled
+      const bool has_missing = flag_next != 0;
+      float acc = acc_next;
+      if (STAGED) {
+        commit_tile();                       // registers -> this warp's only buffer
+        __syncwarp();
+        if (next < p.num_tiles) fetch_tile(next);   // lands while this tile is traversed
+      } else if (next < p.num_tiles) {
+        load_tile(next, buf ^ 1);
+      }
+      if (next < p.num_tiles) {
+        flag_next = __ldg(p.tile_flags + next);
+        const size_t rn = next * 32 + lane;
+        acc_next = (!first && rn < p.rows) ? p.preds[rn] : 0.0f;
+      }
+      if (!STAGED) {
+        mbar_wait(bar_tile0 + buf * 8, (tile_phase >> buf) & 1u);
+        tile_phase ^= 1u << buf;
+      }
+
+      const size_t row = tile * 32 + lane;
+      const bool live = row < p.rows;
+      const uint32_t slot_lane = (uint32_t)(warp * kBufs + buf) * 128u + lane * 4u;
+
+      for (int t = 0; t < ntrees; t += G) {
+        uint32_t a[G];
+        const uint32_t tree_abs = s_base + forest_off + (uint32_t)t * W * 4u;
+        if (has_missing) traverse_group<DEPTH, G, true, WIDE>(tree_abs, s_base, slot_lane, p.col_mask, p.col_lshift, p.miss_code, a);
+        else traverse_group<DEPTH, G, false, WIDE>(tree_abs, s_base, slot_lane, p.col_mask, p.col_lshift, p.miss_code, a);
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          acc += __uint_as_float(lds_u32(a[g]));   // a padding tree adds +0.0f: the sum keeps its bits
+          if (LEAF_IDS && live && tree0 + t + g < p.num_trees)
+            p.leaf_ids[row * (size_t)p.num_trees + tree0 + t + g] =
+                __ldg(p.leaf_origin + (size_t)(tree0 + t + g) * L + ((a[g] - tree_abs - g * W * 4u) / 4 - L));
+        }
+      }
+      if (live) p.preds[row] = last ? apply_transform(acc, p.tf) : acc;
+      if (!STAGED) buf ^= 1;
+    }
+  }
+}
+
+}  // namespace tahoe

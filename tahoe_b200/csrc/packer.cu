@@ -15,6 +15,8 @@
 //     branch test is one unsigned compare.
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 
@@ -260,9 +262,13 @@ static int build_quant(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
   f->rank_bits = rb;
   f->col_bits = cb;
   f->rank_shift = 32 - rb;
+  f->quant = true;            // plan_chunks needs it; cleared again if no tree fits shared memory
+  plan_chunks(f);
+  if (!f->quant) return TAHOE_OK;   // not even one tree fits beside the sample tiles
   // wide form when it fits: the column field is then already the byte offset of the column
   // row in the shared-memory tile region, saving one instruction per node visit
-  f->col_shift = (rb + cb + kQuantColShiftWide <= 32) ? kQuantColShiftWide : kQuantColShift;
+  const int wide_shift = kQuantColShift + ilog2_c(std::max(f->slots, 1));
+  f->col_shift = (rb + cb + wide_shift <= 32) ? wide_shift : kQuantColShift;
   f->col_mask = ((1u << cb) - 1u) << f->col_shift;
   f->miss_code = ((1u << rb) - 1u) << f->rank_shift;
 
@@ -296,7 +302,6 @@ static int build_quant(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
       }
     }
   }
-  f->quant = true;
   return TAHOE_OK;
 }
 
@@ -349,38 +354,70 @@ int pack_sparse(tahoe_forest* f, const tahoe_sparse_node_t* nodes, const float* 
 // ---- shared-memory chunk plan ------------------------------------------------------------
 // Shared memory of one persistent CTA (227 KB opt-in, vs the reference's 0.8 * 48 KB,
 // Struct.h:215-220): [warp tiles][forest chunk][mbarriers].
+// Relative cost of one node visit for a plan, from B200 measurements on the SUSY-shaped forest
+// (profiles/r01_variants_group_size.log): 16 warps x G=6 is the unit.
+static double visit_cost(int warps, int G, bool staged) {
+  static const double by_group[kMaxGroup + 1] = {0.0, 1.50, 1.25, 1.124, 1.096, 1.056, 1.0};
+  const double by_warps = warps >= 16 ? 1.0 : (warps >= 8 ? 1.45 : 2.4);
+  return by_group[G] * by_warps * (staged ? 1.11 : 1.0);
+}
+
 void plan_chunks(tahoe_forest* f) {
   f->trees_per_chunk = 0;
   f->num_chunks = 0;
   f->smem_bytes = 0;
   f->group = 1;
+  f->slots = 0;
+  f->quant_stride = 1;
+  f->quant_smem = 0;
   f->qwords_trees = f->params.num_trees;
   if (!f->quant) return;
-  const int T = f->params.num_trees;
-  const size_t tile_bytes = (size_t)f->params.num_cols * 128;
-  const size_t tiles = (size_t)kSlots * tile_bytes;
+  const int T = f->params.num_trees, C = f->params.num_cols;
+  const size_t tile_bytes = (size_t)C * 128;
   const size_t bars = 1024;
   const size_t tree_bytes = ((size_t)1 << (f->depth + 1)) * 4;
-  if ((size_t)f->smem_optin < tiles + bars + tree_bytes) { f->quant_stride = 1; f->quant_smem = 0; return; }
-  const size_t avail = (size_t)f->smem_optin - tiles - bars;
-  const int max_tpc = (int)std::min<size_t>(avail / tree_bytes, (size_t)T);
-  // traversal group: kGroup trees in flight per thread when a chunk holds that many, else 2 or 1
-  const int G = kGroup <= max_tpc ? kGroup : (max_tpc >= 2 ? 2 : 1);
-  const int tpad = (T + G - 1) / G * G;            // all-zero trees pad the forest to whole groups
-  int tpc = std::min(max_tpc / G * G, tpad);
-  // balance the chunks: same chunk count, trees spread evenly in whole groups
-  const int chunks = (tpad + tpc - 1) / tpc;
-  tpc = ((tpad + chunks - 1) / chunks + G - 1) / G * G;
-  f->group = G;
-  f->qwords_trees = tpad;
-  f->trees_per_chunk = tpc;
-  f->num_chunks = (tpad + tpc - 1) / tpc;
-  f->smem_bytes = tiles + bars + (size_t)tpc * tree_bytes;
+  int want_warps = 0, want_staged = -1, want_group = 0;   // TAHOE_SMEM_PLAN="warps,staged,group"
+  if (const char* e = std::getenv("TAHOE_SMEM_PLAN")) std::sscanf(e, "%d,%d,%d", &want_warps, &want_staged, &want_group);
+
+  // every (warps, tile buffering, group) that fits; cost per sample = node visits at the plan's
+  // rate + one pass of the sample tiles per chunk (HBM/L2 streaming, mostly hidden: weighted 0.8)
+  double best = 0.0;
+  bool found = false;
+  for (int warps = kSmemMaxWarps; warps >= 4; warps >>= 1) {
+    if (want_warps && warps != want_warps) continue;
+    for (int staged = 0; staged <= 1; ++staged) {
+      if (want_staged >= 0 && staged != want_staged) continue;
+      if (staged && C > kStagedMaxCols) continue;
+      const int slots = warps * (staged ? 1 : 2);
+      const size_t tiles = (size_t)slots * tile_bytes;
+      if ((size_t)f->smem_optin < tiles + bars + tree_bytes) continue;
+      const size_t avail = (size_t)f->smem_optin - tiles - bars;
+      const int max_tpc = (int)std::min<size_t>(avail / tree_bytes, (size_t)T);
+      for (int G = 1; G <= std::min(kMaxGroup, max_tpc); ++G) {
+        if (want_group && G != want_group) continue;
+        const int tpad = (T + G - 1) / G * G;          // all-zero trees pad the forest to whole groups
+        int tpc = std::min(max_tpc / G * G, tpad);
+        const int chunks = (tpad + tpc - 1) / tpc;     // balance: same chunk count, even whole groups
+        tpc = ((tpad + chunks - 1) / chunks + G - 1) / G * G;
+        const double visits = (double)tpad * std::max(f->depth, 1) * 3.3e-13 * visit_cost(warps, G, staged);
+        const double stream = (double)chunks * (double)C * 4.0 / 5.0e12;
+        const double cost = visits + 0.8 * stream;
+        if (!found || cost < best) {
+          found = true; best = cost;
+          f->warps = warps; f->staged = staged != 0; f->slots = slots; f->group = G;
+          f->qwords_trees = tpad; f->trees_per_chunk = tpc;
+          f->num_chunks = (tpad + tpc - 1) / tpc;
+          f->smem_bytes = tiles + bars + (size_t)tpc * tree_bytes;
+        }
+      }
+    }
+  }
+  if (!found) { f->quant = false; return; }
 
   // k_quantize: one column's sorted thresholds (every quant_stride-th of them when the column is
   // too long) + its bucket index live in shared memory
   size_t max_n = 0;
-  for (int c = 0; c < f->params.num_cols; ++c)
+  for (int c = 0; c < C; ++c)
     max_n = std::max<size_t>(max_n, (size_t)(f->host.qoffsets[c + 1] - f->host.qoffsets[c]));
   const size_t lut_bytes = ((size_t)f->host.qbuckets + 1) * 4;
   const size_t budget = (size_t)f->smem_optin - 2048 - lut_bytes;
@@ -388,6 +425,26 @@ void plan_chunks(tahoe_forest* f) {
   while ((max_n / S + 1) * 4 > budget) S <<= 1;
   f->quant_stride = S;
   f->quant_smem = lut_bytes + (max_n / S + 1) * 4 + 16;
+}
+
+int query_device(tahoe_forest* f) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    // No GPU (authoring container): the forest can be packed and inspected, with the plan a B200
+    // would get.  Every predict call on such a handle fails with TAHOE_ERR_CUDA -- no CPU path.
+    cudaGetLastError();
+    f->device = -1;
+    f->sm_count = 148;
+    f->smem_optin = 232448;
+    return TAHOE_OK;
+  }
+  cudaDeviceProp prop;
+  TAHOE_CUDA(cudaGetDevice(&f->device));
+  TAHOE_CUDA(cudaGetDeviceProperties(&prop, f->device));
+  f->sm_count = prop.multiProcessorCount;
+  f->smem_optin = (int)prop.sharedMemPerBlockOptin;
+  f->l2_bytes = prop.l2CacheSize;
+  return TAHOE_OK;
 }
 
 template <typename T>
@@ -400,24 +457,7 @@ static int to_device(T** dst, const std::vector<T>& src) {
 }
 
 int upload(tahoe_forest* f) {
-  int ndev = 0;
-  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
-    // No GPU (authoring container): keep the host-side pack for inspection only.  Every
-    // predict call on such a handle fails with TAHOE_ERR_CUDA -- there is no CPU path.
-    cudaGetLastError();
-    f->device = -1;
-    f->sm_count = 148;
-    f->smem_optin = 232448;
-    plan_chunks(f);
-    return TAHOE_OK;
-  }
-  cudaDeviceProp prop;
-  TAHOE_CUDA(cudaGetDevice(&f->device));
-  TAHOE_CUDA(cudaGetDeviceProperties(&prop, f->device));
-  f->sm_count = prop.multiProcessorCount;
-  f->smem_optin = (int)prop.sharedMemPerBlockOptin;
-  f->l2_bytes = prop.l2CacheSize;
-  plan_chunks(f);
+  if (f->device < 0) return TAHOE_OK;   // GPU-less host: host-side pack only
   HostPack& h = f->host;
   int rc;
   if ((rc = to_device(&f->d_heap, h.heap))) return rc;

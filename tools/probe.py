@@ -10,10 +10,14 @@ def main():
     rows = int(sys.argv[2]) if len(sys.argv) > 2 else c["rows"]
     only = [int(x) for x in sys.argv[3].split(",")] if len(sys.argv) > 3 else api.ALL_STRATEGIES
     t0 = time.time()
-    nodes = synth.gen_dense_forest(synth.FOREST_SEED[cfg], c["trees"], c["depth"], c["cols"])
-    f = api.Forest.from_dense(nodes, c["trees"], c["depth"], c["cols"], missing=-999.0)
+    if c["sparse"]:
+        sp, offs, w, lv = synth.gen_sparse_forest(synth.FOREST_SEED[cfg], c["trees"], c["depth"], c["cols"])
+        f = api.Forest.from_sparse(sp, offs, c["cols"], weights=w, missing=-999.0)
+    else:
+        nodes = synth.gen_dense_forest(synth.FOREST_SEED[cfg], c["trees"], c["depth"], c["cols"])
+        f = api.Forest.from_dense(nodes, c["trees"], c["depth"], c["cols"], missing=-999.0)
     inf = f.info()
-    print(f"{cfg}: pack {time.time()-t0:.1f}s chunks={inf.num_chunks} tpc={inf.trees_per_chunk} rank_bits={inf.rank_bits} quant={inf.quantized}", flush=True)
+    print(f"{cfg}: pack {time.time()-t0:.1f}s nodes={inf.num_nodes} mean_depth={inf.mean_depth:.2f} chunks={inf.num_chunks} tpc={inf.trees_per_chunk} rank_bits={inf.rank_bits} quant={inf.quantized} col_shift={inf.col_shift}", flush=True)
     d = api.gen_data_device(synth.DATA_SEED[cfg], rows, c["cols"])
     p = torch.empty(rows, dtype=torch.float32, device="cuda")
     ref = None
