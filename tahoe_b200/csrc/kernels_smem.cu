@@ -16,6 +16,9 @@
 //                  Partial sums are carried in preds[] between chunks by the same thread,
 //                  in tree order, so the float sum is the CPU's sum bit for bit -- no
 //                  [rows x blocks] temp and no segmented reduce.
+#include <algorithm>
+#include <cstdlib>
+
 #include "kernels_smem_traverse.cuh"   // SmemParams; the kernel itself is instantiated per depth
 
 namespace tahoe {
@@ -190,20 +193,39 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.leaf_origin = f->d_leaf_origin;
   p.tf = Transform{f->params.output, (float)f->params.num_trees, f->params.threshold,
                    f->params.global_bias};
-  const unsigned grid = (unsigned)std::min<size_t>((size_t)f->sm_count,
-                                                   (tiles + f->warps - 1) / f->warps);
-  switch (f->depth) {
-#define TAHOE_DEPTH_CASE(D) case D: rc = launch_smem_depth_##D(f, p, grid, a.stream); break;
-    TAHOE_DEPTH_CASE(1) TAHOE_DEPTH_CASE(2) TAHOE_DEPTH_CASE(3) TAHOE_DEPTH_CASE(4)
-    TAHOE_DEPTH_CASE(5) TAHOE_DEPTH_CASE(6) TAHOE_DEPTH_CASE(7) TAHOE_DEPTH_CASE(8)
-    TAHOE_DEPTH_CASE(9) TAHOE_DEPTH_CASE(10) TAHOE_DEPTH_CASE(11) TAHOE_DEPTH_CASE(12)
-    TAHOE_DEPTH_CASE(13) TAHOE_DEPTH_CASE(14)
+  // Row batches (tuning knob, off by default): walk the rows in batches whose rank tiles stay
+  // L2-resident between chunk passes.  Measured on B200 (profiles/r01_row_batch.log): never a win --
+  // the tile stream hides behind the traversal, and every batch pays a pipeline fill and drain.
+  size_t batch_tiles = tiles;
+  if (const char* e = std::getenv("TAHOE_ROW_BATCH_BYTES")) {
+    const size_t budget = (size_t)std::atoll(e);
+    const size_t wave = (size_t)f->sm_count * f->warps;
+    const size_t fit = budget / ((size_t)p.cols * 128);
+    if (budget && f->num_chunks > 1 && fit < tiles) batch_tiles = std::max<size_t>(wave, fit / wave * wave);
+  }
+  for (size_t t0 = 0; t0 < tiles && rc == TAHOE_OK; t0 += batch_tiles) {
+    SmemParams b = p;
+    b.num_tiles = std::min(batch_tiles, tiles - t0);
+    b.rows = std::min(a.rows - t0 * 32, b.num_tiles * 32);
+    b.qtiles = p.qtiles + t0 * (size_t)p.cols * 32;
+    b.tile_flags = p.tile_flags + t0;
+    b.preds = p.preds + t0 * 32;
+    if (p.leaf_ids) b.leaf_ids = p.leaf_ids + t0 * 32 * (size_t)p.num_trees;
+    const unsigned grid = (unsigned)std::min<size_t>((size_t)f->sm_count,
+                                                     (b.num_tiles + f->warps - 1) / f->warps);
+    switch (f->depth) {
+#define TAHOE_DEPTH_CASE(D) case D: rc = launch_smem_depth_##D(f, b, grid, a.stream); break;
+      TAHOE_DEPTH_CASE(1) TAHOE_DEPTH_CASE(2) TAHOE_DEPTH_CASE(3) TAHOE_DEPTH_CASE(4)
+      TAHOE_DEPTH_CASE(5) TAHOE_DEPTH_CASE(6) TAHOE_DEPTH_CASE(7) TAHOE_DEPTH_CASE(8)
+      TAHOE_DEPTH_CASE(9) TAHOE_DEPTH_CASE(10) TAHOE_DEPTH_CASE(11) TAHOE_DEPTH_CASE(12)
+      TAHOE_DEPTH_CASE(13) TAHOE_DEPTH_CASE(14)
 #undef TAHOE_DEPTH_CASE
-    default: set_error("unsupported depth"); return TAHOE_ERR_NOT_APPLICABLE;
+      default: set_error("unsupported depth"); return TAHOE_ERR_NOT_APPLICABLE;
+    }
+    ++*launches;
   }
   if (rc) return rc;
   if (ev) TAHOE_CUDA(cudaEventRecord(ev[2], a.stream));
-  ++*launches;
   return TAHOE_OK;
 }
 
