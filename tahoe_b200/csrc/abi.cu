@@ -36,7 +36,7 @@ static int applicable(const tahoe_forest* f, int strategy, size_t rows) {
     case TAHOE_STRATEGY_SHARED_DATA_PER_THREAD:
       return (size_t)f->params.num_cols * 256 * 4 <= (size_t)f->smem_optin ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
     case TAHOE_STRATEGY_SHARED_DATA:
-      return (!f->sparse && f->d_inter && (size_t)f->params.num_cols * 4 <= (size_t)f->smem_optin)
+      return (!f->sparse && f->d_inter && 2 * (((size_t)f->params.num_cols * 4 + 15) & ~(size_t)15) + 208 <= (size_t)f->smem_optin)
                  ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
     case TAHOE_STRATEGY_SHARED_FOREST:   // whole forest resident (BaseTahoeTest.h:657-668)
       return whole_forest_fits(f) ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;

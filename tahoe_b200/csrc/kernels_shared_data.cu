@@ -9,6 +9,8 @@
 // reduction per row.  No block barrier in the row loop, no idle lanes when T < 256.
 // This is the strategy for wide rows (SVHN-like: a 12 KB row is read once, coalesced)
 // and for small batches, where trees are the only parallelism.
+#include <cstdlib>
+
 #include "device_utils.cuh"
 #include "forest.h"
 
@@ -28,41 +30,72 @@ struct SharedDataParams {
   float* preds;
   int32_t* leaf_ids;
   Transform tf;
-  int warps_per_block;
+  int teams_per_block;       // a team = team_warps warps sharing one row (two row buffers)
+  int team_warps;            // 1, 2 or 4
+  int top_levels;            // levels 0..top_levels-1 of the interleaved forest are copied to shared memory
+  uint32_t top_off;          // byte offset of that copy ([2^top_levels - 1][tpad] uint2)
 };
 
-constexpr int kSdGroup = 4;   // tree slots walked together by one lane (ILP over the L2 latency)
 
-// One row, all of this lane's tree slots, kSdGroup at a time.  Returns the lane's partial sum
-// (double: lane = tree changes the summation order, so the sum is kept within half an ulp of exact).
-__device__ __forceinline__ double sd_walk_row(const SharedDataParams& p, const float* my, size_t row, int lane) {
+__device__ __forceinline__ void team_barrier(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
+// One row, this warp's share of the tree slots (slot groups wt, wt + team_warps, ...), G at a time
+// (G = tree slots walked together by one lane: ILP over the L2 latency).  Returns the warp's partial sum (double: lane = tree changes the summation order, so the
+// sum is kept within half an ulp of exact).  The level step is branch-free -- a walk that has
+// reached its leaf re-reads that leaf -- so the kSdGroup dependent chains (L2 gather -> feature ->
+// compare -> next index) interleave in one warp.
+template <int kSdGroup>
+__device__ __forceinline__ double sd_walk_row(const SharedDataParams& p, const uint2* s_top, const float* my,
+                                              size_t row, int lane, int wt) {
   double acc = 0.0;
-  for (int s0 = lane; s0 < p.tpad; s0 += 32 * kSdGroup) {
+  const int gstride = 32 * p.team_warps;
+  for (int s0 = lane + 32 * wt; s0 < p.tpad; s0 += gstride * kSdGroup) {
     uint32_t n[kSdGroup];
     uint2 e[kSdGroup];
+    const uint2* col[kSdGroup];
+    const uint2* top[kSdGroup];
 #pragma unroll
     for (int g = 0; g < kSdGroup; ++g) {
-      const int slot = s0 + 32 * g;
+      const int slot = min(s0 + gstride * g, p.tpad - 1);   // past the end: repeat the last slot, drop its sum
+      col[g] = p.inter + slot;
+      top[g] = s_top + slot;
       n[g] = 0;
-      e[g] = slot < p.tpad ? __ldg(p.inter + slot) : make_uint2(0u, kMetaLeaf);
+      e[g] = p.top_levels > 0 ? top[g][0] : __ldg(col[g]);
     }
-    for (int l = 0; l < p.depth; ++l) {      // a leaf stays where it is; depth bounds every path
-      bool any = false;
+    // one level: feature -> compare -> child index (a walk on its leaf stays there)
+    auto step = [&](int g) -> bool {
+      const bool leaf = (e[g].y & kMetaLeaf) != 0;
+      const float v = my[leaf ? 0u : (e[g].y & kMetaFidMask)];
+      bool c = branch_right(v, __uint_as_float(e[g].x), e[g].y & kMetaDefLeft, p.missing);
+      c = c != ((e[g].y & kMetaExchange) != 0);       // Struct.h:980
+      n[g] = leaf ? n[g] : 2 * n[g] + 1 + (c ? 1u : 0u);
+      return !leaf;
+    };
+    // The top levels come from shared memory (bank = slot: conflict-free); once the lanes' paths
+    // have parted, every lane of a global load sits in another sector, and each of those L2 round
+    // trips costs ~800 cycles of a dependent chain -- so only the last levels pay it.
+    int l = 0;
+    for (; l < min(p.depth, p.top_levels - 1); ++l) {
 #pragma unroll
       for (int g = 0; g < kSdGroup; ++g) {
-        if (e[g].y & kMetaLeaf) continue;
-        const float v = my[e[g].y & kMetaFidMask];
-        bool c = branch_right(v, __uint_as_float(e[g].x), e[g].y & kMetaDefLeft, p.missing);
-        if (e[g].y & kMetaExchange) c = !c;   // Struct.h:980
-        n[g] = 2 * n[g] + 1 + (c ? 1u : 0u);
-        e[g] = __ldg(p.inter + (size_t)n[g] * p.tpad + (s0 + 32 * g));
-        any = true;
+        step(g);
+        e[g] = top[g][(size_t)n[g] * p.tpad];
       }
-      if (!__any_sync(0xffffffffu, any)) break;
+    }
+    for (; l < p.depth; ++l) {
+      bool live = false;
+#pragma unroll
+      for (int g = 0; g < kSdGroup; ++g) {
+        live |= step(g);
+        e[g] = __ldg(col[g] + (size_t)n[g] * p.tpad);
+      }
+      if (!__any_sync(0xffffffffu, live)) break;   // every walk of the warp already sat on a leaf
     }
 #pragma unroll
     for (int g = 0; g < kSdGroup; ++g) {
-      const int slot = s0 + 32 * g;
+      const int slot = s0 + gstride * g;
       if (slot >= p.tpad) continue;
       acc += (double)__uint_as_float(e[g].x);   // padding slots are leaves holding 0.0f
       if (p.leaf_ids) {
@@ -76,67 +109,107 @@ __device__ __forceinline__ double sd_walk_row(const SharedDataParams& p, const f
   return acc;
 }
 
-// TMA = true : each warp owns two row buffers; rows arrive by one bulk copy each (cp.async.bulk,
-//              row bytes a multiple of 16) completing on the buffer's mbarrier, so the next row
-//              streams in from HBM while the current one is traversed.
-// TMA = false: the warp copies its row with coalesced loads (any width / alignment).
-template <bool TMA>
-__global__ void k_shared_data(SharedDataParams p) {
+// Shared-memory map: [teams][2][row_stride floats] row buffers | [teams][2][4] double partials |
+// [teams][2] mbarriers (TMA only).
+// TMA = true : rows arrive by bulk copies (cp.async.bulk, row bytes a multiple of 16) completing on
+//              the buffer's mbarrier: the next row streams in from HBM while the current one is walked.
+// TMA = false: the team copies its row with coalesced loads (any width / alignment).
+template <bool TMA, int G>
+__global__ void __launch_bounds__(1024, 1) k_shared_data(SharedDataParams p) {
   extern __shared__ __align__(128) uint8_t sd_smem[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const size_t warp_global = (size_t)blockIdx.x * p.warps_per_block + warp;
-  const size_t stride = (size_t)gridDim.x * p.warps_per_block;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int team = warp / p.team_warps, wt = warp % p.team_warps;
+  const int team_threads = 32 * p.team_warps;
+  const uint32_t row_stride = ((uint32_t)p.cols * 4u + 15u) & ~15u;       // bytes, 16-aligned buffers
+  float* buf0 = reinterpret_cast<float*>(sd_smem + (size_t)team * 2 * row_stride);
+  double* partials = reinterpret_cast<double*>(sd_smem + (size_t)p.teams_per_block * 2 * row_stride) + team * 8;
+  const uint32_t bar0 = smem_u32(sd_smem) + (uint32_t)p.teams_per_block * (2 * row_stride + 64) + team * 16u;
+  const size_t team_global = (size_t)blockIdx.x * p.teams_per_block + team;
+  const size_t stride = (size_t)gridDim.x * p.teams_per_block;
+  const uint32_t row_bytes = (uint32_t)p.cols * 4u;
+
+  if (TMA && wt == 0 && lane == 0) { mbar_init(bar0, 1); mbar_init(bar0 + 8, 1); fence_mbar_init(); }
+  const uint2* s_top = reinterpret_cast<const uint2*>(sd_smem + p.top_off);
+  {
+    uint2* dst = reinterpret_cast<uint2*>(sd_smem + p.top_off);
+    const int n_top = p.top_levels > 0 ? ((1 << p.top_levels) - 1) * p.tpad : 0;
+    for (int i = threadIdx.x; i < n_top; i += blockDim.x) dst[i] = __ldg(p.inter + i);
+  }
+  __syncthreads();
+
+  auto load_row_tma = [&](size_t row, int b) {       // team warp 0, lane 0
+    fence_proxy_async();
+    mbar_expect_tx(bar0 + b * 8, row_bytes);
+    const uint8_t* src = reinterpret_cast<const uint8_t*>(p.data + row * (size_t)p.cols);
+    uint32_t done = 0;
+    while (done < row_bytes) {                       // pieces of <= 64 KB
+      const uint32_t piece = min(row_bytes - done, 65536u);
+      bulk_g2s(smem_u32(buf0) + b * row_stride + done, src + done, piece, bar0 + b * 8);
+      done += piece;
+    }
+  };
+  // LSU path: short rows wait in registers (one tile ahead) and are stored when their turn comes;
+  // rows too long for that are copied synchronously
+  constexpr int kStage = 4;
+  const int t = wt * 32 + lane;
+  const bool staged = p.cols <= kStage * team_threads;
+  float stg[kStage];
+  auto fetch_row = [&](size_t row) {
+    const float* g = p.data + row * (size_t)p.cols;
+#pragma unroll
+    for (int k = 0; k < kStage; ++k) {
+      const int i = t + k * team_threads;
+      if (i < p.cols) stg[k] = __ldg(g + i);
+    }
+  };
+  auto commit_row = [&](int b) {
+    float* m = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(buf0) + (size_t)b * row_stride);
+#pragma unroll
+    for (int k = 0; k < kStage; ++k) {
+      const int i = t + k * team_threads;
+      if (i < p.cols) m[i] = stg[k];
+    }
+  };
+  auto copy_row = [&](size_t row, int b) {
+    const float* g = p.data + row * (size_t)p.cols;
+    float* m = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(buf0) + (size_t)b * row_stride);
+    for (int i = t; i < p.cols; i += team_threads) m[i] = __ldg(g + i);
+  };
+
+  uint32_t phase = 0;
+  int b = 0;
+  size_t row = team_global;
   if (TMA) {
-    const uint32_t row_bytes = (uint32_t)p.cols * 4u;
-    const uint32_t s_base = smem_u32(sd_smem);
-    const uint32_t bar0 = s_base + (uint32_t)p.warps_per_block * 2u * row_bytes + warp * 16u;
-    float* buf0 = reinterpret_cast<float*>(sd_smem + (size_t)warp * 2 * row_bytes);
-    if (lane == 0) { mbar_init(bar0, 1); mbar_init(bar0 + 8, 1); fence_mbar_init(); }
-    __syncwarp();
-    auto load_row = [&](size_t row, int b) {
-      if (lane == 0) {
-        fence_proxy_async();
-        mbar_expect_tx(bar0 + b * 8, row_bytes);
-        const uint8_t* src = reinterpret_cast<const uint8_t*>(p.data + row * (size_t)p.cols);
-        uint32_t done = 0;
-        while (done < row_bytes) {             // pieces of <= 64 KB
-          const uint32_t piece = min(row_bytes - done, 65536u);
-          bulk_g2s(smem_u32(buf0) + b * row_bytes + done, src + done, piece, bar0 + b * 8);
-          done += piece;
-        }
-      }
-    };
-    uint32_t phase = 0;
-    int b = 0;
-    size_t row = warp_global;
-    if (row < p.rows) load_row(row, 0);
-    for (; row < p.rows; row += stride) {
-      __syncwarp();                            // everyone finished reading the buffer being refilled
-      if (row + stride < p.rows) load_row(row + stride, b ^ 1);
+    if (row < p.rows && wt == 0 && lane == 0) load_row_tma(row, 0);
+  } else if (row < p.rows && staged) {
+    fetch_row(row);
+  }
+  for (; row < p.rows; row += stride) {
+    const size_t next = row + stride;
+    if (TMA) {
+      // buffer b^1 was last read for the previous row; the team barrier at its end released it
+      if (next < p.rows && wt == 0 && lane == 0) load_row_tma(next, b ^ 1);
       mbar_wait(bar0 + b * 8, (phase >> b) & 1u);
       phase ^= 1u << b;
-      const float* my = buf0 + (size_t)b * p.cols;
-      const double acc = sd_walk_row(p, my, row, lane);
-      if (lane == 0) p.preds[row] = apply_transform((float)acc, p.tf);
-      b ^= 1;
-    }
-  } else {
-    float* my = reinterpret_cast<float*>(sd_smem) + (size_t)warp * p.cols;
-    const bool vec4 = ((p.cols & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.data) & 15) == 0);
-    for (size_t row = warp_global; row < p.rows; row += stride) {
-      const float* g = p.data + row * (size_t)p.cols;
-      __syncwarp();
-      if (vec4) {
-        const float4* g4 = reinterpret_cast<const float4*>(g);
-        float4* m4 = reinterpret_cast<float4*>(my);
-        for (int i = lane; i < (p.cols >> 2); i += 32) m4[i] = __ldg(g4 + i);
+    } else {
+      if (staged) {
+        commit_row(b);
+        if (next < p.rows) fetch_row(next);           // lands while this row is walked
       } else {
-        for (int i = lane; i < p.cols; i += 32) my[i] = __ldg(g + i);
+        copy_row(row, b);
       }
-      __syncwarp();
-      const double acc = sd_walk_row(p, my, row, lane);
-      if (lane == 0) p.preds[row] = apply_transform((float)acc, p.tf);
+      team_barrier(1 + team, team_threads);           // the team's stores of this row are visible
     }
+    const float* my = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(buf0) + (size_t)b * row_stride);
+    const double acc = sd_walk_row<G>(p, s_top, my, row, lane, wt);
+    if (lane == 0) partials[b * 4 + wt] = acc;
+    team_barrier(1 + team, team_threads);
+    if (wt == 0 && lane == 0) {
+      double sum = 0.0;
+      for (int w = 0; w < p.team_warps; ++w) sum += partials[b * 4 + w];   // fixed order: reproducible
+      p.preds[row] = apply_transform((float)sum, p.tf);
+    }
+    b ^= 1;
   }
 }
 
@@ -147,6 +220,7 @@ int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches) {
   }
   if (a.rows == 0) return TAHOE_OK;
   const size_t row_bytes = (size_t)f->params.num_cols * sizeof(float);
+  const size_t row_stride = (row_bytes + 15) & ~(size_t)15;
   SharedDataParams p{};
   p.data = a.data; p.rows = a.rows; p.cols = f->params.num_cols; p.num_trees = f->params.num_trees;
   p.tpad = f->host.tpad; p.depth = f->depth; p.missing = f->params.missing; p.inter = f->d_inter;
@@ -154,33 +228,59 @@ int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.leaf_ids = a.leaf_ids;
   p.tf = Transform{f->params.output, (float)f->params.num_trees, f->params.threshold,
                    f->params.global_bias};
-  // bulk copies need 16-byte rows at 16-byte addresses, and two buffers per warp must fit
-  const bool tma = (row_bytes % 16 == 0) && ((reinterpret_cast<uintptr_t>(a.data) & 15) == 0) &&
-                   row_bytes >= 1024 && 2 * row_bytes + 64 <= (size_t)f->smem_optin;
-  auto go = [&](auto kern, int wpb, size_t smem) -> int {
+  // a team of up to 4 warps shares a row: more warps in flight per byte of row buffer
+  const int slot_groups = p.tpad / 32;
+  p.team_warps = slot_groups >= 4 ? 4 : (slot_groups >= 2 ? 2 : 1);
+  if (const char* e = std::getenv("TAHOE_SD_TEAM")) p.team_warps = std::max(1, std::min(p.team_warps, std::atoi(e)));
+  const int per_warp = (slot_groups + p.team_warps - 1) / p.team_warps;   // slot groups each warp walks
+  const int G = per_warp >= 4 ? 4 : (per_warp >= 2 ? 2 : 1);
+  const size_t per_team = 2 * row_stride + 64 + 16;    // two row buffers, partials, mbarriers
+  if (per_team + 128 > (size_t)f->smem_optin) {
+    set_error("SHARED_DATA: two rows do not fit shared memory");
+    return TAHOE_ERR_NOT_APPLICABLE;
+  }
+  const int max_teams = std::min(15, 32 / p.team_warps);          // named barriers 1..15; 1024 threads
+  // Split shared memory between row buffers (teams in flight) and the top levels of the forest:
+  // throughput ~ teams / (100 cycles per shared-memory level + 800 per L2 level).
+  int best_top = 0, best_teams = 0;
+  double best_rate = 0.0;
+  for (int top = 0; top <= f->depth + 1; ++top) {
+    const size_t top_bytes = top ? (((size_t)1 << top) - 1) * p.tpad * sizeof(uint2) : 0;
+    if (top_bytes + per_team + 128 > (size_t)f->smem_optin) break;
+    const int teams = (int)std::min<size_t>((size_t)max_teams, ((size_t)f->smem_optin - 128 - top_bytes) / per_team);
+    const double rate = teams / (100.0 * top + 800.0 * (f->depth + 1 - top) + 200.0);
+    if (rate > best_rate) { best_rate = rate; best_top = top; best_teams = teams; }
+  }
+  if (const char* e = std::getenv("TAHOE_SD_TOP_LEVELS")) {
+    best_top = std::max(0, std::min(std::atoi(e), f->depth + 1));
+    const size_t top_bytes = best_top ? (((size_t)1 << best_top) - 1) * p.tpad * sizeof(uint2) : 0;
+    if (top_bytes + per_team + 128 > (size_t)f->smem_optin) { set_error("TAHOE_SD_TOP_LEVELS too large"); return TAHOE_ERR_INVALID; }
+    best_teams = (int)std::min<size_t>((size_t)max_teams, ((size_t)f->smem_optin - 128 - top_bytes) / per_team);
+  }
+  p.top_levels = best_top;
+  p.teams_per_block = best_teams;
+  const size_t rows_b = ((size_t)p.teams_per_block * per_team + 127) / 128 * 128;
+  p.top_off = (uint32_t)rows_b;
+  const size_t smem = rows_b + (best_top ? (((size_t)1 << best_top) - 1) * p.tpad * sizeof(uint2) : 0) + 128;
+  // bulk copies need 16-byte rows at 16-byte addresses; short rows are cheaper through the LSU
+  const bool tma = (row_bytes % 16 == 0) && ((reinterpret_cast<uintptr_t>(a.data) & 15) == 0) && row_bytes >= 1024;
+  auto go = [&](auto kern) -> int {
     if (smem > 48 * 1024)
       TAHOE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int threads = p.teams_per_block * p.team_warps * 32;
     int per_sm = 1;
-    TAHOE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, wpb * 32, smem));
+    TAHOE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
     per_sm = std::max(per_sm, 1);
-    const size_t want = (a.rows + wpb - 1) / wpb;
+    const size_t want = (a.rows + p.teams_per_block - 1) / p.teams_per_block;
     const unsigned grid = (unsigned)std::min<size_t>(want, (size_t)f->sm_count * per_sm);
-    p.warps_per_block = wpb;
-    kern<<<grid, wpb * 32, smem, a.stream>>>(p);
+    kern<<<grid, threads, smem, a.stream>>>(p);
     TAHOE_CUDA(cudaGetLastError());
     ++*launches;
     return TAHOE_OK;
   };
-  if (tma) {
-    const int wpb = (int)std::min<size_t>(16, ((size_t)f->smem_optin - 512) / (2 * row_bytes));
-    return go(k_shared_data<true>, wpb, (size_t)wpb * 2 * row_bytes + (size_t)wpb * 16 + 64);
-  }
-  const int wpb = (int)std::min<size_t>(8, (size_t)f->smem_optin / std::max<size_t>(row_bytes, 1));
-  if (wpb < 1) {
-    set_error("SHARED_DATA: one row does not fit shared memory");
-    return TAHOE_ERR_NOT_APPLICABLE;
-  }
-  return go(k_shared_data<false>, wpb, row_bytes * wpb);
+  if (G == 4) return tma ? go(k_shared_data<true, 4>) : go(k_shared_data<false, 4>);
+  if (G == 2) return tma ? go(k_shared_data<true, 2>) : go(k_shared_data<false, 2>);
+  return tma ? go(k_shared_data<true, 1>) : go(k_shared_data<false, 1>);
 }
 
 }  // namespace tahoe
