@@ -197,15 +197,11 @@ def main():
     rows = args.rows or cfg["rows"]
     n_nodes = cfg["trees"] * synth.tree_num_nodes(cfg["depth"])
     # ---- forest: built once on rank 0, broadcast once (the only collective; not timed)
+    from tahoe_b200 import shard
+    nodes = None
     if rank == 0:
         nodes = synth.gen_dense_forest(synth.FOREST_SEED[WORKLOAD], cfg["trees"], cfg["depth"], cfg["cols"])
-    if distributed:
-        buf = torch.empty(n_nodes * 12, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            buf.copy_(torch.from_numpy(nodes.view(np.uint8).reshape(-1)))
-        dist.broadcast(buf, src=0)
-        nodes = buf.cpu().numpy().view(synth.DENSE_NODE)
-        del buf
+    nodes = shard.broadcast_forest(nodes, n_nodes, src=0)
     forest = api.Forest.from_dense(nodes, cfg["trees"], cfg["depth"], cfg["cols"], missing=-999.0)
     info = forest.info()
     strategy = args.strategy if args.strategy >= 0 else forest.select(rows)[0]
@@ -273,6 +269,13 @@ def main():
         abytes = algorithmic_bytes_per_sample(cfg) * rows
         trav_ms = t_ms / n_prof if n_prof else ms_step
         achieved = abytes / (trav_ms * 1e-3) / 1e9
+        # second view of the same kernel: its node and rank words come out of SHARED MEMORY, whose
+        # bandwidth (128 B/clk/SM, B300_MICROARCH.md, x SM clock sampled during the run) is the bound it
+        # actually runs against; ideal bytes = 8 B per node visit (node word + rank word) + 4 B per leaf
+        sm_clock = (clocks.get("sm_mhz") or 1965.0) * 1e6
+        smem_peak = info.sm_count * 128.0 * sm_clock / 1e9
+        smem_bytes = float(rows) * cfg["trees"] * (cfg["depth"] * 8 + 4)
+        smem_achieved = smem_bytes / (trav_ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -288,7 +291,12 @@ def main():
                          "frac": achieved / peak, "traffic": _traffic(), "kernel": "k_smem_forest",
                          "kernel_ms": trav_ms, "quantize_ms": (q_ms / n_prof if n_prof else None),
                          "algorithmic_bytes_per_launch": abytes, "peak_source": peak_src,
-                         "note": "node bytes are served from shared memory, so achieved may exceed the HBM peak"},
+                         "note": "SURVEY 8(d) accounting: sample bytes + forest-node bytes touched; the node bytes "
+                                 "are served from shared memory, so achieved exceeds the HBM peak -- see smem",
+                         "smem": {"bound": "shared-memory bandwidth", "achieved": smem_achieved, "peak": smem_peak,
+                                  "unit": "GB/s", "frac": smem_achieved / smem_peak,
+                                  "peak_source": "148 SMs x 128 B/clk x sampled SM clock",
+                                  "ideal_bytes_per_launch": smem_bytes}},
             "e2e": e2e,
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks,

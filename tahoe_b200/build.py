@@ -13,6 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "lib", "libtahoe_b200.so")
+CLI = os.path.join(HERE, "bin", "Tahoe")
 SOURCES = ["abi.cu", "packer.cu", "textio.cu", "gen.cu", "kernels_direct.cu",
            "kernels_shared_data.cu", "kernels_smem.cu"]
 MAX_DEPTH = 14
@@ -57,6 +58,13 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if jobs or not os.path.exists(LIB):
         run(["nvcc", "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs,
              "-cudart", "static"])
+    # the `Tahoe MODEL DATA` command-line clone (include/BaseTahoeTest.h over the C ABI)
+    cli_src = os.path.join(HERE, "cli", "main.cpp")
+    hdr = os.path.join(HERE, "..", "include", "BaseTahoeTest.h")
+    if force or _newer(cli_src, CLI) or _newer(hdr, CLI) or _newer(LIB, CLI):
+        os.makedirs(os.path.dirname(CLI), exist_ok=True)
+        run(["nvcc", "-O2", "-std=c++17", "-Wno-deprecated-gpu-targets", "-o", CLI, cli_src,
+             "-L" + os.path.dirname(LIB), "-ltahoe_b200", "-Xlinker", "-rpath", "-Xlinker", "$ORIGIN/../lib"])
     return LIB
 
 

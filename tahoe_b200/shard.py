@@ -1,0 +1,72 @@
+"""Sample-sharded multi-GPU plumbing: one process per GPU, the forest replicated
+once, rows split into contiguous ranges, no collective on the predict path.
+
+The reference is single-GPU (BaseTahoeTest.h:78, 645-647); this is the one parallel strategy the
+path admits: pred[r] depends only on row r and the read-only forest (BaseTahoeTest.h:462-466).
+torch.distributed is plumbing only: a one-time broadcast of the AoS forest (NCCL on GPUs, gloo in the
+CPU tests) and an optional, untimed gather of the score slices.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .synth import DENSE_NODE
+
+
+def row_range(rank: int, world: int, total_rows: int) -> tuple[int, int]:
+    """Contiguous range [g*R/G, (g+1)*R/G) of rank g (64-bit arithmetic; ranges tile [0, R) exactly)."""
+    if not (0 <= rank < world):
+        raise ValueError("rank out of range")
+    lo = (int(total_rows) * rank) // world
+    hi = (int(total_rows) * (rank + 1)) // world
+    return lo, hi
+
+
+def broadcast_forest(nodes: np.ndarray | None, num_nodes: int, src: int = 0, device=None) -> np.ndarray:
+    """One-time broadcast of the dense AoS forest (12 B/node) from `src` to every rank."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        assert nodes is not None
+        return np.ascontiguousarray(nodes, dtype=DENSE_NODE)
+    dev = device if device is not None else ("cuda" if dist.get_backend() == "nccl" else "cpu")
+    buf = torch.empty(num_nodes * DENSE_NODE.itemsize, dtype=torch.uint8, device=dev)
+    if dist.get_rank() == src:
+        src_np = np.ascontiguousarray(nodes, dtype=DENSE_NODE).view(np.uint8).reshape(-1)
+        assert src_np.shape[0] == buf.shape[0], "node count mismatch"
+        buf.copy_(torch.from_numpy(src_np))
+    dist.broadcast(buf, src=src)
+    return buf.cpu().numpy().view(DENSE_NODE).copy()
+
+
+def gather_scores(local, total_rows: int, dst: int = 0):
+    """Untimed convenience: concatenate the ranks' score slices (in rank order = row order) on `dst`.
+    `local` is a torch tensor on the backend's device; returns the full tensor on dst, None elsewhere."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return local
+    world, rank = dist.get_world_size(), dist.get_rank()
+    sizes = [row_range(g, world, total_rows) for g in range(world)]
+    assert local.shape[0] == sizes[rank][1] - sizes[rank][0], "slice does not match this rank's row range"
+    longest = max(hi - lo for lo, hi in sizes)
+    padded = torch.zeros(longest, dtype=local.dtype, device=local.device)
+    padded[: local.shape[0]] = local
+    parts = [torch.empty_like(padded) for _ in range(world)] if rank == dst else None
+    dist.gather(padded, parts, dst=dst)
+    if rank != dst:
+        return None
+    return torch.cat([parts[g][: hi - lo] for g, (lo, hi) in enumerate(sizes)])
+
+
+class ShardedForest:
+    """One handle per process/GPU over the same forest; predict() runs the local rows only."""
+
+    def __init__(self, nodes, num_trees: int, depth: int, num_cols: int, *, src: int = 0, **kw):
+        from . import api
+        n = num_trees * ((1 << (depth + 1)) - 1)
+        self.nodes = broadcast_forest(nodes, n, src=src)
+        self.forest = api.Forest.from_dense(self.nodes, num_trees, depth, num_cols, **kw)
+
+    def predict_local(self, data, preds=None, **kw):
+        return self.forest.predict(data, preds, **kw)
