@@ -7,6 +7,8 @@
 //                           (the reference copies each row serially, uncoalesced, row-major).
 // Both sum leaf values in tree order 0..T-1 exactly like predict_on_cpu
 // (BaseTahoeTest.h:462-466), so their raw scores are bit-identical to the CPU's.
+#include <cstdlib>
+
 #include "device_utils.cuh"
 #include "forest.h"
 
@@ -29,7 +31,7 @@ struct DirectParams {
   Transform tf;
 };
 
-template <bool SPARSE, bool SMEM_ROWS>
+template <bool SPARSE, bool SMEM_ROWS, int kDirectGroup>
 __global__ void __launch_bounds__(kDirectThreads) k_direct(DirectParams p) {
   extern __shared__ float s_rows[];  // SMEM_ROWS: [cols][kDirectThreads]
   const size_t block_row0 = (size_t)blockIdx.x * kDirectThreads;
@@ -48,36 +50,94 @@ __global__ void __launch_bounds__(kDirectThreads) k_direct(DirectParams p) {
   if (row >= p.rows) return;
   const float* grow = p.data + row * (size_t)p.cols;
   float acc = 0.0f;
-  for (int t = 0; t < p.num_trees; ++t) {
-    float leaf_val;
-    int32_t leaf_id;
-    if (!SPARSE) {
-      const uint2* tree = p.heap + (int64_t)t * p.tree_stride;
-      uint32_t n = 1;
-      uint2 e = __ldg(tree + 1);
-      while (!(e.y & kMetaLeaf)) {
-        const int fid = e.y & 0x3FFFFFFF;
-        const float v = SMEM_ROWS ? s_rows[fid * kDirectThreads + threadIdx.x] : __ldg(grow + fid);
-        n = 2 * n + (branch_right(v, __uint_as_float(e.x), e.y & kMetaDefLeft, p.missing) ? 1u : 0u);
-        e = __ldg(tree + n);
+  if (kDirectGroup == 1) {
+    // Full machine: plenty of warps hide the L2 latency, and a per-lane loop lets lanes whose walk
+    // ended early drop out instead of re-reading their leaf.
+    for (int t = 0; t < p.num_trees; ++t) {
+      float leaf_val;
+      int32_t leaf_id;
+      if (!SPARSE) {
+        const uint2* tree = p.heap + (int64_t)t * p.tree_stride;
+        uint32_t n = 1;
+        uint2 e = __ldg(tree + 1);
+        while (!(e.y & kMetaLeaf)) {
+          const int fid = e.y & 0x3FFFFFFF;
+          const float v = SMEM_ROWS ? s_rows[fid * kDirectThreads + threadIdx.x] : __ldg(grow + fid);
+          n = 2 * n + (branch_right(v, __uint_as_float(e.x), e.y & kMetaDefLeft, p.missing) ? 1u : 0u);
+          e = __ldg(tree + n);
+        }
+        leaf_val = __uint_as_float(e.x);
+        leaf_id = (int32_t)n - 1;
+      } else {
+        const uint4* tree = p.sparse + p.tree_offsets[t];
+        uint32_t n = 0;
+        uint4 e = __ldg(tree);
+        while (!(e.y & kMetaLeaf)) {
+          const int fid = e.y & 0x3FFFFFFF;
+          const float v = SMEM_ROWS ? s_rows[fid * kDirectThreads + threadIdx.x] : __ldg(grow + fid);
+          n = e.z + (branch_right(v, __uint_as_float(e.x), e.y & kMetaDefLeft, p.missing) ? 1u : 0u);
+          e = __ldg(tree + n);
+        }
+        leaf_val = __uint_as_float(e.x);
+        leaf_id = (int32_t)n;
       }
-      leaf_val = __uint_as_float(e.x);
-      leaf_id = (int32_t)n - 1;
-    } else {
-      const uint4* tree = p.sparse + p.tree_offsets[t];
-      uint32_t n = 0;
-      uint4 e = __ldg(tree);
-      while (!(e.y & kMetaLeaf)) {
-        const int fid = e.y & 0x3FFFFFFF;
-        const float v = SMEM_ROWS ? s_rows[fid * kDirectThreads + threadIdx.x] : __ldg(grow + fid);
-        n = e.z + (branch_right(v, __uint_as_float(e.x), e.y & kMetaDefLeft, p.missing) ? 1u : 0u);
-        e = __ldg(tree + n);
-      }
-      leaf_val = __uint_as_float(e.x);
-      leaf_id = (int32_t)n;
+      acc += leaf_val;
+      if (p.leaf_ids) p.leaf_ids[row * (size_t)p.num_trees + t] = leaf_id;
     }
-    acc += leaf_val;
-    if (p.leaf_ids) p.leaf_ids[row * (size_t)p.num_trees + t] = leaf_id;
+    p.preds[row] = apply_transform(acc, p.tf);
+    return;
+  }
+  // Small batches: kDirectGroup trees are walked together: the level step is branch-free (a walk on its leaf
+  // re-reads it), so the dependent L2 round trips of the walks overlap and lanes whose walk ended
+  // early do not idle through the longest one -- few warps are resident, so latency is what counts.
+  for (int t0 = 0; t0 < p.num_trees; t0 += kDirectGroup) {
+    uint32_t n[kDirectGroup];
+    const void* tree[kDirectGroup];
+    uint32_t ex[kDirectGroup], ey[kDirectGroup], ez[kDirectGroup];
+#pragma unroll
+    for (int g = 0; g < kDirectGroup; ++g) {
+      const int t = min(t0 + g, p.num_trees - 1);          // past the end: repeat the last tree, drop its value
+      if (!SPARSE) {
+        const uint2* tr = p.heap + (int64_t)t * p.tree_stride;
+        tree[g] = tr;
+        n[g] = 1;
+        const uint2 e = __ldg(tr + 1);
+        ex[g] = e.x; ey[g] = e.y; ez[g] = 0;
+      } else {
+        const uint4* tr = p.sparse + p.tree_offsets[t];
+        tree[g] = tr;
+        n[g] = 0;
+        const uint4 e = __ldg(tr);
+        ex[g] = e.x; ey[g] = e.y; ez[g] = e.z;
+      }
+    }
+    for (;;) {
+      bool live = false;
+#pragma unroll
+      for (int g = 0; g < kDirectGroup; ++g) {
+        const bool leaf = (ey[g] & kMetaLeaf) != 0;
+        const int fid = leaf ? 0 : (int)(ey[g] & 0x3FFFFFFF);
+        const float v = SMEM_ROWS ? s_rows[fid * kDirectThreads + threadIdx.x] : __ldg(grow + fid);
+        const bool c = branch_right(v, __uint_as_float(ex[g]), ey[g] & kMetaDefLeft, p.missing);
+        if (!SPARSE) {
+          n[g] = leaf ? n[g] : 2 * n[g] + (c ? 1u : 0u);
+          const uint2 e = __ldg(static_cast<const uint2*>(tree[g]) + n[g]);
+          ex[g] = e.x; ey[g] = e.y;
+        } else {
+          n[g] = leaf ? n[g] : ez[g] + (c ? 1u : 0u);
+          const uint4 e = __ldg(static_cast<const uint4*>(tree[g]) + n[g]);
+          ex[g] = e.x; ey[g] = e.y; ez[g] = e.z;
+        }
+        live |= !leaf;
+      }
+      if (!__any_sync(__activemask(), live)) break;
+    }
+#pragma unroll
+    for (int g = 0; g < kDirectGroup; ++g) {
+      if (t0 + g >= p.num_trees) break;
+      acc += __uint_as_float(ex[g]);                       // tree order: the CPU's float sum, bit for bit
+      if (p.leaf_ids) p.leaf_ids[row * (size_t)p.num_trees + t0 + g] = SPARSE ? (int32_t)n[g] : (int32_t)n[g] - 1;
+    }
   }
   p.preds[row] = apply_transform(acc, p.tf);
 }
@@ -113,8 +173,15 @@ int launch_direct(tahoe_forest* f, const PredictArgs& a, bool rows_in_smem, int*
     ++*launches;
     return TAHOE_OK;
   };
-  if (f->sparse) return rows_in_smem ? go(k_direct<true, true>) : go(k_direct<true, false>);
-  return rows_in_smem ? go(k_direct<false, true>) : go(k_direct<false, false>);
+  // few rows: not enough warps to hide the L2 round trips -> 4 walks per thread
+  int group = a.rows <= (size_t)f->sm_count * 1024 ? 4 : 1;
+  if (const char* e = std::getenv("TAHOE_DIRECT_GROUP")) group = std::atoi(e) == 4 ? 4 : 1;
+  if (group == 4) {
+    if (f->sparse) return rows_in_smem ? go(k_direct<true, true, 4>) : go(k_direct<true, false, 4>);
+    return rows_in_smem ? go(k_direct<false, true, 4>) : go(k_direct<false, false, 4>);
+  }
+  if (f->sparse) return rows_in_smem ? go(k_direct<true, true, 1>) : go(k_direct<true, false, 1>);
+  return rows_in_smem ? go(k_direct<false, true, 1>) : go(k_direct<false, false, 1>);
 }
 
 }  // namespace tahoe
