@@ -36,7 +36,7 @@ static int applicable(const tahoe_forest* f, int strategy, size_t rows) {
     case TAHOE_STRATEGY_SHARED_DATA_PER_THREAD:
       return (size_t)f->params.num_cols * 256 * 4 <= (size_t)f->smem_optin ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
     case TAHOE_STRATEGY_SHARED_DATA:
-      return (!f->sparse && f->d_inter && 2 * (((size_t)f->params.num_cols * 4 + 15) & ~(size_t)15) + 208 <= (size_t)f->smem_optin)
+      return (!f->sparse && !f->host.inter.empty() && 2 * (((size_t)f->params.num_cols * 4 + 15) & ~(size_t)15) + 208 <= (size_t)f->smem_optin)
                  ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
     case TAHOE_STRATEGY_SHARED_FOREST:   // whole forest resident (BaseTahoeTest.h:657-668)
       return whole_forest_fits(f) ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
@@ -47,42 +47,79 @@ static int applicable(const tahoe_forest* f, int strategy, size_t rows) {
   }
 }
 
-// Performance model: per-strategy time = fixed launch cost + node visits / (visit rate at
-// full occupancy * fraction of the machine the batch can fill) + row-staging bytes / HBM.
-// Same functional form as the reference (T_smem + T_gmem per strategy, main.cu:35-63);
-// the rates are B200 measurements (DESIGN.md "Performance model"), not cudaMemcpy guesses.
-struct ModelConst {
-  double visits_per_s;   // full-machine node visits per second
-  double fill_rows;      // rows needed to saturate the machine
-  double fixed_s;        // launch + prologue
-};
-static const ModelConst kModel[TAHOE_NUM_STRATEGIES] = {
-    /* DIRECT            */ {4.0e11, 148.0 * 2048, 6e-6},
-    /* PER_THREAD        */ {5.0e11, 148.0 * 2048, 8e-6},
-    /* SHARED_DATA       */ {2.5e11, 148.0 * 64, 6e-6},
-    /* SHARED_FOREST     */ {2.6e12, 148.0 * 512, 12e-6},
-    /* SPLIT_SHARED_FOREST*/ {2.6e12, 148.0 * 512, 12e-6},
-};
+// Performance model (replaces main.cu:22-82).  Same idea as the reference -- per strategy, a time
+// built from the forest/batch shape and a few machine rates, argmin wins -- but every strategy has a
+// LATENCY term (what one warp's dependent chain costs when the batch cannot fill the machine) and a
+// THROUGHPUT term (node visits over the rate the full machine sustains), and the rates are B200
+// measurements (tools/sweep.py, profiles/r01_sweep_*.json), not multiples of a cudaMemcpy figure.
+namespace model {
+constexpr double kLaunch = 5e-6;            // launch + prologue of one kernel
+constexpr double kL2Visit = 106e-9;         // one dependent L2 node visit of a thread walking 4 trees at once
+constexpr double kDirectRate = 9.0e11;      // visits/s, DIRECT, forest far below L2 capacity
+constexpr double kPerThreadRate = 1.3e12;   // visits/s, rows staged in shared memory
+constexpr double kL1Bytes = 200e3;          // rows of the resident threads that L1 can hold
+constexpr double kRowGather = 1.7e12;       // B/s of 32-byte row sectors gathered through L2
+constexpr double kForestHalf = 80e6;        // forest bytes at which the L2-gather rates halve
+constexpr double kTeamLevel = 0.7e-6;       // SHARED_DATA: one tree level of a row's walk (latency-bound)
+constexpr double kSharedDataRate = 4.8e11;  // visits/s (slot-levels), SHARED_DATA
+constexpr double kRowStream = 3.0e12;       // B/s of sample rows through a TMA-fed SHARED_DATA kernel
+constexpr double kSmemVisit = 3.3e-13;      // s per visit, shared-memory forest, 16 warps x 6 trees (unit plan)
+constexpr double kTileStream = 5.0e12;      // B/s of rank tiles re-read once per chunk (half hidden)
+constexpr double kChunkFixed = 3.0e-6;      // stage one chunk + barrier
+constexpr double kTileLevel = 75e-9;        // one level of one traversal group of a tile (latency-bound)
+constexpr double kQuantRate = 1.7e12;       // B/s in+out of k_quantize, whole table in shared memory
+constexpr double kQuantRateStrided = 0.5e12;  // ... every 2^k-th threshold there, rest probed in L2
+}  // namespace model
 
-static int select_strategy(const tahoe_forest* f, size_t rows, double* out) {
-  const double visits = (double)rows * f->params.num_trees * std::max(f->mean_depth, 1.0);
-  const double hbm = 6.5e12;
+static double forest_bytes(const tahoe_forest* f) {
+  return f->sparse ? (double)f->host.sparse.size() * 16.0 : (double)f->host.heap.size() * 8.0;
+}
+
+static int select_strategy(const tahoe_forest* f, size_t rows_, double* out) {
+  using namespace model;
+  const double R = (double)std::max<size_t>(rows_, 1);
+  const double T = f->params.num_trees, C = f->params.num_cols;
+  const double dbar = std::max(f->mean_depth, 1.0);
+  // a thread's walk through one tree ends with the warp's deepest lane: sparse trees are uneven
+  const double dwalk = f->sparse ? 0.5 * (dbar + f->depth) : dbar;
+  const double l2_scale = 1.0 / (1.0 + forest_bytes(f) / kForestHalf);
   int best = TAHOE_STRATEGY_DIRECT;
   double best_t = std::numeric_limits<double>::infinity();
   for (int s = 0; s < TAHOE_NUM_STRATEGIES; ++s) {
     double t = std::numeric_limits<double>::infinity();
-    if (applicable(f, s, rows) == TAHOE_OK) {
-      const ModelConst& m = kModel[s];
-      const double fill = std::min(1.0, std::max((double)rows, 1.0) / m.fill_rows);
-      double v = visits;
-      if (s >= TAHOE_STRATEGY_SHARED_FOREST) v = (double)rows * f->params.num_trees * f->depth;  // padded
-      t = m.fixed_s + v / (m.visits_per_s * fill);
-      double bytes = (double)rows * f->params.num_cols * 4.0;
-      if (s >= TAHOE_STRATEGY_SHARED_FOREST) {
-        bytes = bytes * 2.0 + bytes * f->num_chunks;      // quantise pass + one tile stream per chunk
-        t += f->num_chunks * 4e-6;                        // chunk staging + barrier
+    if (applicable(f, s, rows_) == TAHOE_OK) {
+      switch (s) {
+        case TAHOE_STRATEGY_DIRECT:
+        case TAHOE_STRATEGY_SHARED_DATA_PER_THREAD: {
+          const bool staged = s == TAHOE_STRATEGY_SHARED_DATA_PER_THREAD;
+          const double rate = (staged ? kPerThreadRate : kDirectRate) * l2_scale;
+          const double lat = T * dwalk * kL2Visit * (staged ? 0.96 : 1.0);
+          double thr = R * T * dbar / rate;
+          // DIRECT gathers features straight from global memory: once the resident threads' rows
+          // outgrow L1, every visit pulls a 32-byte sector of its row through L2
+          if (!staged && C * 4.0 * 2048.0 > kL1Bytes) thr += R * T * dbar * 32.0 / kRowGather;
+          t = kLaunch + std::max(lat, thr);
+          break;
+        }
+        case TAHOE_STRATEGY_SHARED_DATA: {
+          const double tpad = f->host.tpad;
+          const double lat = (f->depth + 1) * kTeamLevel;
+          const double thr = R * tpad * dbar / kSharedDataRate;
+          t = kLaunch + std::max(std::max(lat, thr), R * C * 4.0 / kRowStream);
+          break;
+        }
+        default: {   // SHARED_FOREST / SPLIT_SHARED_FOREST: quantise pass + chunk passes
+          const double plan = smem_visit_cost(f->warps, f->group, f->staged);
+          const double visits = R * (double)f->qwords_trees * f->depth;               // padded depth
+          const double tiles_per_warp = std::ceil(R / 32.0 / ((double)f->sm_count * f->warps));
+          const double groups = (double)f->trees_per_chunk / std::max(f->group, 1);
+          const double lat = f->num_chunks * (kChunkFixed + tiles_per_warp * groups * f->depth * kTileLevel);
+          const double thr = visits * kSmemVisit * plan + 0.5 * f->num_chunks * R * C * 4.0 / kTileStream;
+          const double quant = kLaunch + R * C * 8.0 / (f->quant_stride > 1 ? kQuantRateStrided : kQuantRate);
+          t = kLaunch + quant + std::max(lat, thr);
+          break;
+        }
       }
-      t = std::max(t, m.fixed_s + bytes / hbm);
     }
     if (out) out[s] = t;
     if (t < best_t) { best_t = t; best = s; }

@@ -146,6 +146,7 @@ int pack_sparse(tahoe_forest* f, const tahoe_sparse_node_t* nodes, const float* 
                 const int64_t* tree_offsets);
 int upload(tahoe_forest* f);
 void plan_chunks(tahoe_forest* f);
+double smem_visit_cost(int warps, int group, bool staged);   // relative cost of a node visit under a plan
 
 // launchers (kernels_*.cu); each returns a status and adds to *launches
 struct PredictArgs {

@@ -356,7 +356,7 @@ int pack_sparse(tahoe_forest* f, const tahoe_sparse_node_t* nodes, const float* 
 // Struct.h:215-220): [warp tiles][forest chunk][mbarriers].
 // Relative cost of one node visit for a plan, from B200 measurements on the SUSY-shaped forest
 // (profiles/r01_variants_group_size.log): 16 warps x G=6 is the unit.
-static double visit_cost(int warps, int G, bool staged) {
+double smem_visit_cost(int warps, int G, bool staged) {
   static const double by_group[kMaxGroup + 1] = {0.0, 1.50, 1.25, 1.124, 1.096, 1.056, 1.0};
   const double by_warps = warps >= 16 ? 1.0 : (warps >= 8 ? 1.45 : 2.4);
   return by_group[G] * by_warps * (staged ? 1.11 : 1.0);
@@ -399,9 +399,9 @@ void plan_chunks(tahoe_forest* f) {
         int tpc = std::min(max_tpc / G * G, tpad);
         const int chunks = (tpad + tpc - 1) / tpc;     // balance: same chunk count, even whole groups
         tpc = ((tpad + chunks - 1) / chunks + G - 1) / G * G;
-        const double visits = (double)tpad * std::max(f->depth, 1) * 3.3e-13 * visit_cost(warps, G, staged);
+        const double visits = (double)tpad * std::max(f->depth, 1) * 3.3e-13 * smem_visit_cost(warps, G, staged);
         const double stream = (double)chunks * (double)C * 4.0 / 5.0e12;
-        const double cost = visits + 0.8 * stream;
+        const double cost = visits + 0.5 * stream;
         if (!found || cost < best) {
           found = true; best = cost;
           f->warps = warps; f->staged = staged != 0; f->slots = slots; f->group = G;
