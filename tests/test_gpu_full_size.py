@@ -1,0 +1,100 @@
+"""GPU parity at BASELINE.json's FULL sizes (configs 1-4), through the C ABI.
+
+The oracle is single-digit microseconds per (row, tree) visit chain, so at these sizes it checks a
+seeded row subset (first rows, last rows, a stride through the middle) bit for bit; every row is then
+covered by size-independent properties: all strategies that sum in tree order must agree bit for bit
+with each other on ALL rows, SHARED_DATA within the north-star tolerance, and the host-buffer path
+with the device path."""
+import numpy as np
+import pytest
+
+from tahoe_b200 import api, synth
+from tests.helpers import bits_equal, l1_mass, score_close
+
+pytestmark = pytest.mark.gpu
+ORDERED = (api.DIRECT, api.SHARED_DATA_PER_THREAD, api.SHARED_FOREST, api.SPLIT_SHARED_FOREST)
+
+
+def _subset(rows, k=2048):
+    mid = np.arange(0, rows, max(1, rows // k))[:k]
+    return np.unique(np.r_[0:min(k, rows), mid, max(0, rows - k):rows])
+
+
+def _device_rows(cfg, rows, miss_frac):
+    c = synth.CONFIGS[cfg]
+    return api.gen_data_device(synth.DATA_SEED[cfg], rows, c["cols"], miss_frac=miss_frac)
+
+
+def _host_rows(cfg, idx, miss_frac):
+    """the same generator on the host, only for the rows in idx (element index = row*cols + col)"""
+    c = synth.CONFIGS[cfg]
+    out = np.empty((idx.shape[0], c["cols"]), np.float32)
+    for i, r in enumerate(idx):
+        out[i] = synth.gen_data(synth.DATA_SEED[cfg], 1, c["cols"], miss_frac=miss_frac, row0=int(r))[0]
+    return out
+
+
+@pytest.mark.parametrize("cfg,miss_frac", [("C1", 0.0), ("C2", 0.001), ("C3", 0.0)])
+def test_dense_config_full_size(oracle, cfg, miss_frac):
+    import torch
+    c = synth.CONFIGS[cfg]
+    R, T, d, C = c["rows"], c["trees"], c["depth"], c["cols"]
+    nodes = synth.gen_dense_forest(synth.FOREST_SEED[cfg], T, d, C)
+    f = api.Forest.from_dense(nodes, T, d, C, missing=-999.0)
+    data = _device_rows(cfg, R, miss_frac)
+    idx = _subset(R)
+    host = _host_rows(cfg, idx, miss_frac)
+    assert np.array_equal(data[torch.from_numpy(idx).cuda()].cpu().numpy().view(np.uint32), host.view(np.uint32))
+    want, wids = oracle.predict_dense(nodes, T, d, host, -999.0, want_leaf_ids=True)
+    ref = None
+    ran = []
+    for s in api.ALL_STRATEGIES:
+        if not f.applicable(s, R):
+            continue
+        got = f.predict(data, strategy=s)
+        torch.cuda.synchronize()
+        g = got.cpu().numpy()
+        if s in ORDERED:
+            assert bits_equal(g[idx], want), (cfg, api.STRATEGY_NAMES[s])          # oracle, subset
+            if ref is None:
+                ref = g
+            else:
+                assert bits_equal(g, ref), (cfg, api.STRATEGY_NAMES[s])            # strategy vs strategy, ALL rows
+        else:
+            assert score_close(g[idx], want, l1_mass(nodes, T, d, wids)), (cfg, api.STRATEGY_NAMES[s])
+            if ref is not None:
+                assert np.max(np.abs(g.astype(np.float64) - ref)) <= 1e-5 * T     # every row, L1 mass <= T
+        ran.append(s)
+    assert len(ran) >= 2
+    # leaf ids on the subset rows, through the strategy the model picks for the full batch
+    pick, _ = f.select(R)
+    sub = data[torch.from_numpy(idx).cuda()].contiguous()
+    ids = torch.zeros((idx.shape[0], T), dtype=torch.int32, device="cuda")
+    f.predict(sub, strategy=pick, leaf_ids=ids)
+    torch.cuda.synchronize()
+    assert np.array_equal(ids.cpu().numpy(), wids)
+    if cfg == "C2":       # host-buffer path = device path on every row
+        hp = f.predict_host(data.cpu().numpy(), strategy=pick)
+        assert bits_equal(hp, f.predict(data, strategy=pick).cpu().numpy())
+
+
+def test_sparse_config_full_size(oracle):
+    """config 4: 2000 deep unbalanced trees (<= 20 levels), 1M rows; the dense layout cannot hold it."""
+    import torch
+    c = synth.CONFIGS["C4"]
+    R = c["rows"]
+    sp, offs, w, lv = synth.gen_sparse_forest(synth.FOREST_SEED["C4"], c["trees"], c["depth"], c["cols"])
+    assert int(lv.max()) == 20 and sp.shape[0] > 5_000_000
+    f = api.Forest.from_sparse(sp, offs, c["cols"], weights=w, missing=-999.0)
+    data = _device_rows("C4", R, 0.001)
+    idx = _subset(R, 1024)
+    host = _host_rows("C4", idx, 0.001)
+    want, wids = oracle.predict_sparse(sp, offs, host, -999.0, want_leaf_ids=True)
+    a = f.predict(data, strategy=api.DIRECT).cpu().numpy()
+    b = f.predict(data, strategy=api.SHARED_DATA_PER_THREAD).cpu().numpy()
+    assert bits_equal(a[idx], want) and bits_equal(a, b)
+    sub = data[torch.from_numpy(idx).cuda()].contiguous()
+    ids = torch.zeros((idx.shape[0], c["trees"]), dtype=torch.int32, device="cuda")
+    f.predict(sub, strategy=api.DIRECT, leaf_ids=ids)
+    torch.cuda.synchronize()
+    assert np.array_equal(ids.cpu().numpy(), wids)
