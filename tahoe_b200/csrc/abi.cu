@@ -197,7 +197,7 @@ int tahoe_forest_create_sparse(const tahoe_sparse_node_t* nodes, const float* we
 
 void tahoe_forest_destroy(tahoe_forest_t* f) {
   if (!f) return;
-  cudaFree(f->d_heap); cudaFree(f->d_sparse); cudaFree(f->d_tree_offsets); cudaFree(f->d_inter);
+  cudaFree(f->d_heap); cudaFree(f->d_sparse); cudaFree(f->d_sparse8); cudaFree(f->d_tree_offsets); cudaFree(f->d_inter);
   cudaFree(f->d_tree_order); cudaFree(f->d_orig_ids); cudaFree(f->d_qwords); cudaFree(f->d_qtable);
   cudaFree(f->d_qoffsets); cudaFree(f->d_leaf_origin);
   cudaFree(f->d_qlut_min); cudaFree(f->d_qlut_scale); cudaFree(f->d_qlut);

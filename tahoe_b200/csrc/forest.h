@@ -46,6 +46,8 @@ struct HostPack {
   // H8 / S16
   std::vector<uint2> heap;            // dense: [T][2^(d+1)]; entry 0 of each tree unused
   std::vector<uint4> sparse;          // sparse: {val, bits, left_idx, 0}
+  std::vector<uint2> sparse8;         // sparse, when the fields fit: {val, leaf<<31 | def_left<<30 | (left_idx - own index)<<fid_bits | fid}
+  int sparse_fid_bits = 0;
   std::vector<int64_t> tree_offsets;  // sparse: [T+1]
   // I8
   int tpad = 0;                       // trees padded to a multiple of 32
@@ -108,6 +110,7 @@ struct tahoe_forest {
   // device copies
   uint2* d_heap = nullptr;
   uint4* d_sparse = nullptr;
+  uint2* d_sparse8 = nullptr;
   int64_t* d_tree_offsets = nullptr;
   uint2* d_inter = nullptr;
   int32_t* d_tree_order = nullptr;

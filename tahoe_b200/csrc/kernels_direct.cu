@@ -24,7 +24,9 @@ struct DirectParams {
   float missing;
   const uint2* heap;            // dense: [T][2^(d+1)]
   int64_t tree_stride;          // 2^(d+1)
-  const uint4* sparse;          // sparse nodes
+  const uint4* sparse;          // sparse nodes, S16 {val, bits, left_idx, 0}
+  const uint2* sparse8;         // sparse nodes, S8 {val, leaf|def_left|delta|fid} (when the fields fit)
+  int fid_bits;                 // S8: width of the fid field; delta = left_idx - own index sits above it
   const int64_t* tree_offsets;  // sparse
   float* preds;
   int32_t* leaf_ids;
@@ -142,6 +144,46 @@ __global__ void __launch_bounds__(kDirectThreads) k_direct(DirectParams p) {
   p.preds[row] = apply_transform(acc, p.tf);
 }
 
+// Sparse forests, full machine, 8-byte nodes: the lanes of a warp walk the SAME tree (their loads share
+// the top levels' sectors), each in its own while loop, trees in order.  Tried and dropped
+// (profiles/r01_sparse_notes.md): free-running lanes (every lane in its own tree: full lane
+// utilisation, but 32 sectors per load instead of ~5 -- 1.36x slower).
+template <bool SMEM_ROWS>
+__global__ void __launch_bounds__(kDirectThreads) k_sparse8(DirectParams p) {
+  extern __shared__ float s_rows[];  // SMEM_ROWS: [cols][kDirectThreads]
+  const size_t block_row0 = (size_t)blockIdx.x * kDirectThreads;
+  const size_t row = block_row0 + threadIdx.x;
+  if (SMEM_ROWS) {
+    const size_t nrows = min((size_t)kDirectThreads, p.rows - block_row0);
+    const size_t total = nrows * (size_t)p.cols;
+    const float* src = p.data + block_row0 * (size_t)p.cols;
+    for (size_t w = threadIdx.x; w < total; w += kDirectThreads) {
+      const int r = (int)(w / p.cols), c = (int)(w % p.cols);
+      s_rows[c * kDirectThreads + r] = __ldg(src + w);
+    }
+    __syncthreads();
+  }
+  if (row >= p.rows) return;
+  const float* grow = p.data + row * (size_t)p.cols;
+  const uint32_t fid_mask = (1u << p.fid_bits) - 1u;
+  float acc = 0.0f;
+  for (int t = 0; t < p.num_trees; ++t) {
+    const uint2* tree = p.sparse8 + p.tree_offsets[t];
+    uint32_t n = 0;
+    uint2 e = __ldg(tree);
+    while (!(e.y & kMetaLeaf)) {
+      const uint32_t fid = e.y & fid_mask;
+      const float v = SMEM_ROWS ? s_rows[fid * kDirectThreads + threadIdx.x] : __ldg(grow + fid);
+      n += ((e.y & 0x3FFFFFFFu) >> p.fid_bits) +
+           (branch_right(v, __uint_as_float(e.x), e.y & kMetaDefLeft, p.missing) ? 1u : 0u);
+      e = __ldg(tree + n);
+    }
+    acc += __uint_as_float(e.x);
+    if (p.leaf_ids) p.leaf_ids[row * (size_t)p.num_trees + t] = (int32_t)n;
+  }
+  p.preds[row] = apply_transform(acc, p.tf);
+}
+
 int launch_direct(tahoe_forest* f, const PredictArgs& a, bool rows_in_smem, int* launches) {
   if (a.rows == 0) return TAHOE_OK;
   DirectParams p{};
@@ -153,6 +195,8 @@ int launch_direct(tahoe_forest* f, const PredictArgs& a, bool rows_in_smem, int*
   p.heap = f->d_heap;
   p.tree_stride = (int64_t)1 << (f->depth + 1);
   p.sparse = f->d_sparse;
+  p.sparse8 = f->d_sparse8;
+  p.fid_bits = f->host.sparse_fid_bits;
   p.tree_offsets = f->d_tree_offsets;
   p.preds = a.preds;
   p.leaf_ids = a.leaf_ids;
@@ -176,6 +220,8 @@ int launch_direct(tahoe_forest* f, const PredictArgs& a, bool rows_in_smem, int*
   // few rows: not enough warps to hide the L2 round trips -> 4 walks per thread
   int group = a.rows <= (size_t)f->sm_count * 1024 ? 4 : 1;
   if (const char* e = std::getenv("TAHOE_DIRECT_GROUP")) group = std::atoi(e) == 4 ? 4 : 1;
+  if (f->sparse && group == 1 && f->d_sparse8)   // full machine, 8-byte nodes when the fields fit
+    return rows_in_smem ? go(k_sparse8<true>) : go(k_sparse8<false>);
   if (group == 4) {
     if (f->sparse) return rows_in_smem ? go(k_direct<true, true, 4>) : go(k_direct<true, false, 4>);
     return rows_in_smem ? go(k_direct<false, true, 4>) : go(k_direct<false, false, 4>);

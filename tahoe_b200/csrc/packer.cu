@@ -342,6 +342,37 @@ int pack_sparse(tahoe_forest* f, const tahoe_sparse_node_t* nodes, const float* 
       depth_acc += std::ldexp(1.0, -level[k]);
     }
   }
+  // S8: children follow their parent in breadth-first order, so the child index is stored as a
+  // delta from the node's own index; with the feature id below it the node is 8 bytes, a child pair
+  // 16, and one 32-byte sector holds two pairs
+  {
+    const int fb = std::max(1, ceil_log2((uint64_t)std::max(max_fid + 1, 2)));
+    const uint64_t max_delta = (1ull << (30 - fb)) - 1;
+    bool fits = fb <= 20;
+    for (int t = 0; t < T && fits; ++t) {
+      const int64_t base = tree_offsets[t], n = tree_offsets[t + 1] - base;
+      for (int64_t k = 0; k < n; ++k) {
+        const tahoe_sparse_node_t& nd = nodes[base + k];
+        if (nd.bits < 0) continue;
+        if (nd.left_idx <= k || (uint64_t)(nd.left_idx - k) > max_delta) { fits = false; break; }
+      }
+    }
+    if (fits) {
+      h.sparse8.resize((size_t)total);
+      h.sparse_fid_bits = fb;
+      for (int t = 0; t < T; ++t) {
+        const int64_t base = tree_offsets[t], n = tree_offsets[t + 1] - base;
+        for (int64_t k = 0; k < n; ++k) {
+          const tahoe_sparse_node_t& nd = nodes[base + k];
+          uint32_t y;
+          if (nd.bits < 0) y = kMetaLeaf;
+          else y = ((uint32_t)nd.bits & kMetaDefLeft) | ((uint32_t)(nd.left_idx - k) << fb) |
+                   ((uint32_t)nd.bits & ((1u << fb) - 1u));
+          h.sparse8[base + k] = make_uint2(f2u(nd.val), y);
+        }
+      }
+    }
+  }
   f->sparse = true;
   f->depth = max_level;
   f->num_nodes = total;
@@ -462,6 +493,7 @@ int upload(tahoe_forest* f) {
   int rc;
   if ((rc = to_device(&f->d_heap, h.heap))) return rc;
   if ((rc = to_device(&f->d_sparse, h.sparse))) return rc;
+  if ((rc = to_device(&f->d_sparse8, h.sparse8))) return rc;
   if ((rc = to_device(&f->d_tree_offsets, h.tree_offsets))) return rc;
   if ((rc = to_device(&f->d_inter, h.inter))) return rc;
   if ((rc = to_device(&f->d_tree_order, h.tree_order))) return rc;

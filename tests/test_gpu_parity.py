@@ -73,9 +73,15 @@ def test_sparse_forest(oracle):
     data = synth.gen_data(4343, 3000, 50, miss_frac=0.01, nan_frac=0.005)
     want, wids = oracle.predict_sparse(sp, offs, data, -999.0, want_leaf_ids=True)
     f = api.Forest.from_sparse(sp, offs, 50, weights=w, missing=-999.0)
-    for s in (api.DIRECT, api.SHARED_DATA_PER_THREAD):
-        got, ids = _run(f, data, s)
-        assert np.array_equal(ids, wids) and bits_equal(got, want)
+    import os
+    for group in ("4", "1"):      # small-batch kernel (4 walks per thread) / full-machine kernel (free-running lanes)
+        os.environ["TAHOE_DIRECT_GROUP"] = group
+        try:
+            for s in (api.DIRECT, api.SHARED_DATA_PER_THREAD):
+                got, ids = _run(f, data, s)
+                assert np.array_equal(ids, wids) and bits_equal(got, want), (group, s)
+        finally:
+            del os.environ["TAHOE_DIRECT_GROUP"]
     for s in (api.SHARED_DATA, api.SHARED_FOREST, api.SPLIT_SHARED_FOREST):
         with pytest.raises(api.NotApplicable):
             _run(f, data, s)
