@@ -95,6 +95,10 @@ typedef struct {
   int smem_warps;             /* shared-memory-forest plan: warps per CTA, */
   int smem_staged;            /*   1 = one tile buffer per warp + register staging, 0 = two by TMA, */
   int smem_group;             /*   trees traversed together by one thread */
+  int sd_teams;               /* SHARED_DATA plan: row teams per CTA (0 = two rows do not fit shared memory), */
+  int sd_team_warps;          /*   warps sharing one row, */
+  int sd_top_levels;          /*   forest levels copied to shared memory, */
+  int sd_blocked;             /*   1 = the levels below are walked two at a time through 32-byte blocks */
 } tahoe_forest_info_t;
 
 /* ---- forest lifetime -------------------------------------------------------------
@@ -178,7 +182,10 @@ enum {
   TAHOE_EXPORT_SIMHASH = 8,       /* uint64 [T] simhash per original tree */
   TAHOE_EXPORT_QUANT_LUT = 9,     /* int32 [C][B+1] bucket index: thresholds of the column in lower buckets */
   TAHOE_EXPORT_QUANT_LUT_MIN = 10,  /* float [C] */
-  TAHOE_EXPORT_QUANT_LUT_SCALE = 11 /* float [C] */
+  TAHOE_EXPORT_QUANT_LUT_SCALE = 11, /* float [C] */
+  TAHOE_EXPORT_SD_TOP_NODES = 12,  /* uint2 [2^sd_top_levels - 1][Tpad] leaves pushed down (empty unless sd_blocked) */
+  TAHOE_EXPORT_SD_BLOCKS = 13,     /* uint32 [block][Tpad][8] = {root, left, right, 0} x {val bits, meta} */
+  TAHOE_EXPORT_SD_ORIG_BOTTOM = 14 /* int32 [2^depth][Tpad] bottom position -> original heap id of the leaf */
 };
 int tahoe_forest_export(const tahoe_forest_t* f, int which, void* buf, size_t* bytes);
 

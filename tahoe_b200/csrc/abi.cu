@@ -36,8 +36,7 @@ static int applicable(const tahoe_forest* f, int strategy, size_t rows) {
     case TAHOE_STRATEGY_SHARED_DATA_PER_THREAD:
       return (size_t)f->params.num_cols * 256 * 4 <= (size_t)f->smem_optin ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
     case TAHOE_STRATEGY_SHARED_DATA:
-      return (!f->sparse && !f->host.inter.empty() && 2 * (((size_t)f->params.num_cols * 4 + 15) & ~(size_t)15) + 208 <= (size_t)f->smem_optin)
-                 ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
+      return (!f->sparse && !f->host.inter.empty() && f->sd_teams >= 1) ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
     case TAHOE_STRATEGY_SHARED_FOREST:   // whole forest resident (BaseTahoeTest.h:657-668)
       return whole_forest_fits(f) ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
     case TAHOE_STRATEGY_SPLIT_SHARED_FOREST:  // at least one tree per chunk (:670-679)
@@ -198,7 +197,8 @@ int tahoe_forest_create_sparse(const tahoe_sparse_node_t* nodes, const float* we
 void tahoe_forest_destroy(tahoe_forest_t* f) {
   if (!f) return;
   cudaFree(f->d_heap); cudaFree(f->d_sparse); cudaFree(f->d_sparse8); cudaFree(f->d_tree_offsets); cudaFree(f->d_inter);
-  cudaFree(f->d_tree_order); cudaFree(f->d_orig_ids); cudaFree(f->d_qwords); cudaFree(f->d_qtable);
+  cudaFree(f->d_tree_order); cudaFree(f->d_orig_ids);
+  cudaFree(f->d_sd_top_nodes); cudaFree(f->d_sd_blocks); cudaFree(f->d_sd_orig_bottom); cudaFree(f->d_qwords); cudaFree(f->d_qtable);
   cudaFree(f->d_qoffsets); cudaFree(f->d_leaf_origin);
   cudaFree(f->d_qlut_min); cudaFree(f->d_qlut_scale); cudaFree(f->d_qlut);
   for (auto& w : f->ws) free_workspace(w);
@@ -220,6 +220,8 @@ int tahoe_forest_info(const tahoe_forest_t* f, tahoe_forest_info_t* info) {
   info->exchanged_nodes = f->exchanged; info->mean_depth = f->mean_depth; info->device = f->device;
   info->sm_count = f->sm_count; info->smem_optin_bytes = f->smem_optin; info->col_shift = f->col_shift;
   info->smem_warps = f->warps; info->smem_staged = f->staged; info->smem_group = f->group;
+  info->sd_teams = f->sd_teams; info->sd_team_warps = f->sd_team_warps;
+  info->sd_top_levels = f->sd_top; info->sd_blocked = f->sd_blocked;
   return TAHOE_OK;
 }
 
@@ -324,6 +326,9 @@ int tahoe_forest_export(const tahoe_forest_t* f, int which, void* buf, size_t* b
     case TAHOE_EXPORT_QUANT_LUT: src = h.qlut.data(); n = h.qlut.size() * 4; break;
     case TAHOE_EXPORT_QUANT_LUT_MIN: src = h.qlut_min.data(); n = h.qlut_min.size() * 4; break;
     case TAHOE_EXPORT_QUANT_LUT_SCALE: src = h.qlut_scale.data(); n = h.qlut_scale.size() * 4; break;
+    case TAHOE_EXPORT_SD_TOP_NODES: src = h.sd_top_nodes.data(); n = h.sd_top_nodes.size() * sizeof(uint2); break;
+    case TAHOE_EXPORT_SD_BLOCKS: src = h.sd_blocks.data(); n = h.sd_blocks.size() * sizeof(uint4); break;
+    case TAHOE_EXPORT_SD_ORIG_BOTTOM: src = h.sd_orig_bottom.data(); n = h.sd_orig_bottom.size() * 4; break;
     default: set_error("unknown export id"); return TAHOE_ERR_INVALID;
   }
   if (buf) {

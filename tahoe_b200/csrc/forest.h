@@ -55,6 +55,12 @@ struct HostPack {
   std::vector<int32_t> tree_order;    // [tpad] slot -> original tree, -1 padding
   std::vector<int32_t> orig_ids;      // [N][tpad] position -> original heap id
   std::vector<uint64_t> simhash;      // [T]
+  // B32 (SHARED_DATA): leaves pushed down to the bottom level; the top sd_top levels as [node][tpad]
+  // (shared-memory copy), the levels below in two-level blocks {root, left, right, -} of 32 bytes --
+  // one L2 sector serves two levels of a walk
+  std::vector<uint2> sd_top_nodes;    // [2^sd_top - 1][tpad]
+  std::vector<uint4> sd_blocks;       // [block][tpad][2]; block order: level sd_top roots, level sd_top+2 roots, ...
+  std::vector<int32_t> sd_orig_bottom;  // [2^d][tpad] bottom position -> original heap id of the leaf reached
   // Q4
   std::vector<uint32_t> qwords;       // [T][2^(d+1)]
   std::vector<float> qtable;          // sorted distinct thresholds, all columns back to back
@@ -105,6 +111,12 @@ struct tahoe_forest {
   int quant_stride = 1;          // k_quantize keeps every quant_stride-th threshold of a column in shared memory
   size_t quant_smem = 0;
 
+  // SHARED_DATA plan (plan_shared_data, at create): teams of team_warps warps share a row
+  int sd_teams = 0, sd_team_warps = 1, sd_group = 1;
+  int sd_top = 0;                // forest levels copied to shared memory
+  bool sd_blocked = false;       // B32 two-level blocks below the top levels
+  size_t sd_smem = 0;
+
   tahoe::HostPack host;
 
   // device copies
@@ -115,6 +127,9 @@ struct tahoe_forest {
   uint2* d_inter = nullptr;
   int32_t* d_tree_order = nullptr;
   int32_t* d_orig_ids = nullptr;
+  uint2* d_sd_top_nodes = nullptr;
+  uint4* d_sd_blocks = nullptr;
+  int32_t* d_sd_orig_bottom = nullptr;
   uint32_t* d_qwords = nullptr;
   float* d_qtable = nullptr;
   int32_t* d_qoffsets = nullptr;
@@ -149,6 +164,7 @@ int pack_sparse(tahoe_forest* f, const tahoe_sparse_node_t* nodes, const float* 
                 const int64_t* tree_offsets);
 int upload(tahoe_forest* f);
 void plan_chunks(tahoe_forest* f);
+void plan_shared_data(tahoe_forest* f);   // teams / top levels / B32 blocks; needs host.inter and query_device
 double smem_visit_cost(int warps, int group, bool staged);   // relative cost of a node visit under a plan
 
 // launchers (kernels_*.cu); each returns a status and adds to *launches

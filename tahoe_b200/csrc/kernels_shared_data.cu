@@ -34,7 +34,19 @@ struct SharedDataParams {
   int team_warps;            // 1, 2 or 4
   int top_levels;            // levels 0..top_levels-1 of the interleaved forest are copied to shared memory
   uint32_t top_off;          // byte offset of that copy ([2^top_levels - 1][tpad] uint2)
+  // B32 (BLOCKED kernels): the copy comes from top_nodes (leaves pushed down); levels top_levels..depth
+  // are walked two at a time through 32-byte blocks {root, left, right, -}
+  const uint2* top_nodes;    // [2^top_levels - 1][tpad]
+  const uint4* blocks;       // [block][tpad][2]
+  const int32_t* orig_bottom;  // [2^depth][tpad]
+  int block_levels;          // (depth + 1 - top_levels) / 2 >= 1
 };
+
+__device__ __forceinline__ void ldg_block(const uint4* p, uint32_t (&w)[8]) {   // one 32-byte sector, one request
+  asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+               : "l"(p));
+}
 
 
 __device__ __forceinline__ void team_barrier(int id, int threads) {
@@ -109,12 +121,80 @@ __device__ __forceinline__ double sd_walk_row(const SharedDataParams& p, const u
   return acc;
 }
 
+// B32 walk of one row: top_levels (>= 1) levels from shared memory, then block_levels L2 trips of
+// two levels each.  Leaves are pushed down in this layout, so every walk makes exactly `depth`
+// decisions and ends on the bottom level -- no leaf test in the loop, no early exit.
+template <int kSdGroup>
+__device__ __forceinline__ double sd_walk_row_blocked(const SharedDataParams& p, const uint2* s_top, const float* my,
+                                                      size_t row, int lane, int wt) {
+  double acc = 0.0;
+  const int gstride = 32 * p.team_warps;
+  auto decide = [&](uint32_t val, uint32_t meta) -> uint32_t {
+    const bool leaf = (meta & kMetaLeaf) != 0;     // a pushed-down copy: both children are the same leaf
+    const float v = my[leaf ? 0u : (meta & kMetaFidMask)];
+    const bool c = branch_right(v, __uint_as_float(val), meta & kMetaDefLeft, p.missing);
+    return (c != ((meta & kMetaExchange) != 0)) ? 1u : 0u;       // Struct.h:980
+  };
+  for (int s0 = lane + 32 * wt; s0 < p.tpad; s0 += gstride * kSdGroup) {
+    uint32_t q[kSdGroup];      // position inside the current level
+    int slot[kSdGroup];
+    uint2 e[kSdGroup];
+#pragma unroll
+    for (int g = 0; g < kSdGroup; ++g) {
+      slot[g] = min(s0 + gstride * g, p.tpad - 1);   // past the end: repeat the last slot, drop its sum
+      q[g] = 0;
+      e[g] = s_top[slot[g]];
+    }
+    for (int l = 0; l < p.top_levels; ++l) {         // decisions on levels 0 .. top_levels-1
+      const uint32_t next_first = (2u << l) - 1u;
+#pragma unroll
+      for (int g = 0; g < kSdGroup; ++g) {
+        q[g] = 2 * q[g] + decide(e[g].x, e[g].y);
+        if (l + 1 < p.top_levels) e[g] = s_top[(size_t)(next_first + q[g]) * p.tpad + slot[g]];
+      }
+    }
+    size_t base = 0;
+    float leaf_val[kSdGroup];
+    for (int j = 0; j < p.block_levels; ++j) {
+      uint32_t w[kSdGroup][8];
+#pragma unroll
+      for (int g = 0; g < kSdGroup; ++g)
+        ldg_block(p.blocks + ((base + q[g]) * p.tpad + slot[g]) * 2, w[g]);
+      const bool last = j + 1 == p.block_levels;
+#pragma unroll
+      for (int g = 0; g < kSdGroup; ++g) {
+        const uint32_t c0 = decide(w[g][0], w[g][1]);
+        const uint32_t cv = c0 ? w[g][4] : w[g][2], cm = c0 ? w[g][5] : w[g][3];
+        if (last) {                                  // the child is the bottom-level leaf
+          q[g] = 2 * q[g] + c0;
+          leaf_val[g] = __uint_as_float(cv);
+        } else {
+          q[g] = 4 * q[g] + 2 * c0 + decide(cv, cm);
+        }
+      }
+      base += (size_t)1 << (p.top_levels + 2 * j);
+    }
+#pragma unroll
+    for (int g = 0; g < kSdGroup; ++g) {
+      if (s0 + gstride * g >= p.tpad) continue;
+      acc += (double)leaf_val[g];                    // padding slots are leaves holding 0.0f
+      if (p.leaf_ids) {
+        const int t = p.tree_order[slot[g]];
+        if (t >= 0) p.leaf_ids[row * (size_t)p.num_trees + t] = p.orig_bottom[(size_t)q[g] * p.tpad + slot[g]];
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  return acc;
+}
+
 // Shared-memory map: [teams][2][row_stride floats] row buffers | [teams][2][4] double partials |
 // [teams][2] mbarriers (TMA only).
 // TMA = true : rows arrive by bulk copies (cp.async.bulk, row bytes a multiple of 16) completing on
 //              the buffer's mbarrier: the next row streams in from HBM while the current one is walked.
 // TMA = false: the team copies its row with coalesced loads (any width / alignment).
-template <bool TMA, int G>
+template <bool TMA, int G, bool BLOCKED>
 __global__ void __launch_bounds__(1024, 1) k_shared_data(SharedDataParams p) {
   extern __shared__ __align__(128) uint8_t sd_smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -133,7 +213,8 @@ __global__ void __launch_bounds__(1024, 1) k_shared_data(SharedDataParams p) {
   {
     uint2* dst = reinterpret_cast<uint2*>(sd_smem + p.top_off);
     const int n_top = p.top_levels > 0 ? ((1 << p.top_levels) - 1) * p.tpad : 0;
-    for (int i = threadIdx.x; i < n_top; i += blockDim.x) dst[i] = __ldg(p.inter + i);
+    const uint2* src = BLOCKED ? p.top_nodes : p.inter;
+    for (int i = threadIdx.x; i < n_top; i += blockDim.x) dst[i] = __ldg(src + i);
   }
   __syncthreads();
 
@@ -201,7 +282,8 @@ __global__ void __launch_bounds__(1024, 1) k_shared_data(SharedDataParams p) {
       team_barrier(1 + team, team_threads);           // the team's stores of this row are visible
     }
     const float* my = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(buf0) + (size_t)b * row_stride);
-    const double acc = sd_walk_row<G>(p, s_top, my, row, lane, wt);
+    const double acc = BLOCKED ? sd_walk_row_blocked<G>(p, s_top, my, row, lane, wt)
+                               : sd_walk_row<G>(p, s_top, my, row, lane, wt);
     if (lane == 0) partials[b * 4 + wt] = acc;
     team_barrier(1 + team, team_threads);
     if (wt == 0 && lane == 0) {
@@ -218,6 +300,10 @@ int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches) {
     set_error("SHARED_DATA needs the dense interleaved layout");
     return TAHOE_ERR_NOT_APPLICABLE;
   }
+  if (f->sd_teams < 1) {
+    set_error("SHARED_DATA: two rows do not fit shared memory");
+    return TAHOE_ERR_NOT_APPLICABLE;
+  }
   if (a.rows == 0) return TAHOE_OK;
   const size_t row_bytes = (size_t)f->params.num_cols * sizeof(float);
   const size_t row_stride = (row_bytes + 15) & ~(size_t)15;
@@ -228,40 +314,15 @@ int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.leaf_ids = a.leaf_ids;
   p.tf = Transform{f->params.output, (float)f->params.num_trees, f->params.threshold,
                    f->params.global_bias};
-  // a team of up to 4 warps shares a row: more warps in flight per byte of row buffer
-  const int slot_groups = p.tpad / 32;
-  p.team_warps = slot_groups >= 4 ? 4 : (slot_groups >= 2 ? 2 : 1);
-  if (const char* e = std::getenv("TAHOE_SD_TEAM")) p.team_warps = std::max(1, std::min(p.team_warps, std::atoi(e)));
-  const int per_warp = (slot_groups + p.team_warps - 1) / p.team_warps;   // slot groups each warp walks
-  const int G = per_warp >= 4 ? 4 : (per_warp >= 2 ? 2 : 1);
+  // the plan (teams, top levels, B32 blocks) was made when the forest was packed: plan_shared_data
+  p.team_warps = f->sd_team_warps;
+  p.top_levels = f->sd_top;
+  p.teams_per_block = f->sd_teams;
+  p.top_nodes = f->d_sd_top_nodes; p.blocks = f->d_sd_blocks; p.orig_bottom = f->d_sd_orig_bottom;
+  p.block_levels = f->sd_blocked ? (f->depth + 1 - f->sd_top) / 2 : 0;
   const size_t per_team = 2 * row_stride + 64 + 16;    // two row buffers, partials, mbarriers
-  if (per_team + 128 > (size_t)f->smem_optin) {
-    set_error("SHARED_DATA: two rows do not fit shared memory");
-    return TAHOE_ERR_NOT_APPLICABLE;
-  }
-  const int max_teams = std::min(15, 32 / p.team_warps);          // named barriers 1..15; 1024 threads
-  // Split shared memory between row buffers (teams in flight) and the top levels of the forest:
-  // throughput ~ teams / (100 cycles per shared-memory level + 800 per L2 level).
-  int best_top = 0, best_teams = 0;
-  double best_rate = 0.0;
-  for (int top = 0; top <= f->depth + 1; ++top) {
-    const size_t top_bytes = top ? (((size_t)1 << top) - 1) * p.tpad * sizeof(uint2) : 0;
-    if (top_bytes + per_team + 128 > (size_t)f->smem_optin) break;
-    const int teams = (int)std::min<size_t>((size_t)max_teams, ((size_t)f->smem_optin - 128 - top_bytes) / per_team);
-    const double rate = teams / (100.0 * top + 800.0 * (f->depth + 1 - top) + 200.0);
-    if (rate > best_rate) { best_rate = rate; best_top = top; best_teams = teams; }
-  }
-  if (const char* e = std::getenv("TAHOE_SD_TOP_LEVELS")) {
-    best_top = std::max(0, std::min(std::atoi(e), f->depth + 1));
-    const size_t top_bytes = best_top ? (((size_t)1 << best_top) - 1) * p.tpad * sizeof(uint2) : 0;
-    if (top_bytes + per_team + 128 > (size_t)f->smem_optin) { set_error("TAHOE_SD_TOP_LEVELS too large"); return TAHOE_ERR_INVALID; }
-    best_teams = (int)std::min<size_t>((size_t)max_teams, ((size_t)f->smem_optin - 128 - top_bytes) / per_team);
-  }
-  p.top_levels = best_top;
-  p.teams_per_block = best_teams;
-  const size_t rows_b = ((size_t)p.teams_per_block * per_team + 127) / 128 * 128;
-  p.top_off = (uint32_t)rows_b;
-  const size_t smem = rows_b + (best_top ? (((size_t)1 << best_top) - 1) * p.tpad * sizeof(uint2) : 0) + 128;
+  p.top_off = (uint32_t)(((size_t)p.teams_per_block * per_team + 127) / 128 * 128);
+  const size_t smem = f->sd_smem;
   // bulk copies need 16-byte rows at 16-byte addresses; short rows are cheaper through the LSU
   const bool tma = (row_bytes % 16 == 0) && ((reinterpret_cast<uintptr_t>(a.data) & 15) == 0) && row_bytes >= 1024;
   auto go = [&](auto kern) -> int {
@@ -278,9 +339,15 @@ int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches) {
     ++*launches;
     return TAHOE_OK;
   };
-  if (G == 4) return tma ? go(k_shared_data<true, 4>) : go(k_shared_data<false, 4>);
-  if (G == 2) return tma ? go(k_shared_data<true, 2>) : go(k_shared_data<false, 2>);
-  return tma ? go(k_shared_data<true, 1>) : go(k_shared_data<false, 1>);
+  const int G = f->sd_group;
+  if (f->sd_blocked) {
+    if (G == 4) return tma ? go(k_shared_data<true, 4, true>) : go(k_shared_data<false, 4, true>);
+    if (G == 2) return tma ? go(k_shared_data<true, 2, true>) : go(k_shared_data<false, 2, true>);
+    return tma ? go(k_shared_data<true, 1, true>) : go(k_shared_data<false, 1, true>);
+  }
+  if (G == 4) return tma ? go(k_shared_data<true, 4, false>) : go(k_shared_data<false, 4, false>);
+  if (G == 2) return tma ? go(k_shared_data<true, 2, false>) : go(k_shared_data<false, 2, false>);
+  return tma ? go(k_shared_data<true, 1, false>) : go(k_shared_data<false, 1, false>);
 }
 
 }  // namespace tahoe

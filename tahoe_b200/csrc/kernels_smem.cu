@@ -30,7 +30,7 @@ struct QuantParams {
   int cols;
   float missing;
   const float* table;      // sorted distinct thresholds, per column
-  const int32_t* offsets;  // [cols+1]
+  const int32_t* offsets;  // [cols] padded starts, then [cols] counts
   int buckets;             // B
   const float* lut_min;    // [cols]
   const float* lut_scale;  // [cols]
@@ -61,8 +61,8 @@ __global__ void __launch_bounds__(kQuantThreads, 1) k_quantize(QuantParams p) {
   const int split = blockIdx.x / p.cols;
   const int B = p.buckets;
   const int S = 1 << p.stride_log2;
-  const int off = p.offsets[c];
-  const int n = p.offsets[c + 1] - off;
+  const int off = p.offsets[c];                      // 16-byte aligned, NaN-padded (packer upload)
+  const int n = p.offsets[p.cols + c];
   const int ns = n >> p.stride_log2;                 // whole blocks of S thresholds
   int32_t* s_lut = reinterpret_cast<int32_t*>(qsm);  // [B+1], in units of blocks, clamped to ns
   float* s_tab = reinterpret_cast<float*>(s_lut + (B + 1));   // [ns] last threshold of each block
@@ -88,9 +88,14 @@ __global__ void __launch_bounds__(kQuantThreads, 1) k_quantize(QuantParams p) {
       if (s_tab[mid] <= v) lo = mid + 1; else hi = mid;
     }
     int r = lo << p.stride_log2;
-    if (S > 1) {                                 // count inside that block (sorted: stop at the first > v)
-      const int end = min(n, r + S);
-      while (r < end && __ldg(tab + r) <= v) ++r;
+    if (S > 1) {                                 // count inside that block: independent 16-byte loads
+      const float4* blk = reinterpret_cast<const float4*>(tab + r);
+      int cnt = 0;
+      for (int j = 0; j < (S >> 2); ++j) {
+        const float4 q = __ldg(blk + j);
+        cnt += (q.x <= v) + (q.y <= v) + (q.z <= v) + (q.w <= v);
+      }
+      r += cnt;
     }
     return (uint32_t)r << p.rank_shift;
   };

@@ -14,6 +14,7 @@
 //     node (rank, column, default direction) is one shared-memory word and the
 //     branch test is one unsigned compare.
 #include <algorithm>
+#include <limits>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -181,7 +182,100 @@ int pack_dense(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
       }
     }
   }
+  if (build_inter) plan_shared_data(f);
   return build_quant(f, nodes);
+}
+
+// ---- SHARED_DATA plan + B32 blocks ----------------------------------------------------------
+// A team of up to 4 warps shares a row (two row buffers per team, lane = tree slot).  Shared memory
+// is split between row buffers (teams in flight) and the top levels of the forest; below them a walk
+// pays one L2 round trip per level (~800 cycles of a dependent chain, a 32-byte sector per 8-byte
+// node once the lanes' paths have parted).  B32 halves both: the levels below the top are stored as
+// two-level blocks {root, left child, right child} in one sector, so one trip decides two levels.
+void plan_shared_data(tahoe_forest* f) {
+  HostPack& h = f->host;
+  const int d = f->depth, tpad = h.tpad;
+  const size_t row_bytes = (size_t)f->params.num_cols * sizeof(float);
+  const size_t row_stride = (row_bytes + 15) & ~(size_t)15;
+  const int slot_groups = tpad / 32;
+  f->sd_team_warps = slot_groups >= 4 ? 4 : (slot_groups >= 2 ? 2 : 1);
+  if (const char* e = std::getenv("TAHOE_SD_TEAM")) f->sd_team_warps = std::max(1, std::min(f->sd_team_warps, std::atoi(e)));
+  const int per_warp = (slot_groups + f->sd_team_warps - 1) / f->sd_team_warps;   // slot groups each warp walks
+  f->sd_group = per_warp >= 4 ? 4 : (per_warp >= 2 ? 2 : 1);
+  const size_t per_team = 2 * row_stride + 64 + 16;    // two row buffers, partials, mbarriers
+  f->sd_teams = 0;
+  f->sd_blocked = false;
+  if (per_team + 128 > (size_t)f->smem_optin) return;  // SHARED_DATA not applicable: two rows do not fit
+  const int max_teams = std::min(15, 32 / f->sd_team_warps);          // named barriers 1..15; 1024 threads
+  auto top_bytes = [&](int top) { return top ? (((size_t)1 << top) - 1) * tpad * sizeof(uint2) : (size_t)0; };
+  auto teams_for = [&](int top) {
+    return (int)std::min<size_t>((size_t)max_teams, ((size_t)f->smem_optin - 128 - top_bytes(top)) / per_team);
+  };
+  // blocked form: top levels K with (d + 1 - K) even and K <= d - 1, blocks small enough to keep
+  const char* eb = std::getenv("TAHOE_SD_BLOCKED");
+  const bool want_blocked = d >= 2 && !(eb && std::atoi(eb) == 0);
+  int best_top = 0;
+  bool best_blocked = false;
+  double best_rate = 0.0;
+  for (int blocked = 0; blocked <= (want_blocked ? 1 : 0); ++blocked) {
+    for (int top = blocked ? 1 : 0; top <= (blocked ? d - 1 : d + 1); ++top) {
+      if (blocked && ((d + 1 - top) & 1)) continue;
+      if (top_bytes(top) + per_team + 128 > (size_t)f->smem_optin) break;
+      if (blocked) {
+        size_t roots = 0;
+        for (int L = top; L < d; L += 2) roots += (size_t)1 << L;
+        if (roots * tpad * 32 > ((size_t)512 << 20)) continue;
+      }
+      const int below = d + 1 - top;
+      const double rate = teams_for(top) / (100.0 * top + 800.0 * (blocked ? below / 2 : below) + 200.0);
+      if (rate > best_rate) { best_rate = rate; best_top = top; best_blocked = blocked != 0; }
+    }
+  }
+  if (const char* e = std::getenv("TAHOE_SD_TOP_LEVELS")) {
+    int top = std::max(0, std::min(std::atoi(e), d + 1));
+    if (top_bytes(top) + per_team + 128 <= (size_t)f->smem_optin) {
+      best_top = top;
+      best_blocked = want_blocked && top >= 1 && top <= d - 1 && !((d + 1 - top) & 1);
+    }
+  }
+  f->sd_top = best_top;
+  f->sd_blocked = best_blocked;
+  f->sd_teams = teams_for(best_top);
+  f->sd_smem = ((size_t)f->sd_teams * per_team + 127) / 128 * 128 + top_bytes(best_top) + 128;
+  if (!best_blocked) return;
+
+  const int K = best_top;
+  const int64_t npt = ((int64_t)1 << (d + 1)) - 1;
+  size_t roots = 0;
+  for (int L = K; L < d; L += 2) roots += (size_t)1 << L;
+  h.sd_top_nodes.assign((((size_t)1 << K) - 1) * tpad, make_uint2(0, kMetaLeaf));
+  h.sd_blocks.assign(roots * tpad * 2, make_uint4(0, 0, 0, 0));
+  h.sd_orig_bottom.assign(((size_t)1 << d) * tpad, 0);
+  std::vector<uint2> pd((size_t)npt);
+  std::vector<int32_t> po((size_t)npt);
+  for (int slot = 0; slot < tpad; ++slot) {
+    for (int64_t k = 0; k < npt; ++k) {       // leaves pushed down: everything under a leaf is that leaf
+      uint2 node = h.inter[(size_t)k * tpad + slot];
+      int32_t o = h.orig_ids[(size_t)k * tpad + slot];
+      if (k > 0 && (pd[(k - 1) / 2].y & kMetaLeaf)) { node = pd[(k - 1) / 2]; o = po[(k - 1) / 2]; }
+      pd[k] = node;
+      po[k] = o;
+    }
+    for (int64_t k = 0; k < ((int64_t)1 << K) - 1; ++k) h.sd_top_nodes[(size_t)k * tpad + slot] = pd[k];
+    size_t base = 0;
+    for (int L = K; L < d; L += 2) {
+      const int64_t first = ((int64_t)1 << L) - 1;
+      for (int64_t q = 0; q < ((int64_t)1 << L); ++q) {
+        const int64_t r = first + q;
+        uint4* blk = h.sd_blocks.data() + ((base + q) * tpad + slot) * 2;
+        blk[0] = make_uint4(pd[r].x, pd[r].y, pd[2 * r + 1].x, pd[2 * r + 1].y);
+        blk[1] = make_uint4(pd[2 * r + 2].x, pd[2 * r + 2].y, 0u, 0u);
+      }
+      base += (size_t)1 << L;
+    }
+    const int64_t bottom = ((int64_t)1 << d) - 1;
+    for (int64_t q = 0; q < ((int64_t)1 << d); ++q) h.sd_orig_bottom[(size_t)q * tpad + slot] = po[bottom + q];
+  }
 }
 
 // ---- Q4: rank-quantised heap ------------------------------------------------------
@@ -454,6 +548,7 @@ void plan_chunks(tahoe_forest* f) {
   const size_t budget = (size_t)f->smem_optin - 2048 - lut_bytes;
   int S = 1;
   while ((max_n / S + 1) * 4 > budget) S <<= 1;
+  if (S == 2) S = 4;   // the in-block count reads whole float4s
   f->quant_stride = S;
   f->quant_smem = lut_bytes + (max_n / S + 1) * 4 + 16;
 }
@@ -498,6 +593,9 @@ int upload(tahoe_forest* f) {
   if ((rc = to_device(&f->d_inter, h.inter))) return rc;
   if ((rc = to_device(&f->d_tree_order, h.tree_order))) return rc;
   if ((rc = to_device(&f->d_orig_ids, h.orig_ids))) return rc;
+  if ((rc = to_device(&f->d_sd_top_nodes, h.sd_top_nodes))) return rc;
+  if ((rc = to_device(&f->d_sd_blocks, h.sd_blocks))) return rc;
+  if ((rc = to_device(&f->d_sd_orig_bottom, h.sd_orig_bottom))) return rc;
   if (!h.qwords.empty()) {   // padded with all-zero trees to whole traversal groups
     const size_t W = (size_t)1 << (f->depth + 1);
     const size_t words = (size_t)f->qwords_trees * W;
@@ -505,8 +603,24 @@ int upload(tahoe_forest* f) {
     TAHOE_CUDA(cudaMemset(f->d_qwords, 0, words * 4));
     TAHOE_CUDA(cudaMemcpy(f->d_qwords, h.qwords.data(), h.qwords.size() * 4, cudaMemcpyHostToDevice));
   }
-  if ((rc = to_device(&f->d_qtable, h.qtable))) return rc;
-  if ((rc = to_device(&f->d_qoffsets, h.qoffsets))) return rc;
+  if (!h.qtable.empty()) {
+    // device copy of the threshold tables: every column starts on a 16-byte boundary and is padded
+    // with NaN (NaN <= v is false) to whole blocks of quant_stride thresholds plus one, so k_quantize
+    // can finish a search with unguarded float4 loads.  d_qoffsets = [C padded starts][C counts].
+    const int C = f->params.num_cols;
+    const size_t S = (size_t)std::max(f->quant_stride, 4);
+    std::vector<float> padded;
+    std::vector<int32_t> offs(2 * (size_t)C);
+    for (int c = 0; c < C; ++c) {
+      const size_t n = (size_t)(h.qoffsets[c + 1] - h.qoffsets[c]);
+      offs[c] = (int32_t)padded.size();
+      offs[(size_t)C + c] = (int32_t)n;
+      padded.insert(padded.end(), h.qtable.begin() + h.qoffsets[c], h.qtable.begin() + h.qoffsets[c + 1]);
+      padded.resize(offs[c] + (n / S + 1) * S, std::numeric_limits<float>::quiet_NaN());
+    }
+    if ((rc = to_device(&f->d_qtable, padded))) return rc;
+    if ((rc = to_device(&f->d_qoffsets, offs))) return rc;
+  }
   if ((rc = to_device(&f->d_leaf_origin, h.leaf_origin))) return rc;
   if ((rc = to_device(&f->d_qlut_min, h.qlut_min))) return rc;
   if ((rc = to_device(&f->d_qlut_scale, h.qlut_scale))) return rc;

@@ -64,6 +64,54 @@ def interleaved_traverse(inter, orig_ids, tree_order, tpad, depth, T, data, miss
     return vals, ids
 
 
+def blocked_traverse(top_nodes, blocks, orig_bottom, tree_order, tpad, depth, K, T, data, missing):
+    """B32 (SHARED_DATA): K top levels [2^K-1][tpad][2] with leaves pushed down, then two-level blocks
+    [block][tpad][8] = {root, left, right, -}.  Exactly `depth` decisions, the kernel's index algebra.
+    -> (values [R,T], ids [R,T]) in ORIGINAL tree order"""
+    top = top_nodes.reshape((1 << K) - 1, tpad, 2)
+    blk = blocks.reshape(-1, tpad, 8)
+    ob = orig_bottom.reshape(1 << depth, tpad)
+    J = (depth + 1 - K) // 2
+    assert K >= 1 and J >= 1 and K + 2 * J == depth + 1
+    R = data.shape[0]
+    rows = np.arange(R)
+    vals = np.zeros((R, T), np.float32)
+    ids = np.zeros((R, T), np.int32)
+
+    def decide(val, meta):
+        leaf = (meta & LEAF) != 0
+        fid = np.where(leaf, 0, (meta & FIDMASK).astype(np.int64))
+        c = _right(data[rows, fid], val.view(np.float32), (meta & DEFLEFT) != 0, missing)
+        return np.where((meta & EXCH) != 0, ~c, c).astype(np.int64)
+
+    for slot in range(tpad):
+        t = tree_order[slot]
+        q = np.zeros(R, np.int64)
+        for l in range(K):
+            e = top[(1 << l) - 1 + q, slot]
+            q = 2 * q + decide(e[:, 0], e[:, 1])
+        base = 0
+        for j in range(J):
+            w = blk[base + q, slot]
+            c0 = decide(w[:, 0], w[:, 1])
+            cv = np.where(c0 == 1, w[:, 4], w[:, 2])
+            cm = np.where(c0 == 1, w[:, 5], w[:, 3])
+            if j == J - 1:
+                q = 2 * q + c0
+                assert np.all(cm & LEAF)
+                leaf_val = cv
+            else:
+                q = 4 * q + 2 * c0 + decide(cv, cm)
+            base += 1 << (K + 2 * j)
+        assert base == blk.shape[0]
+        if t < 0:
+            assert np.all(leaf_val == 0)
+            continue
+        vals[:, t] = leaf_val.view(np.float32)
+        ids[:, t] = ob[q, slot]
+    return vals, ids
+
+
 def quantize_rows(data, table, offsets, rank_shift, miss_code, missing):
     """k_quantize: float rows -> rank words [R,C] (uint32)."""
     R, Ccols = data.shape

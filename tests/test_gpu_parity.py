@@ -49,6 +49,29 @@ def test_all_strategies_match_reference(oracle, name):
     assert score_close(got, want, mass)
 
 
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_shared_data_blocked_walk(oracle, name, monkeypatch):
+    """SHARED_DATA through the 32-byte two-level blocks, forced for every legal split of the levels
+    (the planner only picks it for forests that outgrow shared memory)."""
+    c = load_case(name)
+    d = c["depth"]
+    _, wids = oracle.predict_dense(c["nodes"], c["trees"], d, c["data"], float(c["missing"]), want_leaf_ids=True)
+    want = golden_preds(c, 0, 0.0, 0.0)
+    mass = l1_mass(c["nodes"], c["trees"], d, wids)
+    for top in range(1, d):
+        if (d + 1 - top) % 2:
+            continue
+        monkeypatch.setenv("TAHOE_SD_TOP_LEVELS", str(top))
+        f = api.Forest.from_dense(c["nodes"], c["trees"], d, c["cols"], missing=float(c["missing"]))
+        info = f.info()
+        if info.sd_teams < 1 or info.sd_top_levels != top:
+            continue
+        assert info.sd_blocked
+        got, ids = _run(f, c["data"], api.SHARED_DATA)
+        assert np.array_equal(ids, wids), (name, top)
+        assert score_close(got, want, mass), (name, top)
+
+
 @pytest.mark.parametrize("flags,thr,bias", TRANSFORMS[1:])
 def test_output_transforms(oracle, flags, thr, bias):
     c = load_case("char_w")

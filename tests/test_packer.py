@@ -52,6 +52,39 @@ def test_interleaved_layout_with_exchange_bits(oracle, name):
     np.testing.assert_allclose(vals.sum(1, dtype=np.float64), want.astype(np.float64), rtol=1e-5, atol=1e-5)
 
 
+@pytest.mark.parametrize("name", PACK_CASES)
+@pytest.mark.parametrize("top", [None, 1, 2, 3])
+def test_blocked_layout_for_shared_data(oracle, name, top, monkeypatch):
+    """B32: pushed-down leaves + two-level 32-byte blocks give the oracle's leaves, for the planned split
+    of levels and for forced ones (TAHOE_SD_TOP_LEVELS is read when the forest is packed)."""
+    c = load_case(name)
+    if top is not None:
+        monkeypatch.setenv("TAHOE_SD_TOP_LEVELS", str(top))
+    f = _forest(c)
+    info = f.info()
+    d = c["depth"]
+    if top is not None and (top > d - 1 or (d + 1 - top) % 2):
+        assert not info.sd_blocked
+        return
+    if d < 2 or info.sd_teams < 1:
+        assert not info.sd_blocked
+        return
+    if top is None and not info.sd_blocked:
+        assert info.sd_top_levels == d + 1      # small forest: the planner keeps all of it in shared memory
+        return
+    assert info.sd_blocked and (top is None or info.sd_top_levels == top)
+    K = info.sd_top_levels
+    assert 1 <= K <= d - 1 and (d + 1 - K) % 2 == 0
+    want, wids = oracle.predict_dense(c["nodes"], c["trees"], d, c["data"], float(c["missing"]), want_leaf_ids=True)
+    order = f.export(api.EXPORT_TREE_ORDER, np.int32)
+    vals, ids = emulate.blocked_traverse(f.export(api.EXPORT_SD_TOP_NODES, np.uint32),
+                                         f.export(api.EXPORT_SD_BLOCKS, np.uint32),
+                                         f.export(api.EXPORT_SD_ORIG_BOTTOM, np.int32), order, order.shape[0],
+                                         d, K, c["trees"], c["data"], float(c["missing"]))
+    assert np.array_equal(ids, wids)
+    np.testing.assert_allclose(vals.sum(1, dtype=np.float64), want.astype(np.float64), rtol=1e-5, atol=1e-5)
+
+
 @pytest.mark.parametrize("name", ["tiny", "char_w", "short_w", "ties"])
 def test_probability_reorder_matches_reference_packer(name):
     """Our swapped trees, tree by tree, equal the reference packer's (Struct.h:1775-1825)."""
