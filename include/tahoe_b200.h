@@ -99,6 +99,9 @@ typedef struct {
   int sd_team_warps;          /*   warps sharing one row, */
   int sd_top_levels;          /*   forest levels copied to shared memory, */
   int sd_blocked;             /*   1 = the levels below are walked two at a time through 32-byte blocks */
+  int sparse_cut;             /* sparse forests through shared memory: breadth-first nodes of each tree kept there */
+  double sparse_deep_walks;   /*   expected fraction of (row, tree) walks that go deeper (finished in L2) */
+  int sparse_fid_bits;        /*   width of the feature-id field of an 8-byte sparse node (0 = fields do not fit) */
 } tahoe_forest_info_t;
 
 /* ---- forest lifetime -------------------------------------------------------------
@@ -185,7 +188,10 @@ enum {
   TAHOE_EXPORT_QUANT_LUT_SCALE = 11, /* float [C] */
   TAHOE_EXPORT_SD_TOP_NODES = 12,  /* uint2 [2^sd_top_levels - 1][Tpad] leaves pushed down (empty unless sd_blocked) */
   TAHOE_EXPORT_SD_BLOCKS = 13,     /* uint32 [block][Tpad][8] = {root, left, right, 0} x {val bits, meta} */
-  TAHOE_EXPORT_SD_ORIG_BOTTOM = 14 /* int32 [2^depth][Tpad] bottom position -> original heap id of the leaf */
+  TAHOE_EXPORT_SD_ORIG_BOTTOM = 14, /* int32 [2^depth][Tpad] bottom position -> original heap id of the leaf */
+  TAHOE_EXPORT_SPARSE_BFS = 15,      /* uint2 [nodes] sparse trees renumbered breadth-first: {val, leaf<<31|def_left<<30|delta<<fid_bits|fid} */
+  TAHOE_EXPORT_SPARSE_BFS_ORIG = 16, /* int32 [nodes] breadth-first index -> caller's node index inside its tree */
+  TAHOE_EXPORT_SPARSE_TOP = 17       /* uint2 [chunks * trees_per_chunk][sparse_cut] shared-memory image of the tree tops */
 };
 int tahoe_forest_export(const tahoe_forest_t* f, int which, void* buf, size_t* bytes);
 

@@ -26,7 +26,7 @@ ALL_STRATEGIES = list(STRATEGY_NAMES)
 (EXPORT_HEAP_NODES, EXPORT_INTERLEAVED, EXPORT_TREE_ORDER, EXPORT_ORIG_IDS, EXPORT_QUANT_WORDS,
  EXPORT_QUANT_TABLE, EXPORT_QUANT_OFFSETS, EXPORT_LEAF_ORIGIN, EXPORT_SIMHASH, EXPORT_QUANT_LUT,
  EXPORT_QUANT_LUT_MIN, EXPORT_QUANT_LUT_SCALE, EXPORT_SD_TOP_NODES, EXPORT_SD_BLOCKS,
- EXPORT_SD_ORIG_BOTTOM) = range(15)
+ EXPORT_SD_ORIG_BOTTOM, EXPORT_SPARSE_BFS, EXPORT_SPARSE_BFS_ORIG, EXPORT_SPARSE_TOP) = range(18)
 
 
 class TahoeError(RuntimeError):
@@ -56,7 +56,8 @@ class ForestInfo(C.Structure):
                 ("sm_count", C.c_int), ("smem_optin_bytes", C.c_int), ("col_shift", C.c_int),
                 ("smem_warps", C.c_int), ("smem_staged", C.c_int), ("smem_group", C.c_int),
                 ("sd_teams", C.c_int), ("sd_team_warps", C.c_int), ("sd_top_levels", C.c_int),
-                ("sd_blocked", C.c_int)]
+                ("sd_blocked", C.c_int), ("sparse_cut", C.c_int), ("sparse_deep_walks", C.c_double),
+                ("sparse_fid_bits", C.c_int)]
 
 
 _lib = None

@@ -26,7 +26,10 @@ static void free_workspace(Workspace& w) {
   w = Workspace{};
 }
 
-static bool whole_forest_fits(const tahoe_forest* f) { return f->quant && f->num_chunks == 1; }
+static bool whole_forest_fits(const tahoe_forest* f) {
+  if (f->sparse) return f->sp_tpc >= 1 && f->sp_chunks == 1 && f->sp_overflow == 0.0;
+  return f->quant && f->num_chunks == 1;
+}
 
 static int applicable(const tahoe_forest* f, int strategy, size_t rows) {
   (void)rows;
@@ -40,6 +43,7 @@ static int applicable(const tahoe_forest* f, int strategy, size_t rows) {
     case TAHOE_STRATEGY_SHARED_FOREST:   // whole forest resident (BaseTahoeTest.h:657-668)
       return whole_forest_fits(f) ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
     case TAHOE_STRATEGY_SPLIT_SHARED_FOREST:  // at least one tree per chunk (:670-679)
+      if (f->sparse) return f->sp_tpc >= 1 ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
       return (f->quant && f->trees_per_chunk >= 1) ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
     default:
       return TAHOE_ERR_INVALID;
@@ -67,7 +71,12 @@ constexpr double kTileStream = 5.0e12;      // B/s of rank tiles re-read once pe
 constexpr double kChunkFixed = 3.0e-6;      // stage one chunk + barrier
 constexpr double kTileLevel = 75e-9;        // one level of one traversal group of a tile (latency-bound)
 constexpr double kQuantRate = 1.7e12;       // B/s in+out of k_quantize, whole table in shared memory
-constexpr double kQuantRateStrided = 0.5e12;  // ... every 2^k-th threshold there, rest probed in L2
+constexpr double kQuantRateStrided = 1.0e12;
+constexpr double kSparseVisit = 6.0e-13;      // s per node visit, sparse tree tops in shared memory (free-running lanes)
+constexpr double kSparseChunkRow = 7.0e-11;   // s per row per chunk: tile re-stream + refill latency share
+constexpr double kSparseDeep = 4.7e-11;       // s per walk that leaves the tops and is finished in L2
+constexpr double kSparseStep = 60e-9;         // one step of a lane's two interleaved sequences (latency)
+constexpr double kSparseTileFixed = 2e-6;     // refill a warp's tile buffer + final drain  // ... every 2^k-th threshold there, rest probed in L2
 }  // namespace model
 
 static double forest_bytes(const tahoe_forest* f) {
@@ -107,7 +116,18 @@ static int select_strategy(const tahoe_forest* f, size_t rows_, double* out) {
           t = kLaunch + std::max(std::max(lat, thr), R * C * 4.0 / kRowStream);
           break;
         }
-        default: {   // SHARED_FOREST / SPLIT_SHARED_FOREST: quantise pass + chunk passes
+        default: if (f->sparse) {   // tile pass + tree tops in shared memory + deep walks finished in L2
+          const double warps = (double)f->sm_count * kSparseWarps;
+          const double tiles_per_warp = std::ceil(R / 32.0 / warps);
+          const double visits = R * T * (dbar + 1.0);
+          const double thr = visits * kSparseVisit + f->sp_chunks * R * kSparseChunkRow +
+                             R * T * f->sp_overflow * kSparseDeep;
+          // one warp's chain: two sequences of tpc/2 trees per tile, then the tile refill
+          const double lat = f->sp_chunks * (kChunkFixed + tiles_per_warp *
+                             (0.5 * f->sp_tpc * (dbar + 1.0) * kSparseStep + kSparseTileFixed));
+          t = 2.0 * kLaunch + R * C * 8.0 / kRowStream + std::max(lat, thr);
+          break;
+        } else {   // SHARED_FOREST / SPLIT_SHARED_FOREST: quantise pass + chunk passes
           const double plan = smem_visit_cost(f->warps, f->group, f->staged);
           const double visits = R * (double)f->qwords_trees * f->depth;               // padded depth
           const double tiles_per_warp = std::ceil(R / 32.0 / ((double)f->sm_count * f->warps));
@@ -140,7 +160,7 @@ static int predict_impl(tahoe_forest* f, int strategy, const PredictArgs& a) {
     case TAHOE_STRATEGY_DIRECT: rc = launch_direct(f, a, false, &launches); break;
     case TAHOE_STRATEGY_SHARED_DATA_PER_THREAD: rc = launch_direct(f, a, true, &launches); break;
     case TAHOE_STRATEGY_SHARED_DATA: rc = launch_shared_data(f, a, &launches); break;
-    default: rc = launch_smem_forest(f, a, &launches); break;
+    default: rc = f->sparse ? launch_sparse_smem(f, a, &launches) : launch_smem_forest(f, a, &launches); break;
   }
   f->last_launches = launches;
   return rc;
@@ -198,6 +218,7 @@ void tahoe_forest_destroy(tahoe_forest_t* f) {
   if (!f) return;
   cudaFree(f->d_heap); cudaFree(f->d_sparse); cudaFree(f->d_sparse8); cudaFree(f->d_tree_offsets); cudaFree(f->d_inter);
   cudaFree(f->d_tree_order); cudaFree(f->d_orig_ids);
+  cudaFree(f->d_sp_full); cudaFree(f->d_sp_orig); cudaFree(f->d_sp_top);
   cudaFree(f->d_sd_top_nodes); cudaFree(f->d_sd_blocks); cudaFree(f->d_sd_orig_bottom); cudaFree(f->d_qwords); cudaFree(f->d_qtable);
   cudaFree(f->d_qoffsets); cudaFree(f->d_leaf_origin);
   cudaFree(f->d_qlut_min); cudaFree(f->d_qlut_scale); cudaFree(f->d_qlut);
@@ -213,7 +234,10 @@ int tahoe_forest_info(const tahoe_forest_t* f, tahoe_forest_info_t* info) {
   info->num_trees = f->params.num_trees; info->depth = f->depth; info->num_cols = f->params.num_cols;
   info->is_sparse = f->sparse; info->num_nodes = f->num_nodes; info->node_width_bytes = f->node_width;
   info->quantized = f->quant; info->rank_bits = f->rank_bits; info->col_bits = f->col_bits;
-  info->trees_per_chunk = f->trees_per_chunk; info->num_chunks = f->num_chunks;
+  info->trees_per_chunk = f->sparse ? f->sp_tpc : f->trees_per_chunk;
+  info->num_chunks = f->sparse ? f->sp_chunks : f->num_chunks;
+  info->sparse_cut = f->sp_cut; info->sparse_deep_walks = f->sp_overflow;
+  info->sparse_fid_bits = f->host.sparse_fid_bits;
   info->bytes_heap = (int64_t)(f->host.heap.size() * sizeof(uint2) + f->host.sparse.size() * sizeof(uint4));
   info->bytes_interleaved = (int64_t)(f->host.inter.size() * sizeof(uint2));
   info->bytes_quantized = (int64_t)(f->host.qwords.size() * sizeof(uint32_t));
@@ -329,6 +353,9 @@ int tahoe_forest_export(const tahoe_forest_t* f, int which, void* buf, size_t* b
     case TAHOE_EXPORT_SD_TOP_NODES: src = h.sd_top_nodes.data(); n = h.sd_top_nodes.size() * sizeof(uint2); break;
     case TAHOE_EXPORT_SD_BLOCKS: src = h.sd_blocks.data(); n = h.sd_blocks.size() * sizeof(uint4); break;
     case TAHOE_EXPORT_SD_ORIG_BOTTOM: src = h.sd_orig_bottom.data(); n = h.sd_orig_bottom.size() * 4; break;
+    case TAHOE_EXPORT_SPARSE_BFS: src = h.sp_full.data(); n = h.sp_full.size() * sizeof(uint2); break;
+    case TAHOE_EXPORT_SPARSE_BFS_ORIG: src = h.sp_orig.data(); n = h.sp_orig.size() * 4; break;
+    case TAHOE_EXPORT_SPARSE_TOP: src = h.sp_top.data(); n = h.sp_top.size() * sizeof(uint2); break;
     default: set_error("unknown export id"); return TAHOE_ERR_INVALID;
   }
   if (buf) {

@@ -35,6 +35,8 @@ constexpr int kMaxGroup = 6;                     // trees traversed together by 
 constexpr int kStagedMaxCols = 32;               // register-staged tiles keep one word per column per lane
 constexpr int ilog2_c(int v) { return v <= 1 ? 0 : 1 + ilog2_c(v >> 1); }
 
+constexpr int kSparseWarps = 16;                 // k_sparse_smem: warps per persistent CTA
+constexpr int kSparsePend = 96;                  // pending deep walks a warp can hold before it must drain
 constexpr int kQuantColShift = 7;                // Q4 word, compact form: column index in bits 7.. (the wide
                                                  // form puts it at log2(128 * tile slots): the field is then
                                                  // the byte offset of the column row in the tile region)
@@ -49,6 +51,11 @@ struct HostPack {
   std::vector<uint2> sparse8;         // sparse, when the fields fit: {val, leaf<<31 | def_left<<30 | (left_idx - own index)<<fid_bits | fid}
   int sparse_fid_bits = 0;
   std::vector<int64_t> tree_offsets;  // sparse: [T+1]
+  // T8 (sparse forests through shared memory): every tree renumbered breadth-first, 8 B/node as S8;
+  // the first sp_cut nodes of each tree ("top") are what a chunk keeps in shared memory
+  std::vector<uint2> sp_full;         // [total] breadth-first S8 nodes, same tree_offsets
+  std::vector<int32_t> sp_orig;       // [total] breadth-first index -> caller's node index inside the tree
+  std::vector<uint2> sp_top;          // [sp_chunks * sp_tpc][sp_cut]; short trees padded with leaf 0.0
   // I8
   int tpad = 0;                       // trees padded to a multiple of 32
   std::vector<uint2> inter;           // [N][tpad]
@@ -111,6 +118,12 @@ struct tahoe_forest {
   int quant_stride = 1;          // k_quantize keeps every quant_stride-th threshold of a column in shared memory
   size_t quant_smem = 0;
 
+  // sparse shared-memory plan (plan_sparse_smem, at create): k_sparse_smem keeps the first sp_cut
+  // breadth-first nodes of sp_tpc trees in shared memory; deeper nodes are walked in L2 (sp_full)
+  int sp_cut = 0, sp_tpc = 0, sp_chunks = 0;
+  size_t sp_smem = 0;
+  double sp_overflow = 0.0;      // expected walks per (row, tree) that leave the top, children equally likely
+
   // SHARED_DATA plan (plan_shared_data, at create): teams of team_warps warps share a row
   int sd_teams = 0, sd_team_warps = 1, sd_group = 1;
   int sd_top = 0;                // forest levels copied to shared memory
@@ -123,6 +136,9 @@ struct tahoe_forest {
   uint2* d_heap = nullptr;
   uint4* d_sparse = nullptr;
   uint2* d_sparse8 = nullptr;
+  uint2* d_sp_full = nullptr;
+  int32_t* d_sp_orig = nullptr;
+  uint2* d_sp_top = nullptr;
   int64_t* d_tree_offsets = nullptr;
   uint2* d_inter = nullptr;
   int32_t* d_tree_order = nullptr;
@@ -179,6 +195,7 @@ struct PredictArgs {
 int launch_direct(tahoe_forest* f, const PredictArgs& a, bool rows_in_smem, int* launches);
 int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches);
 int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches);
+int launch_sparse_smem(tahoe_forest* f, const PredictArgs& a, int* launches);   // kernels_sparse_smem.cu
 int query_device(tahoe_forest* f);
 int ensure_workspace(tahoe_forest* f, Workspace* ws, size_t rows);
 

@@ -70,6 +70,7 @@ static void swap_subtrees(TreeScratch& t, int64_t a, int64_t b, int64_t npt) {
 }
 
 static int build_quant(tahoe_forest* f, const tahoe_dense_node_t* nodes);
+static void plan_sparse_smem(tahoe_forest* f, const tahoe_sparse_node_t* nodes);
 
 int pack_dense(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
   const int T = f->params.num_trees, d = f->params.depth, C = f->params.num_cols;
@@ -473,7 +474,108 @@ int pack_sparse(tahoe_forest* f, const tahoe_sparse_node_t* nodes, const float* 
   f->node_width = width_rule(max_fid);
   f->mean_depth = T ? depth_acc / T : 0.0;
   f->quant = false;
+  plan_sparse_smem(f, nodes);
   return TAHOE_OK;
+}
+
+// ---- T8: sparse forests through shared memory ------------------------------------------------
+// Deep unbalanced trees do not fit shared memory, but their walks are short: most end within a few
+// levels of the root.  Each tree is renumbered breadth-first (the top of the tree comes first) and
+// the first `cut` nodes of every tree of a chunk are kept in shared memory; a walk that steps past
+// them is finished in L2 on the full breadth-first copy.  The cut balances chunk passes (each one
+// re-streams the sample tiles) against those deep walks.
+static void plan_sparse_smem(tahoe_forest* f, const tahoe_sparse_node_t* nodes) {
+  HostPack& h = f->host;
+  const int T = f->params.num_trees, C = f->params.num_cols;
+  f->sp_cut = f->sp_tpc = f->sp_chunks = 0;
+  f->sp_smem = 0;
+  if (h.sparse8.empty() || T < 1) return;         // the 8-byte node fields must fit
+  const int fb = h.sparse_fid_bits;
+  const uint64_t max_delta = (1ull << (30 - fb)) - 1;
+  const size_t tile_bytes = (size_t)kSparseWarps * C * 128;      // one float tile per warp
+  const size_t fixed = tile_bytes + (size_t)kSparseWarps * kSparsePend * 8 + 1024;
+  if (fixed + 4096 > (size_t)f->smem_optin) return;
+  const size_t tree_budget = (size_t)f->smem_optin - fixed;
+
+  // breadth-first renumbering; level and reach probability (children equally likely) per node
+  const int64_t total = h.tree_offsets[T];
+  h.sp_full.assign((size_t)total, make_uint2(0, kMetaLeaf));
+  h.sp_orig.assign((size_t)total, 0);
+  std::vector<int32_t> newidx, order;
+  int64_t max_n = 0;
+  // over_by_cut[j]: expected deep walks per (row, forest) for cut = 32 << j
+  const int kCuts = 9;
+  double over_by_cut[kCuts] = {0};
+  for (int t = 0; t < T; ++t) {
+    const int64_t base = h.tree_offsets[t], n = h.tree_offsets[t + 1] - base;
+    max_n = std::max(max_n, n);
+    newidx.assign((size_t)n, -1);
+    order.clear();
+    order.push_back(0);
+    newidx[0] = 0;
+    for (size_t q = 0; q < order.size(); ++q) {
+      const int32_t k = order[q];
+      const tahoe_sparse_node_t& nd = nodes[base + k];
+      if (nd.bits < 0) continue;
+      if (order.size() + 2 > (size_t)n) { h.sp_full.clear(); h.sp_orig.clear(); return; }   // shared children: not a tree
+      for (int c = 0; c < 2; ++c) {
+        newidx[nd.left_idx + c] = (int32_t)order.size();
+        order.push_back(nd.left_idx + c);
+      }
+    }
+    // reach probabilities in breadth-first numbering
+    std::vector<double> pr(order.size(), 0.0);
+    pr[0] = 1.0;
+    for (size_t q = 0; q < order.size(); ++q) {
+      const tahoe_sparse_node_t& nd = nodes[base + order[q]];
+      uint32_t y;
+      if (nd.bits < 0) {
+        y = kMetaLeaf;
+      } else {
+        const int64_t nl = newidx[nd.left_idx];
+        if ((uint64_t)(nl - (int64_t)q) > max_delta) { h.sp_full.clear(); h.sp_orig.clear(); return; }
+        y = ((uint32_t)nd.bits & kMetaDefLeft) | ((uint32_t)(nl - (int64_t)q) << fb) |
+            ((uint32_t)nd.bits & ((1u << fb) - 1u));
+        pr[nl] = pr[nl + 1] = 0.5 * pr[q];
+        for (int j = 0; j < kCuts; ++j) {
+          const int64_t cut = (int64_t)32 << j;
+          if ((int64_t)q < cut && nl + 1 >= cut) over_by_cut[j] += (nl >= cut ? 2 : 1) * 0.5 * pr[q];
+        }
+      }
+      h.sp_full[base + q] = make_uint2(f2u(nd.val), y);
+      h.sp_orig[base + q] = order[q];
+    }
+  }
+  // cut: a power of two (or, capped, the longest tree), cheapest under
+  //   chunks * (one pass of the tile stream + per-tile fixed cost) + deep walks * their L2 cost
+  int best_j = -1;
+  double best_cost = 0.0;
+  int want = 0;
+  if (const char* e = std::getenv("TAHOE_SPARSE_CUT")) want = std::atoi(e);
+  for (int j = 0; j < kCuts; ++j) {
+    const int64_t cut = (int64_t)32 << j;
+    if (want && cut != want) continue;
+    const size_t tpc = tree_budget / ((size_t)cut * 8);
+    if (tpc < 1) break;
+    const double chunks = std::ceil((double)T / (double)std::min<size_t>(tpc, (size_t)T));
+    const double cost = chunks * 7.0e-11 + over_by_cut[j] * 4.7e-11;
+    if (best_j < 0 || cost < best_cost) { best_j = j; best_cost = cost; }
+    if (cut >= max_n) break;                       // every tree already whole
+  }
+  if (best_j < 0) { h.sp_full.clear(); h.sp_orig.clear(); return; }
+  const int64_t cut = (int64_t)32 << best_j;
+  f->sp_cut = (int)cut;
+  f->sp_tpc = (int)std::min<size_t>(tree_budget / ((size_t)cut * 8), (size_t)T);
+  if (const char* e = std::getenv("TAHOE_SPARSE_TPC")) f->sp_tpc = std::max(1, std::min(f->sp_tpc, std::atoi(e)));
+  f->sp_chunks = (T + f->sp_tpc - 1) / f->sp_tpc;
+  f->sp_overflow = over_by_cut[best_j] / T;
+  f->sp_smem = fixed + (size_t)f->sp_tpc * cut * 8;
+  h.sp_top.assign((size_t)f->sp_chunks * f->sp_tpc * cut, make_uint2(0, kMetaLeaf));
+  for (int t = 0; t < T; ++t) {
+    const int64_t base = h.tree_offsets[t], n = h.tree_offsets[t + 1] - base;
+    std::copy(h.sp_full.begin() + base, h.sp_full.begin() + base + std::min<int64_t>(n, cut),
+              h.sp_top.begin() + (size_t)t * cut);
+  }
 }
 
 // ---- shared-memory chunk plan ------------------------------------------------------------
@@ -589,6 +691,9 @@ int upload(tahoe_forest* f) {
   if ((rc = to_device(&f->d_heap, h.heap))) return rc;
   if ((rc = to_device(&f->d_sparse, h.sparse))) return rc;
   if ((rc = to_device(&f->d_sparse8, h.sparse8))) return rc;
+  if ((rc = to_device(&f->d_sp_full, h.sp_full))) return rc;
+  if ((rc = to_device(&f->d_sp_orig, h.sp_orig))) return rc;
+  if ((rc = to_device(&f->d_sp_top, h.sp_top))) return rc;
   if ((rc = to_device(&f->d_tree_offsets, h.tree_offsets))) return rc;
   if ((rc = to_device(&f->d_inter, h.inter))) return rc;
   if ((rc = to_device(&f->d_tree_order, h.tree_order))) return rc;

@@ -172,3 +172,33 @@ def quant_traverse(qwords, leaf_origin, T, depth, F, col_mask, miss_code, col_sh
         vals[:, t] = q[t, n].view(np.float32)
         ids[:, t] = lo[t, n - L]
     return vals, ids
+
+
+def sparse_bfs_traverse(nodes8, orig, offsets, fid_bits, cut, data, missing):
+    """T8: breadth-first 8-byte sparse nodes {val, leaf<<31 | def_left<<30 | delta<<fid_bits | fid}.
+    -> (values [R,T], caller's leaf node index [R,T], walks that stepped past `cut` [R,T] bool)"""
+    nd = nodes8.reshape(-1, 2)
+    T = len(offsets) - 1
+    R = data.shape[0]
+    rows = np.arange(R)
+    vals = np.zeros((R, T), np.float32)
+    ids = np.zeros((R, T), np.int32)
+    deep = np.zeros((R, T), bool)
+    fmask = (1 << fid_bits) - 1
+    for t in range(T):
+        base = int(offsets[t])
+        n = np.zeros(R, np.int64)
+        while True:
+            e = nd[base + n]
+            leaf = (e[:, 1] & LEAF) != 0
+            if leaf.all():
+                break
+            fid = np.where(leaf, 0, (e[:, 1] & fmask).astype(np.int64))
+            c = _right(data[rows, fid], e[:, 0].view(np.float32), (e[:, 1] & DEFLEFT) != 0, missing)
+            delta = ((e[:, 1] & 0x3FFFFFFF) >> fid_bits).astype(np.int64)
+            assert np.all(delta[~leaf] >= 1)
+            n = np.where(leaf, n, n + delta + c)
+            deep[:, t] |= n >= cut
+        vals[:, t] = nd[base + n, 0].view(np.float32)
+        ids[:, t] = orig[base + n]
+    return vals, ids, deep

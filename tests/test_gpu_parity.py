@@ -105,9 +105,36 @@ def test_sparse_forest(oracle):
                 assert np.array_equal(ids, wids) and bits_equal(got, want), (group, s)
         finally:
             del os.environ["TAHOE_DIRECT_GROUP"]
-    for s in (api.SHARED_DATA, api.SHARED_FOREST, api.SPLIT_SHARED_FOREST):
-        with pytest.raises(api.NotApplicable):
-            _run(f, data, s)
+    with pytest.raises(api.NotApplicable):
+        _run(f, data, api.SHARED_DATA)
+
+
+@pytest.mark.parametrize("cut,tpc,rows", [(None, None, 3000), (32, 7, 3000), (64, 64, 33), (32, 1, 2368 * 32 + 5),
+                                          (256, 20, 1)])
+def test_sparse_forest_through_shared_memory(oracle, monkeypatch, cut, tpc, rows):
+    """k_sparse_smem: tree tops in shared memory, deep walks parked and finished in L2.  Small cuts and
+    chunk sizes force many parked walks, partial drains and several chunks; leaf ids stay exact, the
+    score is a re-ordered float sum."""
+    if cut is not None:
+        monkeypatch.setenv("TAHOE_SPARSE_CUT", str(cut))
+        monkeypatch.setenv("TAHOE_SPARSE_TPC", str(tpc))
+    sp, offs, w, lv = synth.gen_sparse_forest(4242, 64, 12, 50)
+    data = synth.gen_data(4343, rows, 50, miss_frac=0.01, nan_frac=0.005)
+    want, wids = oracle.predict_sparse(sp, offs, data, -999.0, want_leaf_ids=True)
+    f = api.Forest.from_sparse(sp, offs, 50, weights=w, missing=-999.0)
+    info = f.info()
+    if cut is not None:
+        assert info.sparse_cut == cut and info.trees_per_chunk == tpc and info.num_chunks == -(-64 // tpc)
+    assert f.applicable(api.SPLIT_SHARED_FOREST, rows)
+    leafvals = np.abs(sp["val"][offs[:-1][None, :] + wids]).sum(1)       # L1 mass of each row's summands
+    got, ids = _run(f, data, api.SPLIT_SHARED_FOREST)
+    assert np.array_equal(ids, wids)
+    assert score_close(got, want, leafvals)
+    got2, _ = _run(f, data, api.SPLIT_SHARED_FOREST, want_ids=False)
+    assert bits_equal(got, got2)                                          # reproducible
+    if f.applicable(api.SHARED_FOREST, rows):
+        got3, _ = _run(f, data, api.SHARED_FOREST, want_ids=False)
+        assert bits_equal(got, got3)
 
 
 @pytest.mark.parametrize("rows", [0, 1, 31, 32, 33, 2368 * 32 + 5])

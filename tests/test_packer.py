@@ -182,7 +182,10 @@ def test_sparse_pack_validation():
     f = api.Forest.from_sparse(sp, offs, 6, weights=w, missing=-999.0)
     inf = f.info()
     assert inf.is_sparse == 1 and inf.num_nodes == sp.shape[0] and inf.quantized == 0
-    assert not f.applicable(api.SPLIT_SHARED_FOREST, 10) and f.applicable(api.DIRECT, 10)
+    # small trees: every one is whole in shared memory, so both shared-forest strategies apply
+    assert f.applicable(api.SPLIT_SHARED_FOREST, 10) and f.applicable(api.SHARED_FOREST, 10)
+    assert not f.applicable(api.SHARED_DATA, 10) and f.applicable(api.DIRECT, 10)
+    assert inf.sparse_deep_walks == 0.0 and inf.num_chunks == 1
     bad = sp.copy()
     bad["left_idx"][0] = 0
     with pytest.raises(api.TahoeError):
@@ -198,3 +201,33 @@ def test_predict_without_gpu_fails_loudly():
     out = np.zeros(c["rows"], np.float32)
     with pytest.raises(api.TahoeError):
         f.predict_host(np.ascontiguousarray(c["data"]), out, strategy=api.DIRECT)
+
+
+@pytest.mark.parametrize("cut", [None, 32, 64])
+def test_sparse_breadth_first_layout(oracle, cut, monkeypatch):
+    """T8 (sparse forests through shared memory): the breadth-first renumbering walks to the oracle's
+    leaves, the shared-memory image is its per-tree prefix, and the planner's deep-walk estimate is sane."""
+    if cut is not None:
+        monkeypatch.setenv("TAHOE_SPARSE_CUT", str(cut))
+    sp, offs, w, lv = synth.gen_sparse_forest(99, 24, 12, 20)
+    data = synth.gen_data(98, 600, 20, miss_frac=0.02, nan_frac=0.01)
+    want, wids = oracle.predict_sparse(sp, offs, data, -999.0, want_leaf_ids=True)
+    f = api.Forest.from_sparse(sp, offs, 20, weights=w, missing=-999.0)
+    info = f.info()
+    assert info.sparse_cut >= 32 and info.trees_per_chunk >= 1 and info.sparse_fid_bits >= 1
+    assert cut is None or info.sparse_cut == cut
+    nodes8 = f.export(api.EXPORT_SPARSE_BFS, np.uint32)
+    orig = f.export(api.EXPORT_SPARSE_BFS_ORIG, np.int32)
+    vals, ids, deep = emulate.sparse_bfs_traverse(nodes8, orig, offs, info.sparse_fid_bits, info.sparse_cut,
+                                                  data, -999.0)
+    assert np.array_equal(ids, wids)
+    np.testing.assert_allclose(vals.sum(1, dtype=np.float64), want.astype(np.float64), rtol=1e-5, atol=1e-5)
+    top = f.export(api.EXPORT_SPARSE_TOP, np.uint32).reshape(-1, info.sparse_cut, 2)
+    full = nodes8.reshape(-1, 2)
+    assert top.shape[0] == info.num_chunks * info.trees_per_chunk >= 24
+    for t in range(24):
+        n = min(int(offs[t + 1] - offs[t]), info.sparse_cut)
+        assert np.array_equal(top[t, :n], full[offs[t]:offs[t] + n])
+        assert np.all(top[t, n:, 1] == 0x80000000) and np.all(top[t, n:, 0] == 0)
+    # uniform random features: the measured share of deep walks is near the planner's estimate
+    assert abs(deep.mean() - info.sparse_deep_walks) < 0.05
