@@ -489,7 +489,7 @@ static void plan_sparse_smem(tahoe_forest* f, const tahoe_sparse_node_t* nodes) 
   const int T = f->params.num_trees, C = f->params.num_cols;
   f->sp_cut = f->sp_tpc = f->sp_chunks = 0;
   f->sp_smem = 0;
-  if (h.sparse8.empty() || T < 1) return;         // the 8-byte node fields must fit
+  if (h.sparse8.empty() || T < 1 || C > 64) return;   // the 8-byte node fields must fit (top form: 6-bit fid)
   const int fb = h.sparse_fid_bits;
   const uint64_t max_delta = (1ull << (30 - fb)) - 1;
   const size_t tile_bytes = (size_t)kSparseWarps * C * 128;      // one float tile per warp
@@ -504,7 +504,7 @@ static void plan_sparse_smem(tahoe_forest* f, const tahoe_sparse_node_t* nodes) 
   std::vector<int32_t> newidx, order;
   int64_t max_n = 0;
   // over_by_cut[j]: expected deep walks per (row, forest) for cut = 32 << j
-  const int kCuts = 9;
+  const int kCuts = 7;   // cut <= 2048: the shared-memory node form keeps delta * 8 in 15 bits
   double over_by_cut[kCuts] = {0};
   for (int t = 0; t < T; ++t) {
     const int64_t base = h.tree_offsets[t], n = h.tree_offsets[t + 1] - base;
@@ -570,11 +570,20 @@ static void plan_sparse_smem(tahoe_forest* f, const tahoe_sparse_node_t* nodes) 
   f->sp_chunks = (T + f->sp_tpc - 1) / f->sp_tpc;
   f->sp_overflow = over_by_cut[best_j] / T;
   f->sp_smem = fixed + (size_t)f->sp_tpc * cut * 8;
-  h.sp_top.assign((size_t)f->sp_chunks * f->sp_tpc * cut, make_uint2(0, kMetaLeaf));
+  h.sp_top.assign((size_t)f->sp_chunks * f->sp_tpc * cut, make_uint2(0, 1u));   // padding: leaf 0.0
   for (int t = 0; t < T; ++t) {
     const int64_t base = h.tree_offsets[t], n = h.tree_offsets[t + 1] - base;
-    std::copy(h.sp_full.begin() + base, h.sp_full.begin() + base + std::min<int64_t>(n, cut),
-              h.sp_top.begin() + (size_t)t * cut);
+    // shared-memory form of a top node (kernels_sparse_smem.cu):
+    //   y = (delta * 8) << 17 | fid << 11 | def_left << 1 | leaf   (delta <= cut + 1 < 4096)
+    for (int64_t q = 0; q < std::min<int64_t>(n, cut); ++q) {
+      const uint2 e = h.sp_full[base + q];
+      uint32_t y = 1u;
+      if (!(e.y & kMetaLeaf)) {
+        const uint32_t delta = (e.y & 0x3FFFFFFFu) >> fb, fid = e.y & ((1u << fb) - 1u);
+        y = ((delta * 8u) << 17) | (fid << 11) | ((e.y & kMetaDefLeft) ? 2u : 0u);
+      }
+      h.sp_top[(size_t)t * cut + q] = make_uint2(e.x, y);
+    }
   }
 }
 

@@ -209,10 +209,10 @@ def test_sparse_breadth_first_layout(oracle, cut, monkeypatch):
     leaves, the shared-memory image is its per-tree prefix, and the planner's deep-walk estimate is sane."""
     if cut is not None:
         monkeypatch.setenv("TAHOE_SPARSE_CUT", str(cut))
-    sp, offs, w, lv = synth.gen_sparse_forest(99, 24, 12, 20)
-    data = synth.gen_data(98, 600, 20, miss_frac=0.02, nan_frac=0.01)
+    sp, offs, w, lv = synth.gen_sparse_forest(99, 24, 12, 50)
+    data = synth.gen_data(98, 600, 50, miss_frac=0.02, nan_frac=0.01)
     want, wids = oracle.predict_sparse(sp, offs, data, -999.0, want_leaf_ids=True)
-    f = api.Forest.from_sparse(sp, offs, 20, weights=w, missing=-999.0)
+    f = api.Forest.from_sparse(sp, offs, 50, weights=w, missing=-999.0)
     info = f.info()
     assert info.sparse_cut >= 32 and info.trees_per_chunk >= 1 and info.sparse_fid_bits >= 1
     assert cut is None or info.sparse_cut == cut
@@ -225,9 +225,19 @@ def test_sparse_breadth_first_layout(oracle, cut, monkeypatch):
     top = f.export(api.EXPORT_SPARSE_TOP, np.uint32).reshape(-1, info.sparse_cut, 2)
     full = nodes8.reshape(-1, 2)
     assert top.shape[0] == info.num_chunks * info.trees_per_chunk >= 24
-    for t in range(24):
+    fb = info.sparse_fid_bits
+    for t in range(24):          # shared-memory form: y = (delta*8) << 17 | fid << 11 | def_left << 1 | leaf
         n = min(int(offs[t + 1] - offs[t]), info.sparse_cut)
-        assert np.array_equal(top[t, :n], full[offs[t]:offs[t] + n])
-        assert np.all(top[t, n:, 1] == 0x80000000) and np.all(top[t, n:, 0] == 0)
+        src, img = full[offs[t]:offs[t] + n], top[t, :n]
+        leaf = (src[:, 1] & 0x80000000) != 0
+        assert np.array_equal(img[:, 0], src[:, 0]) and np.array_equal((img[:, 1] & 1) != 0, leaf)
+        assert np.all(img[leaf, 1] == 1)
+        y = src[~leaf, 1]
+        want_y = ((((y & 0x3FFFFFFF) >> fb) * 8) << 17) | ((y & ((1 << fb) - 1)) << 11) | ((y >> 30) & 1) << 1
+        assert np.array_equal(img[~leaf, 1], want_y.astype(np.uint32))
+        # the fields the kernel extracts do not overlap
+        assert np.array_equal(img[~leaf, 1] >> 17, ((y & 0x3FFFFFFF) >> fb) * 8)
+        assert np.array_equal((img[~leaf, 1] & 0x1F800) >> 11, y & ((1 << fb) - 1))
+        assert np.all(top[t, n:, 1] == 1) and np.all(top[t, n:, 0] == 0)
     # uniform random features: the measured share of deep walks is near the planner's estimate
     assert abs(deep.mean() - info.sparse_deep_walks) < 0.05
