@@ -64,19 +64,19 @@ constexpr double kL1Bytes = 200e3;          // rows of the resident threads that
 constexpr double kRowGather = 1.7e12;       // B/s of 32-byte row sectors gathered through L2
 constexpr double kForestHalf = 80e6;        // forest bytes at which the L2-gather rates halve
 constexpr double kTeamLevel = 0.7e-6;       // SHARED_DATA: one tree level of a row's walk (latency-bound)
-constexpr double kSharedDataRate = 4.8e11;  // visits/s (slot-levels), SHARED_DATA
-constexpr double kRowStream = 3.0e12;       // B/s of sample rows through a TMA-fed SHARED_DATA kernel
+constexpr double kSharedDataRate = 7.0e11;  // visits/s (slot-levels), SHARED_DATA
+constexpr double kRowStream = 3.7e12;       // B/s of sample rows through a TMA-fed SHARED_DATA kernel
 constexpr double kSmemVisit = 3.3e-13;      // s per visit, shared-memory forest, 16 warps x 6 trees (unit plan)
 constexpr double kTileStream = 5.0e12;      // B/s of rank tiles re-read once per chunk (half hidden)
 constexpr double kChunkFixed = 3.0e-6;      // stage one chunk + barrier
 constexpr double kTileLevel = 75e-9;        // one level of one traversal group of a tile (latency-bound)
 constexpr double kQuantRate = 1.7e12;       // B/s in+out of k_quantize, whole table in shared memory
-constexpr double kQuantRateStrided = 1.0e12;
-constexpr double kSparseVisit = 6.0e-13;      // s per node visit, sparse tree tops in shared memory (free-running lanes)
-constexpr double kSparseChunkRow = 7.0e-11;   // s per row per chunk: tile re-stream + refill latency share
-constexpr double kSparseDeep = 4.7e-11;       // s per walk that leaves the tops and is finished in L2
-constexpr double kSparseStep = 60e-9;         // one step of a lane's two interleaved sequences (latency)
-constexpr double kSparseTileFixed = 2e-6;     // refill a warp's tile buffer + final drain  // ... every 2^k-th threshold there, rest probed in L2
+constexpr double kQuantRateStrided = 1.0e12;   // ... every 2^k-th threshold there, rest probed in L2
+constexpr double kSparseVisit = 2.3e-12;      // s per node visit, sparse tree tops in shared memory (free-running lanes)
+constexpr double kSparseChunkRow = 1.0e-10;   // s per row per chunk: tile re-stream + refill latency share
+constexpr double kSparseDeep = 3.1e-11;       // s per walk that leaves the tops and is finished in L2
+constexpr double kSparseStep = 300e-9;        // one step of a lane's two interleaved sequences (latency)
+constexpr double kSparseTileFixed = 8e-6;     // refill a warp's tile buffer + final drain
 }  // namespace model
 
 static double forest_bytes(const tahoe_forest* f) {
@@ -100,12 +100,18 @@ static int select_strategy(const tahoe_forest* f, size_t rows_, double* out) {
         case TAHOE_STRATEGY_DIRECT:
         case TAHOE_STRATEGY_SHARED_DATA_PER_THREAD: {
           const bool staged = s == TAHOE_STRATEGY_SHARED_DATA_PER_THREAD;
-          const double rate = (staged ? kPerThreadRate : kDirectRate) * l2_scale;
+          // sparse trees are uneven: a warp's lanes idle until its deepest walk ends (14 of 32 lanes
+          // active on config 4), and staging rows does not pay for itself there
+          const double rate = (f->sparse ? kDirectRate / (staged ? 2.2 : 1.6) : (staged ? kPerThreadRate : kDirectRate)) * l2_scale;
           const double lat = T * dwalk * kL2Visit * (staged ? 0.96 : 1.0);
           double thr = R * T * dbar / rate;
           // DIRECT gathers features straight from global memory: once the resident threads' rows
           // outgrow L1, every visit pulls a 32-byte sector of its row through L2
-          if (!staged && C * 4.0 * 2048.0 > kL1Bytes) thr += R * T * dbar * 32.0 / kRowGather;
+          // (the share of visits that miss grows with how far the rows overflow L1)
+          if (!staged && C * 4.0 * 2048.0 > kL1Bytes) {
+            const double miss = std::min(1.0, (C * 4.0 * 2048.0 / kL1Bytes - 1.0) / 8.0);
+            thr += miss * R * T * dbar * 32.0 / kRowGather;
+          }
           t = kLaunch + std::max(lat, thr);
           break;
         }

@@ -558,7 +558,7 @@ static void plan_sparse_smem(tahoe_forest* f, const tahoe_sparse_node_t* nodes) 
     const size_t tpc = tree_budget / ((size_t)cut * 8);
     if (tpc < 1) break;
     const double chunks = std::ceil((double)T / (double)std::min<size_t>(tpc, (size_t)T));
-    const double cost = chunks * 7.0e-11 + over_by_cut[j] * 4.7e-11;
+    const double cost = chunks * 1.0e-10 + over_by_cut[j] * 3.1e-11;   // B200 fit: profiles/r01_sparse_notes.md
     if (best_j < 0 || cost < best_cost) { best_j = j; best_cost = cost; }
     if (cut >= max_n) break;                       // every tree already whole
   }
