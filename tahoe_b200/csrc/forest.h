@@ -36,7 +36,7 @@ constexpr int kStagedMaxCols = 32;               // register-staged tiles keep o
 constexpr int ilog2_c(int v) { return v <= 1 ? 0 : 1 + ilog2_c(v >> 1); }
 
 constexpr int kSparseWarps = 16;                 // k_sparse_smem: warps per persistent CTA
-constexpr int kSparsePend = 128;                 // pending deep walks a warp can hold before it must drain
+constexpr int kSparsePend = 160;                 // pending deep walks a warp can hold before it must drain
 constexpr int kQuantColShift = 7;                // Q4 word, compact form: column index in bits 7.. (the wide
                                                  // form puts it at log2(128 * tile slots): the field is then
                                                  // the byte offset of the column row in the tile region)

@@ -13,7 +13,7 @@
 //                   every row tile through them.  thread = sample.  Lanes are FREE-RUNNING: a lane
 //                   that reaches a leaf starts its next tree at once instead of idling until the
 //                   warp's deepest walk ends (in shared memory there is no sector sharing to lose),
-//                   two independent tree sequences per lane for latency.  A walk that steps past the
+//                   three independent tree sequences per lane for latency.  A walk that steps past the
 //                   cut is parked in a per-warp list; whenever 32 are parked the warp finishes them
 //                   together in L2 on the full breadth-first copy, one walk per lane, and hands the
 //                   leaf values back to the owning lanes with shuffles.
@@ -236,6 +236,9 @@ __global__ void __launch_bounds__(kSparseWarps * 32, 1) k_sparse_smem(SparseSmem
 #pragma unroll
           for (int g = 0; g < G; ++g) left |= rem[g];          // rem >= 0
           if (!__any_sync(0xffffffffu, left != 0)) break;
+          bool deep[G];
+          uint32_t a2[G];
+          bool any_deep = false;
 #pragma unroll
           for (int g = 0; g < G; ++g) {
             const bool act = rem[g] != 0;
@@ -245,10 +248,11 @@ __global__ void __launch_bounds__(kSparseWarps * 32, 1) k_sparse_smem(SparseSmem
             if (MISSING) {
               if (fabsf(v - p.missing) <= 1.0e-6f) c = !(e[g].y & kTopDefLeft);   // BaseTahoeTest.h:451-452
             }
-            const uint32_t a2 = a[g] + (e[g].y >> 17) + (c ? 8u : 0u);
-            const bool past = a2 >= lim[g];
+            a2[g] = a[g] + (e[g].y >> 17) + (c ? 8u : 0u);
+            const bool past = a2[g] >= lim[g];
             const bool done = act & (leaf | past);
-            const bool deep = act & !leaf & past;
+            deep[g] = act & !leaf & past;
+            any_deep |= deep[g];
             accg[g] += (act & leaf) ? __uint_as_float(e[g].x) : 0.0f;
             if (LEAF_IDS) {
               if (act & leaf) {
@@ -256,17 +260,27 @@ __global__ void __launch_bounds__(kSparseWarps * 32, 1) k_sparse_smem(SparseSmem
                 p.leaf_ids[row * (size_t)p.num_trees + tr] = p.orig[p.tree_offsets[tr] + ((a[g] - (lim[g] - cut8)) >> 3)];
               }
             }
-            const uint32_t park = __ballot_sync(0xffffffffu, deep);
-            if (park) {
-              if (deep)
+            // next node of the sequence (the parked walk, if any, is recorded below from a2 / lim / rem)
+            const uint32_t an = done ? lim[g] : (act ? a2[g] : a[g]);
+            e[g] = lds_u64(an);            // a finished sequence sits on the next tree's root or the sentinel leaf
+            a[g] = an;
+          }
+          // one vote for all sequences; parking is the rare path
+          if (__any_sync(0xffffffffu, any_deep)) {
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+              const uint32_t park = __ballot_sync(0xffffffffu, deep[g]);
+              if (deep[g])
                 pend[count + __popc(park & lt_mask)] =
-                    make_uint2(((uint32_t)(tlast[g] - rem[g]) << 5) | lane, (a2 - (lim[g] - cut8)) >> 3);
+                    make_uint2(((uint32_t)(tlast[g] - rem[g]) << 5) | lane, (a2[g] - (lim[g] - cut8)) >> 3);
               count += __popc(park);
             }
-            a[g] = done ? lim[g] : (act ? a2 : a[g]);
+          }
+#pragma unroll
+          for (int g = 0; g < G; ++g) {
+            const bool done = a[g] == lim[g];          // the sequence moved on to the next tree
             lim[g] += done ? cut8 : 0u;
             rem[g] -= done ? 1 : 0;
-            e[g] = lds_u64(a[g]);          // a finished sequence sits on the next tree's root or the sentinel leaf
           }
           while (count >= 32) drain(32, std::true_type{});   // keeps count + 32*G within kSparsePend
         }
@@ -326,9 +340,10 @@ int launch_sparse_smem(tahoe_forest* f, const PredictArgs& a, int* launches) {
     ++*launches;
     return TAHOE_OK;
   };
-  int group = 2;
+  int group = 3;   // measured on config 4: 28.7 / 24.6 / 23.4 / 24.5 ms for 1 / 2 / 3 / 4 sequences per lane
   if (const char* e = std::getenv("TAHOE_SPARSE_GROUP")) group = std::atoi(e);
   if (a.leaf_ids) rc = go(k_sparse_smem<true, 2>);
+  else if (group == 4) rc = go(k_sparse_smem<false, 4>);
   else rc = group == 3 ? go(k_sparse_smem<false, 3>) : (group == 1 ? go(k_sparse_smem<false, 1>) : go(k_sparse_smem<false, 2>));
   if (ev && rc == TAHOE_OK) TAHOE_CUDA(cudaEventRecord(ev[2], a.stream));
   return rc;
