@@ -139,7 +139,8 @@ static int select_strategy(const tahoe_forest* f, size_t rows_, double* out) {
           const double tiles_per_warp = std::ceil(R / 32.0 / ((double)f->sm_count * f->warps));
           const double groups = (double)f->trees_per_chunk / std::max(f->group, 1);
           const double lat = f->num_chunks * (kChunkFixed + tiles_per_warp * groups * f->depth * kTileLevel);
-          const double thr = visits * kSmemVisit * plan + 0.5 * f->num_chunks * R * C * 4.0 / kTileStream;
+          const double thr = kSmemVisit * (visits * plan + f->num_chunks * R *
+                             smem_tile_cost(f->params.num_cols, f->staged, f->trees_per_chunk, f->depth));
           const double quant = kLaunch + R * C * 8.0 / (f->quant_stride > 1 ? kQuantRateStrided : kQuantRate);
           t = kLaunch + quant + std::max(lat, thr);
           break;

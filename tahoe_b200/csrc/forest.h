@@ -113,6 +113,10 @@ struct tahoe_forest {
   int warps = tahoe::kSmemMaxWarps;  // warps per CTA of k_smem_forest
   bool staged = false;           // one tile buffer per warp, next tile staged in registers (else 2, by TMA)
   int slots = 0;                 // tile buffers per CTA = warps * (staged ? 1 : 2), a power of two
+  // tile region of k_smem_forest: word (col, slot, lane) at col*col_stride + slot*slot_stride + lane*4
+  // (wide: column-major, the column field of a node sits at bit 7 + log2 slots; compact: slot-major
+  // with the columns rounded up to a power of two, column field at bit 7)
+  uint32_t tile_col_stride = 0, tile_slot_stride = 0, tile_region = 0;
   int qwords_trees = 0;          // trees in d_qwords: num_trees padded with all-zero trees (leaf value +0.0f)
   size_t smem_bytes = 0;
   int quant_stride = 1;          // k_quantize keeps every quant_stride-th threshold of a column in shared memory
@@ -182,6 +186,7 @@ int upload(tahoe_forest* f);
 void plan_chunks(tahoe_forest* f);
 void plan_shared_data(tahoe_forest* f);   // teams / top levels / B32 blocks; needs host.inter and query_device
 double smem_visit_cost(int warps, int group, bool staged);   // relative cost of a node visit under a plan
+double smem_tile_cost(int cols, bool staged, int trees_per_chunk, int depth);   // one tile pass, in node visits
 
 // launchers (kernels_*.cu); each returns a status and adds to *launches
 struct PredictArgs {

@@ -192,8 +192,7 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.padded_trees = f->qwords_trees;
   p.trees_per_chunk = f->trees_per_chunk; p.num_chunks = f->num_chunks;
   p.col_mask = f->col_mask; p.miss_code = f->miss_code;
-  p.col_stride = 128u * (uint32_t)f->slots;
-  p.col_lshift = ilog2_c(f->slots);
+  p.col_stride = f->tile_col_stride; p.slot_stride = f->tile_slot_stride; p.tile_region = f->tile_region;
   p.preds = a.preds; p.leaf_ids = a.leaf_ids;
   p.leaf_origin = f->d_leaf_origin;
   p.tf = Transform{f->params.output, (float)f->params.num_trees, f->params.threshold,

@@ -1,7 +1,7 @@
 // kernels_smem_depth.cu -- the instantiations of k_smem_forest for ONE tree depth.
 // Compiled 14 times (-DTAHOE_DEPTH=1..14, tahoe_b200/build.py) so the builds run in parallel; each
 // object exports launch_smem_depth_<N>(), which picks the instantiation the handle's plan names:
-// trees per group (1..6), wide/compact column field, TMA double-buffered or register-staged tiles.
+// trees per group (1..6), TMA double-buffered or register-staged tiles.
 #include "kernels_smem_traverse.cuh"
 
 #ifndef TAHOE_DEPTH
@@ -21,25 +21,10 @@ int TAHOE_CAT(launch_smem_depth_, TAHOE_DEPTH)(tahoe_forest* f, const SmemParams
     TAHOE_CUDA(cudaGetLastError());
     return TAHOE_OK;
   };
-  const bool wide = f->col_shift != kQuantColShift;
-  const int sel = (wide ? 1 : 0) | (f->staged ? 2 : 0);
   // the leaf-id instantiation is the checking path: one tree at a time keeps the build small
-  if (p.leaf_ids) {
-    switch (sel) {
-      case 0: return go(k_smem_forest<D, 1, true, false, false>);
-      case 1: return go(k_smem_forest<D, 1, true, true, false>);
-      case 2: return go(k_smem_forest<D, 1, true, false, true>);
-      default: return go(k_smem_forest<D, 1, true, true, true>);
-    }
-  }
-#define TAHOE_G_CASE(G)                                                   \
-  case G:                                                                 \
-    switch (sel) {                                                        \
-      case 0: return go(k_smem_forest<D, G, false, false, false>);        \
-      case 1: return go(k_smem_forest<D, G, false, true, false>);         \
-      case 2: return go(k_smem_forest<D, G, false, false, true>);         \
-      default: return go(k_smem_forest<D, G, false, true, true>);         \
-    }
+  if (p.leaf_ids) return f->staged ? go(k_smem_forest<D, 1, true, true>) : go(k_smem_forest<D, 1, true, false>);
+#define TAHOE_G_CASE(G) \
+  case G: return f->staged ? go(k_smem_forest<D, G, false, true>) : go(k_smem_forest<D, G, false, false>);
   switch (f->group) {
     TAHOE_G_CASE(1) TAHOE_G_CASE(2) TAHOE_G_CASE(3) TAHOE_G_CASE(4) TAHOE_G_CASE(5) TAHOE_G_CASE(6)
     default: break;

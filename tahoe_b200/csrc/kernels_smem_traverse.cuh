@@ -19,8 +19,13 @@ struct SmemParams {
   int padded_trees;         // trees in qwords: whole traversal groups, the extra ones all zero
   int trees_per_chunk, num_chunks;
   uint32_t col_mask, miss_code;
-  uint32_t col_stride;      // bytes between column rows of the tile region = 128 * tile slots
-  int col_lshift;           // compact node form: (node & col_mask) << col_lshift = column row offset
+  // tile region: word (col, slot, lane) at col*col_stride + slot*slot_stride + lane*4, and
+  // (node & col_mask) == col*col_stride, so a lane's address is one AND-OR.  Two layouts:
+  //   wide    column-major  col_stride = 128*slots, slot_stride = 128   (column field at bit 7+log2 slots)
+  //   compact slot-major    col_stride = 128, slot_stride = 128 * cols rounded up to a power of two
+  //           (column field at bit 7: for forests whose rank + column bits leave no room for the wide field)
+  uint32_t col_stride, slot_stride;
+  uint32_t tile_region;     // bytes of the tile region (the forest chunk follows it)
   float* preds;
   int32_t* leaf_ids;
   const int32_t* leaf_origin;  // [T][2^d]
@@ -30,9 +35,9 @@ struct SmemParams {
 constexpr int kSmemMaxThreads = kSmemMaxWarps * 32;
 
 // Shared-memory map of k_smem_forest (byte offsets from smem[]):
-//   [0, cols*col_stride)           tile region: word (col, slot, lane) at col*col_stride + slot*128 + lane*4
-//                                  -- all warp buffers of a column interleaved, so the region base is
-//                                  one CTA-uniform constant and a lane's address is a pure bit-field OR
+//   [0, tile_region)               tile region: word (col, slot, lane) at col*col_stride + slot*slot_stride
+//                                  + lane*4 -- the region base is one CTA-uniform constant and a
+//                                  lane's address is a pure bit-field OR
 //   [.., + trees_per_chunk*W*4)    the resident chunk of rank-quantised trees
 //   [.., + (1 + slots)*8)          mbarriers: chunk, then one per tile buffer
 // slots = warps * 2 (tiles double-buffered by TMA bulk copies) or warps * 1 (STAGED: the next tile
@@ -45,15 +50,14 @@ constexpr int kSmemMaxThreads = kSmemMaxWarps * 32;
 //   slot_lane  slot*128 + lane*4 : this lane's bank inside this warp's current tile buffer
 // a[g] is the shared ADDRESS of the current node, so one visit is six instructions:
 //   LDS  node  [a]
-//   LOP3 (node & col_mask) | slot_lane           (WIDE; the compact form adds one shift)
+//   LOP3 (node & col_mask) | slot_lane
 //   LDS  rank  [that + s_base]                   (uniform-register base, folded into the LDS)
 //   ISETP rank > node ; SEL k = right ? 4-B : -B ; IADD3 a = a + a + k      (B = tree address)
 // i.e. a' - B = 2(a - B) + 4*right, the heap step on byte offsets, with no separate address add.
 // Loads are asm so the address arithmetic stays exactly this; ptxas still interleaves the G chains.
-template <int DEPTH, int G, bool MISSING, bool WIDE>
+template <int DEPTH, int G, bool MISSING>
 __device__ __forceinline__ void traverse_group(uint32_t tree_abs, uint32_t s_base, uint32_t slot_lane,
-                                               uint32_t col_mask, int col_lshift, uint32_t miss_code,
-                                               uint32_t (&a)[G]) {
+                                               uint32_t col_mask, uint32_t miss_code, uint32_t (&a)[G]) {
   constexpr uint32_t W4 = 4u << (DEPTH + 1);  // bytes per tree
   uint32_t k0[G];
 #pragma unroll
@@ -68,8 +72,7 @@ __device__ __forceinline__ void traverse_group(uint32_t tree_abs, uint32_t s_bas
     for (int g = 0; g < G; ++g) N[g] = lds_u32(a[g]);
 #pragma unroll
     for (int g = 0; g < G; ++g) {
-      const uint32_t col_off = WIDE ? (N[g] & col_mask) : ((N[g] & col_mask) << col_lshift);
-      F[g] = lds_u32(s_base + (col_off | slot_lane));
+      F[g] = lds_u32(s_base + ((N[g] & col_mask) | slot_lane));
     }
 #pragma unroll
     for (int g = 0; g < G; ++g) {
@@ -82,11 +85,11 @@ __device__ __forceinline__ void traverse_group(uint32_t tree_abs, uint32_t s_bas
   }
 }
 
-__device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) {
-  asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+__device__ __forceinline__ void sts_u128(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
-template <int DEPTH, int G, bool LEAF_IDS, bool WIDE, bool STAGED>
+template <int DEPTH, int G, bool LEAF_IDS, bool STAGED>
 __global__ void __launch_bounds__(kSmemMaxThreads, 1) k_smem_forest(SmemParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr uint32_t W = 1u << (DEPTH + 1);      // words per tree
@@ -96,7 +99,7 @@ __global__ void __launch_bounds__(kSmemMaxThreads, 1) k_smem_forest(SmemParams p
   const int nwarps = blockDim.x >> 5;
   const int slots = nwarps * kBufs;
   const uint32_t tile_bytes = (uint32_t)p.cols * 128u;
-  const uint32_t forest_off = (uint32_t)p.cols * p.col_stride;
+  const uint32_t forest_off = p.tile_region;
   const uint32_t bars_off = forest_off + (uint32_t)p.trees_per_chunk * W * 4u;
   const uint32_t s_base = smem_u32(smem);
   const uint32_t bar_chunk = s_base + bars_off;
@@ -119,26 +122,31 @@ __global__ void __launch_bounds__(kSmemMaxThreads, 1) k_smem_forest(SmemParams p
     const uint32_t bar = bar_tile0 + b * 8;
     if (lane == 0) mbar_expect_tx(bar, tile_bytes);
     __syncwarp();
-    const uint32_t slot_off = (uint32_t)(warp * kBufs + b) * 128u;
+    const uint32_t slot_off = (uint32_t)(warp * kBufs + b) * p.slot_stride;
     const uint32_t* src = p.qtiles + tile * (size_t)p.cols * 32;
     for (int c = lane; c < p.cols; c += 32) {
       fence_proxy_async();
       bulk_g2s(s_base + c * p.col_stride + slot_off, src + c * 32, 128u, bar);
     }
   };
-  // STAGED path: the tile's words for this lane ([col][lane]: one coalesced 128-byte row per column)
-  uint32_t st[STAGED ? kStagedMaxCols : 1];
+  // STAGED path: the tile is cols*8 consecutive 16-byte pieces in global memory ([col][32 lanes]);
+  // lane l keeps pieces l, l+32, ... in registers and stores each to its column row
+  constexpr int kPieces = kStagedMaxCols / 4;            // per lane
+  uint4 st[STAGED ? kPieces : 1];
+  const int npieces = p.cols * 8;
   auto fetch_tile = [&](size_t tile) {
-    const uint32_t* src = p.qtiles + tile * (size_t)p.cols * 32 + lane;
+    const uint4* src = reinterpret_cast<const uint4*>(p.qtiles + tile * (size_t)p.cols * 32) + lane;
 #pragma unroll
-    for (int c = 0; c < (STAGED ? kStagedMaxCols : 0); ++c)
-      if (c < p.cols) st[c] = __ldg(src + c * 32);
+    for (int j = 0; j < (STAGED ? kPieces : 0); ++j)
+      if (lane + 32 * j < npieces) st[j] = __ldg(src + 32 * j);
   };
   auto commit_tile = [&]() {
-    const uint32_t dst = s_base + (uint32_t)warp * 128u + lane * 4u;
+    // piece i = lane + 32 j: column i / 8, bytes (i % 8) * 16 of that column's 128-byte row
+    const uint32_t dst = s_base + (uint32_t)warp * p.slot_stride + (uint32_t)(lane & 7) * 16u +
+                         (uint32_t)(lane >> 3) * p.col_stride;
 #pragma unroll
-    for (int c = 0; c < (STAGED ? kStagedMaxCols : 0); ++c)
-      if (c < p.cols) sts_u32(dst + c * p.col_stride, st[c]);
+    for (int j = 0; j < (STAGED ? kPieces : 0); ++j)
+      if (lane + 32 * j < npieces) sts_u128(dst + (uint32_t)(4 * j) * p.col_stride, st[j]);
   };
 
   for (int chunk = 0; chunk < p.num_chunks; ++chunk) {
@@ -201,13 +209,13 @@ __global__ void __launch_bounds__(kSmemMaxThreads, 1) k_smem_forest(SmemParams p
 
       const size_t row = tile * 32 + lane;
       const bool live = row < p.rows;
-      const uint32_t slot_lane = (uint32_t)(warp * kBufs + buf) * 128u + lane * 4u;
+      const uint32_t slot_lane = (uint32_t)(warp * kBufs + buf) * p.slot_stride + lane * 4u;
 
       for (int t = 0; t < ntrees; t += G) {
         uint32_t a[G];
         const uint32_t tree_abs = s_base + forest_off + (uint32_t)t * W * 4u;
-        if (has_missing) traverse_group<DEPTH, G, true, WIDE>(tree_abs, s_base, slot_lane, p.col_mask, p.col_lshift, p.miss_code, a);
-        else traverse_group<DEPTH, G, false, WIDE>(tree_abs, s_base, slot_lane, p.col_mask, p.col_lshift, p.miss_code, a);
+        if (has_missing) traverse_group<DEPTH, G, true>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a);
+        else traverse_group<DEPTH, G, false>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a);
 #pragma unroll
         for (int g = 0; g < G; ++g) {
           acc += __uint_as_float(lds_u32(a[g]));   // a padding tree adds +0.0f: the sum keeps its bits

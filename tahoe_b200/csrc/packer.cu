@@ -360,10 +360,8 @@ static int build_quant(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
   f->quant = true;            // plan_chunks needs it; cleared again if no tree fits shared memory
   plan_chunks(f);
   if (!f->quant) return TAHOE_OK;   // not even one tree fits beside the sample tiles
-  // wide form when it fits: the column field is then already the byte offset of the column
-  // row in the shared-memory tile region, saving one instruction per node visit
-  const int wide_shift = kQuantColShift + ilog2_c(std::max(f->slots, 1));
-  f->col_shift = (rb + cb + wide_shift <= 32) ? wide_shift : kQuantColShift;
+  // col_shift was chosen with the plan: the column field of a node word is always the byte offset of
+  // the column row in the plan's tile region
   f->col_mask = ((1u << cb) - 1u) << f->col_shift;
   f->miss_code = ((1u << rb) - 1u) << f->rank_shift;
 
@@ -590,12 +588,27 @@ static void plan_sparse_smem(tahoe_forest* f, const tahoe_sparse_node_t* nodes) 
 // ---- shared-memory chunk plan ------------------------------------------------------------
 // Shared memory of one persistent CTA (227 KB opt-in, vs the reference's 0.8 * 48 KB,
 // Struct.h:215-220): [warp tiles][forest chunk][mbarriers].
-// Relative cost of one node visit for a plan, from B200 measurements on the SUSY-shaped forest
-// (profiles/r01_variants_group_size.log): 16 warps x G=6 is the unit.
+// Relative cost of one node visit for a plan, from B200 measurements on the SUSY- and Higgs-shaped
+// forests (profiles/r01_smem_plans.log): 16 warps x 6 trees is the unit.  What matters is the
+// number of dependent chains in flight per SM (warps x trees per thread); TMA-fed tiles with few
+// warps lose the overlap that hides the bulk copies.
 double smem_visit_cost(int warps, int G, bool staged) {
+  const int chains = warps * G;
+  const double by_chains = chains >= 40 ? 1.0 : chains >= 32 ? 1.12 : chains >= 24 ? 1.25
+                         : chains >= 16 ? 1.5 : chains >= 12 ? 1.9 : 2.5;
+  if (staged) return by_chains * (warps >= 16 ? 1.0 : (warps >= 8 ? 1.04 : 1.15));
+  // TMA-fed tiles: the group size matters at every warp count, and few warps lose the overlap
   static const double by_group[kMaxGroup + 1] = {0.0, 1.50, 1.25, 1.124, 1.096, 1.056, 1.0};
-  const double by_warps = warps >= 16 ? 1.0 : (warps >= 8 ? 1.45 : 2.4);
-  return by_group[G] * by_warps * (staged ? 1.11 : 1.0);
+  return by_group[G] * (warps >= 16 ? 1.0 : (warps >= 8 ? 1.3 : 2.4));
+}
+
+// One pass of a row's tile through a chunk, in node-visit units: the staged path moves the tile
+// through the LSU twice (C/4 128-bit loads + stores per lane = 2C wavefronts against ~2.5 per
+// visit) plus its fixed part; bulk copies cost the fixed part only, but are exposed when a chunk
+// holds too little work per tile to hide them.
+double smem_tile_cost(int cols, bool staged, int trees_per_chunk, int depth) {
+  if (staged) return (2.0 * cols + 20.0) / 2.5;
+  return 8.0 + ((double)trees_per_chunk * depth < 100.0 ? 45.0 : 0.0);
 }
 
 void plan_chunks(tahoe_forest* f) {
@@ -615,8 +628,8 @@ void plan_chunks(tahoe_forest* f) {
   int want_warps = 0, want_staged = -1, want_group = 0;   // TAHOE_SMEM_PLAN="warps,staged,group"
   if (const char* e = std::getenv("TAHOE_SMEM_PLAN")) std::sscanf(e, "%d,%d,%d", &want_warps, &want_staged, &want_group);
 
-  // every (warps, tile buffering, group) that fits; cost per sample = node visits at the plan's
-  // rate + one pass of the sample tiles per chunk (HBM/L2 streaming, mostly hidden: weighted 0.8)
+  // every (warps, tile buffering, group) that fits; cost per sample (in node-visit units) = node
+  // visits at the plan's rate + one tile pass per chunk
   double best = 0.0;
   bool found = false;
   for (int warps = kSmemMaxWarps; warps >= 4; warps >>= 1) {
@@ -625,25 +638,32 @@ void plan_chunks(tahoe_forest* f) {
       if (want_staged >= 0 && staged != want_staged) continue;
       if (staged && C > kStagedMaxCols) continue;
       const int slots = warps * (staged ? 1 : 2);
-      const size_t tiles = (size_t)slots * tile_bytes;
+      // wide column field (column-major tile region) when rank + column bits leave room for it,
+      // else the compact field with a slot-major region whose columns are padded to a power of two
+      const bool wide = f->rank_bits + f->col_bits + kQuantColShift + ilog2_c(slots) <= 32;
+      const size_t cols_pad = (size_t)1 << ceil_log2((uint64_t)C);
+      const size_t tiles = wide ? (size_t)slots * tile_bytes : (size_t)slots * cols_pad * 128;
       if ((size_t)f->smem_optin < tiles + bars + tree_bytes) continue;
       const size_t avail = (size_t)f->smem_optin - tiles - bars;
-      const int max_tpc = (int)std::min<size_t>(avail / tree_bytes, (size_t)T);
+      const int max_tpc = (int)std::min<size_t>(avail / tree_bytes, (size_t)T + kMaxGroup);   // padding trees count
       for (int G = 1; G <= std::min(kMaxGroup, max_tpc); ++G) {
         if (want_group && G != want_group) continue;
         const int tpad = (T + G - 1) / G * G;          // all-zero trees pad the forest to whole groups
         int tpc = std::min(max_tpc / G * G, tpad);
         const int chunks = (tpad + tpc - 1) / tpc;     // balance: same chunk count, even whole groups
         tpc = ((tpad + chunks - 1) / chunks + G - 1) / G * G;
-        const double visits = (double)tpad * std::max(f->depth, 1) * 3.3e-13 * smem_visit_cost(warps, G, staged);
-        const double stream = (double)chunks * (double)C * 4.0 / 5.0e12;
-        const double cost = visits + 0.5 * stream;
+        const double visits = (double)tpad * std::max(f->depth, 1) * smem_visit_cost(warps, G, staged != 0);
+        const double cost = visits + (double)chunks * smem_tile_cost(C, staged != 0, tpc, std::max(f->depth, 1));
         if (!found || cost < best) {
           found = true; best = cost;
           f->warps = warps; f->staged = staged != 0; f->slots = slots; f->group = G;
           f->qwords_trees = tpad; f->trees_per_chunk = tpc;
           f->num_chunks = (tpad + tpc - 1) / tpc;
           f->smem_bytes = tiles + bars + (size_t)tpc * tree_bytes;
+          f->tile_region = (uint32_t)tiles;
+          f->tile_col_stride = wide ? 128u * (uint32_t)slots : 128u;
+          f->tile_slot_stride = wide ? 128u : (uint32_t)(cols_pad * 128);
+          f->col_shift = wide ? kQuantColShift + ilog2_c(slots) : kQuantColShift;
         }
       }
     }

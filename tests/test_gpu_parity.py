@@ -130,11 +130,14 @@ def test_sparse_forest_through_shared_memory(oracle, monkeypatch, cut, tpc, rows
     got, ids = _run(f, data, api.SPLIT_SHARED_FOREST)
     assert np.array_equal(ids, wids)
     assert score_close(got, want, leafvals)
+    # the perf instantiation (other number of tree sequences per lane: another order again)
     got2, _ = _run(f, data, api.SPLIT_SHARED_FOREST, want_ids=False)
-    assert bits_equal(got, got2)                                          # reproducible
+    assert score_close(got2, want, leafvals)
+    got2b, _ = _run(f, data, api.SPLIT_SHARED_FOREST, want_ids=False)
+    assert bits_equal(got2, got2b)                                        # reproducible run to run
     if f.applicable(api.SHARED_FOREST, rows):
         got3, _ = _run(f, data, api.SHARED_FOREST, want_ids=False)
-        assert bits_equal(got, got3)
+        assert bits_equal(got2, got3)
 
 
 @pytest.mark.parametrize("rows", [0, 1, 31, 32, 33, 2368 * 32 + 5])
