@@ -68,8 +68,9 @@ constexpr double kSharedDataRate = 7.0e11;  // visits/s (slot-levels), SHARED_DA
 constexpr double kRowStream = 3.7e12;       // B/s of sample rows through a TMA-fed SHARED_DATA kernel
 constexpr double kSmemVisit = 3.3e-13;      // s per visit, shared-memory forest, 16 warps x 6 trees (unit plan)
 constexpr double kTileStream = 5.0e12;      // B/s of rank tiles re-read once per chunk (half hidden)
-constexpr double kChunkFixed = 3.0e-6;      // stage one chunk + barrier
-constexpr double kTileLevel = 75e-9;        // one level of one traversal group of a tile (latency-bound)
+constexpr double kChunkFixed = 1.2e-6;      // stage one chunk + barrier
+constexpr double kTileLevel = 40e-9;        // one level of one traversal group of a tile: this much alone ...
+constexpr double kTileLevelPerWarp = 7.5e-9;  // ... plus this per warp sharing the SM (16 warps: 160 ns, 8: 100 ns)
 constexpr double kQuantRate = 1.7e12;       // B/s in+out of k_quantize, whole table in shared memory
 constexpr double kQuantRateStrided = 1.0e12;   // ... every 2^k-th threshold there, rest probed in L2
 constexpr double kSparseVisit = 2.3e-12;      // s per node visit, sparse tree tops in shared memory (free-running lanes)
@@ -138,7 +139,8 @@ static int select_strategy(const tahoe_forest* f, size_t rows_, double* out) {
           const double visits = R * (double)f->qwords_trees * f->depth;               // padded depth
           const double tiles_per_warp = std::ceil(R / 32.0 / ((double)f->sm_count * f->warps));
           const double groups = (double)f->trees_per_chunk / std::max(f->group, 1);
-          const double lat = f->num_chunks * (kChunkFixed + tiles_per_warp * groups * f->depth * kTileLevel);
+          const double lat = f->num_chunks * (kChunkFixed + tiles_per_warp * groups * f->depth *
+                                              (kTileLevel + kTileLevelPerWarp * f->warps));
           const double thr = kSmemVisit * (visits * plan + f->num_chunks * R *
                              smem_tile_cost(f->params.num_cols, f->staged, f->trees_per_chunk, f->depth));
           const double quant = kLaunch + R * C * 8.0 / (f->quant_stride > 1 ? kQuantRateStrided : kQuantRate);
