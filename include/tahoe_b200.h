@@ -102,6 +102,11 @@ typedef struct {
   int sparse_cut;             /* sparse forests through shared memory: breadth-first nodes of each tree kept there */
   double sparse_deep_walks;   /*   expected fraction of (row, tree) walks that go deeper (finished in L2) */
   int sparse_fid_bits;        /*   width of the feature-id field of an 8-byte sparse node (0 = fields do not fit) */
+  int sparse_top_depth;       /* sparse forests, quantised tops (QT): levels of every tree kept as a dense 4-byte heap (0 = not built) */
+  int sparse_top_active;      /*   1 = SHARED_FOREST / SPLIT_SHARED_FOREST run the QT path (else the 8-byte breadth-first tops) */
+  int sparse_top_trees_per_chunk;
+  int sparse_top_chunks;
+  double sparse_top_deep_walks; /* expected fraction of (row, tree) walks still on an internal node below the top (finished in L2) */
 } tahoe_forest_info_t;
 
 /* ---- forest lifetime -------------------------------------------------------------
@@ -163,6 +168,18 @@ int tahoe_profile_read(tahoe_forest_t* f, double* quantize_ms, double* traverse_
 int tahoe_load_model_text(const char* path, tahoe_dense_node_t** nodes, int* num_trees, int* depth);
 int tahoe_load_data_text(const char* path, float** data, int* num_rows, int* num_cols, float* missing);
 void tahoe_free_host(void* p);
+/* Both loaders map the file and parse it on all host threads (TAHOE_LOADER_THREADS), with the
+ * reference's exact per-line semantics ((float)atof / atoi of a 1024-byte fgets buffer, a short
+ * file repeating its last line); TAHOE_LOADER_SEQUENTIAL=1 forces the reference's one-thread loop.
+ *
+ * Binary cache of a parsed file (the reference re-parses its text on every run): a
+ * 64-byte header {magic, version, kind, shape, missing, payload bytes, FNV-1a 64 checksum} followed
+ * by the raw payload (12-byte AoS nodes / row-major float32).  Loading verifies magic, version,
+ * shape against payload size, and the checksum; buffers are released with tahoe_free_host. */
+int tahoe_save_model_binary(const char* path, const tahoe_dense_node_t* nodes, int num_trees, int depth);
+int tahoe_load_model_binary(const char* path, tahoe_dense_node_t** nodes, int* num_trees, int* depth);
+int tahoe_save_data_binary(const char* path, const float* data, int num_rows, int num_cols, float missing);
+int tahoe_load_data_binary(const char* path, float** data, int* num_rows, int* num_cols, float* missing);
 
 /* ---- synthetic inputs (device) -------------------------------------------------------
  * Seeded U(-1,1) sample matrix written straight into device memory; bit-identical
@@ -191,7 +208,9 @@ enum {
   TAHOE_EXPORT_SD_ORIG_BOTTOM = 14, /* int32 [2^depth][Tpad] bottom position -> original heap id of the leaf */
   TAHOE_EXPORT_SPARSE_BFS = 15,      /* uint2 [nodes] sparse trees renumbered breadth-first: {val, leaf<<31|def_left<<30|delta<<fid_bits|fid} */
   TAHOE_EXPORT_SPARSE_BFS_ORIG = 16, /* int32 [nodes] breadth-first index -> caller's node index inside its tree */
-  TAHOE_EXPORT_SPARSE_TOP = 17       /* uint2 [chunks * trees_per_chunk][sparse_cut] shared-memory image of the tree tops */
+  TAHOE_EXPORT_SPARSE_TOP = 17,      /* uint2 [chunks * trees_per_chunk][sparse_cut] shared-memory image of the tree tops */
+  TAHOE_EXPORT_SPARSE_DEEPQ = 18     /* uint2 [total] breadth-first sparse nodes in rank form {rank word | leaf value, child delta | leaf<<31};
+                                        the dense tops of the QT layout are exported as QUANT_WORDS / LEAF_ORIGIN */
 };
 int tahoe_forest_export(const tahoe_forest_t* f, int which, void* buf, size_t* bytes);
 

@@ -26,7 +26,8 @@ ALL_STRATEGIES = list(STRATEGY_NAMES)
 (EXPORT_HEAP_NODES, EXPORT_INTERLEAVED, EXPORT_TREE_ORDER, EXPORT_ORIG_IDS, EXPORT_QUANT_WORDS,
  EXPORT_QUANT_TABLE, EXPORT_QUANT_OFFSETS, EXPORT_LEAF_ORIGIN, EXPORT_SIMHASH, EXPORT_QUANT_LUT,
  EXPORT_QUANT_LUT_MIN, EXPORT_QUANT_LUT_SCALE, EXPORT_SD_TOP_NODES, EXPORT_SD_BLOCKS,
- EXPORT_SD_ORIG_BOTTOM, EXPORT_SPARSE_BFS, EXPORT_SPARSE_BFS_ORIG, EXPORT_SPARSE_TOP) = range(18)
+ EXPORT_SD_ORIG_BOTTOM, EXPORT_SPARSE_BFS, EXPORT_SPARSE_BFS_ORIG, EXPORT_SPARSE_TOP,
+ EXPORT_SPARSE_DEEPQ) = range(19)
 
 
 class TahoeError(RuntimeError):
@@ -57,7 +58,9 @@ class ForestInfo(C.Structure):
                 ("smem_warps", C.c_int), ("smem_staged", C.c_int), ("smem_group", C.c_int),
                 ("sd_teams", C.c_int), ("sd_team_warps", C.c_int), ("sd_top_levels", C.c_int),
                 ("sd_blocked", C.c_int), ("sparse_cut", C.c_int), ("sparse_deep_walks", C.c_double),
-                ("sparse_fid_bits", C.c_int)]
+                ("sparse_fid_bits", C.c_int), ("sparse_top_depth", C.c_int), ("sparse_top_active", C.c_int),
+                ("sparse_top_trees_per_chunk", C.c_int), ("sparse_top_chunks", C.c_int),
+                ("sparse_top_deep_walks", C.c_double)]
 
 
 _lib = None
@@ -88,6 +91,10 @@ def lib() -> C.CDLL:
     L.tahoe_load_model_text.argtypes = [C.c_char_p, C.POINTER(vp), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.tahoe_load_data_text.argtypes = [C.c_char_p, C.POINTER(vp), C.POINTER(C.c_int),
                                        C.POINTER(C.c_int), C.POINTER(C.c_float)]
+    L.tahoe_save_model_binary.argtypes = [C.c_char_p, vp, C.c_int, C.c_int]
+    L.tahoe_load_model_binary.argtypes = L.tahoe_load_model_text.argtypes
+    L.tahoe_save_data_binary.argtypes = [C.c_char_p, vp, C.c_int, C.c_int, C.c_float]
+    L.tahoe_load_data_binary.argtypes = L.tahoe_load_data_text.argtypes
     L.tahoe_free_host.argtypes = [vp]
     L.tahoe_free_host.restype = None
     L.tahoe_gen_data_device.argtypes = [C.c_uint64, sz, sz, C.c_int, C.c_float, C.c_float, vp, vp]
@@ -226,18 +233,40 @@ class Forest:
         return buf
 
 
-def load_model_text(path: str):
+def load_model_text(path: str, binary: bool = False):
     p, t, d = C.c_void_p(), C.c_int(), C.c_int()
-    _check(lib().tahoe_load_model_text(path.encode(), C.byref(p), C.byref(t), C.byref(d)))
+    fn = lib().tahoe_load_model_binary if binary else lib().tahoe_load_model_text
+    _check(fn(path.encode(), C.byref(p), C.byref(t), C.byref(d)))
     n = t.value * ((1 << (d.value + 1)) - 1)
     arr = np.frombuffer((C.c_char * (n * 12)).from_address(p.value), dtype=DENSE_NODE).copy()
     lib().tahoe_free_host(p)
     return arr, t.value, d.value
 
 
-def load_data_text(path: str):
+def save_model_binary(path: str, nodes: np.ndarray, num_trees: int, depth: int) -> None:
+    nodes = np.ascontiguousarray(nodes, dtype=DENSE_NODE)
+    assert nodes.size == num_trees * ((1 << (depth + 1)) - 1)
+    _check(lib().tahoe_save_model_binary(path.encode(), nodes.ctypes.data_as(C.c_void_p), num_trees, depth))
+
+
+def load_model_binary(path: str):
+    return load_model_text(path, binary=True)
+
+
+def save_data_binary(path: str, data: np.ndarray, missing: float) -> None:
+    data = np.ascontiguousarray(data, dtype=np.float32)
+    _check(lib().tahoe_save_data_binary(path.encode(), data.ctypes.data_as(C.c_void_p), data.shape[0],
+                                        data.shape[1], C.c_float(missing)))
+
+
+def load_data_binary(path: str):
+    return load_data_text(path, binary=True)
+
+
+def load_data_text(path: str, binary: bool = False):
     p, r, c, m = C.c_void_p(), C.c_int(), C.c_int(), C.c_float()
-    _check(lib().tahoe_load_data_text(path.encode(), C.byref(p), C.byref(r), C.byref(c), C.byref(m)))
+    fn = lib().tahoe_load_data_binary if binary else lib().tahoe_load_data_text
+    _check(fn(path.encode(), C.byref(p), C.byref(r), C.byref(c), C.byref(m)))
     n = r.value * c.value
     arr = np.frombuffer((C.c_char * (n * 4)).from_address(p.value), dtype=np.float32).copy()
     lib().tahoe_free_host(p)

@@ -27,6 +27,7 @@ static void free_workspace(Workspace& w) {
 }
 
 static bool whole_forest_fits(const tahoe_forest* f) {
+  if (f->sparse && f->sp_use_qt) return f->num_chunks == 1 && f->qt_overflow == 0.0;
   if (f->sparse) return f->sp_tpc >= 1 && f->sp_chunks == 1 && f->sp_overflow == 0.0;
   return f->quant && f->num_chunks == 1;
 }
@@ -43,6 +44,7 @@ static int applicable(const tahoe_forest* f, int strategy, size_t rows) {
     case TAHOE_STRATEGY_SHARED_FOREST:   // whole forest resident (BaseTahoeTest.h:657-668)
       return whole_forest_fits(f) ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
     case TAHOE_STRATEGY_SPLIT_SHARED_FOREST:  // at least one tree per chunk (:670-679)
+      if (f->sparse && f->sp_use_qt) return f->trees_per_chunk >= 1 ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
       if (f->sparse) return f->sp_tpc >= 1 ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
       return (f->quant && f->trees_per_chunk >= 1) ? TAHOE_OK : TAHOE_ERR_NOT_APPLICABLE;
     default:
@@ -77,6 +79,7 @@ constexpr double kSparseVisit = 2.3e-12;      // s per node visit, sparse tree t
 constexpr double kSparseChunkRow = 1.0e-10;   // s per row per chunk: tile re-stream + refill latency share
 constexpr double kSparseDeep = 3.1e-11;       // s per walk that leaves the tops and is finished in L2
 constexpr double kSparseStep = 300e-9;        // one step of a lane's two interleaved sequences (latency)
+constexpr double kDeepWalk = 2.0e-11;          // s per parked walk of the QT layout (64 finished together in L2)
 constexpr double kSparseTileFixed = 8e-6;     // refill a warp's tile buffer + final drain
 }  // namespace model
 
@@ -123,7 +126,7 @@ static int select_strategy(const tahoe_forest* f, size_t rows_, double* out) {
           t = kLaunch + std::max(std::max(lat, thr), R * C * 4.0 / kRowStream);
           break;
         }
-        default: if (f->sparse) {   // tile pass + tree tops in shared memory + deep walks finished in L2
+        default: if (f->sparse && !f->sp_use_qt) {   // T8: tile pass + tree tops in shared memory + deep walks finished in L2
           const double warps = (double)f->sm_count * kSparseWarps;
           const double tiles_per_warp = std::ceil(R / 32.0 / warps);
           const double visits = R * T * (dbar + 1.0);
@@ -135,14 +138,17 @@ static int select_strategy(const tahoe_forest* f, size_t rows_, double* out) {
           t = 2.0 * kLaunch + R * C * 8.0 / kRowStream + std::max(lat, thr);
           break;
         } else {   // SHARED_FOREST / SPLIT_SHARED_FOREST: quantise pass + chunk passes
+          // (sparse forests, QT layout: the same kernel on the dense tops + parked deep walks in L2)
+          const int depth = f->qdepth;
           const double plan = smem_visit_cost(f->warps, f->group, f->staged);
-          const double visits = R * (double)f->qwords_trees * f->depth;               // padded depth
+          const double visits = R * (double)f->qwords_trees * depth;               // padded depth
           const double tiles_per_warp = std::ceil(R / 32.0 / ((double)f->sm_count * f->warps));
           const double groups = (double)f->trees_per_chunk / std::max(f->group, 1);
-          const double lat = f->num_chunks * (kChunkFixed + tiles_per_warp * groups * f->depth *
+          const double lat = f->num_chunks * (kChunkFixed + tiles_per_warp * groups * depth *
                                               (kTileLevel + kTileLevelPerWarp * f->warps));
           const double thr = kSmemVisit * (visits * plan + f->num_chunks * R *
-                             smem_tile_cost(f->params.num_cols, f->staged, f->trees_per_chunk, f->depth));
+                             smem_tile_cost(f->params.num_cols, f->staged, f->trees_per_chunk, depth)) +
+                             (f->sparse ? R * T * f->qt_overflow * kDeepWalk : 0.0);
           const double quant = kLaunch + R * C * 8.0 / (f->quant_stride > 1 ? kQuantRateStrided : kQuantRate);
           t = kLaunch + quant + std::max(lat, thr);
           break;
@@ -169,7 +175,7 @@ static int predict_impl(tahoe_forest* f, int strategy, const PredictArgs& a) {
     case TAHOE_STRATEGY_DIRECT: rc = launch_direct(f, a, false, &launches); break;
     case TAHOE_STRATEGY_SHARED_DATA_PER_THREAD: rc = launch_direct(f, a, true, &launches); break;
     case TAHOE_STRATEGY_SHARED_DATA: rc = launch_shared_data(f, a, &launches); break;
-    default: rc = f->sparse ? launch_sparse_smem(f, a, &launches) : launch_smem_forest(f, a, &launches); break;
+    default: rc = (f->sparse && !f->sp_use_qt) ? launch_sparse_smem(f, a, &launches) : launch_smem_forest(f, a, &launches); break;
   }
   f->last_launches = launches;
   return rc;
@@ -227,7 +233,7 @@ void tahoe_forest_destroy(tahoe_forest_t* f) {
   if (!f) return;
   cudaFree(f->d_heap); cudaFree(f->d_sparse); cudaFree(f->d_sparse8); cudaFree(f->d_tree_offsets); cudaFree(f->d_inter);
   cudaFree(f->d_tree_order); cudaFree(f->d_orig_ids);
-  cudaFree(f->d_sp_full); cudaFree(f->d_sp_orig); cudaFree(f->d_sp_top);
+  cudaFree(f->d_sp_full); cudaFree(f->d_sp_orig); cudaFree(f->d_sp_top); cudaFree(f->d_sp_deepq);
   cudaFree(f->d_sd_top_nodes); cudaFree(f->d_sd_blocks); cudaFree(f->d_sd_orig_bottom); cudaFree(f->d_qwords); cudaFree(f->d_qtable);
   cudaFree(f->d_qoffsets); cudaFree(f->d_leaf_origin);
   cudaFree(f->d_qlut_min); cudaFree(f->d_qlut_scale); cudaFree(f->d_qlut);
@@ -247,6 +253,9 @@ int tahoe_forest_info(const tahoe_forest_t* f, tahoe_forest_info_t* info) {
   info->num_chunks = f->sparse ? f->sp_chunks : f->num_chunks;
   info->sparse_cut = f->sp_cut; info->sparse_deep_walks = f->sp_overflow;
   info->sparse_fid_bits = f->host.sparse_fid_bits;
+  info->sparse_top_depth = f->qt ? f->qt_depth : 0; info->sparse_top_active = f->sp_use_qt;
+  info->sparse_top_trees_per_chunk = f->qt ? f->trees_per_chunk : 0; info->sparse_top_chunks = f->qt ? f->num_chunks : 0;
+  info->sparse_top_deep_walks = f->qt_overflow;
   info->bytes_heap = (int64_t)(f->host.heap.size() * sizeof(uint2) + f->host.sparse.size() * sizeof(uint4));
   info->bytes_interleaved = (int64_t)(f->host.inter.size() * sizeof(uint2));
   info->bytes_quantized = (int64_t)(f->host.qwords.size() * sizeof(uint32_t));
@@ -365,6 +374,7 @@ int tahoe_forest_export(const tahoe_forest_t* f, int which, void* buf, size_t* b
     case TAHOE_EXPORT_SPARSE_BFS: src = h.sp_full.data(); n = h.sp_full.size() * sizeof(uint2); break;
     case TAHOE_EXPORT_SPARSE_BFS_ORIG: src = h.sp_orig.data(); n = h.sp_orig.size() * 4; break;
     case TAHOE_EXPORT_SPARSE_TOP: src = h.sp_top.data(); n = h.sp_top.size() * sizeof(uint2); break;
+    case TAHOE_EXPORT_SPARSE_DEEPQ: src = h.sp_deepq.data(); n = h.sp_deepq.size() * sizeof(uint2); break;
     default: set_error("unknown export id"); return TAHOE_ERR_INVALID;
   }
   if (buf) {

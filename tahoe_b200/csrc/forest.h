@@ -33,6 +33,8 @@ constexpr uint32_t kMetaLeaf = 1u << 31;         // same bit as IS_LEAF_MASK, St
 constexpr int kSmemMaxWarps = 16;                // 512 threads, one persistent CTA per SM
 constexpr int kMaxGroup = 6;                     // trees traversed together by one thread (ILP): 1..6
 constexpr int kStagedMaxCols = 32;               // register-staged tiles keep one word per column per lane
+constexpr int kStagedMaxColsDeep = 64;           // ... the sparse (deep) variant at <= 8 warps: 255 registers per thread
+constexpr int kDeepPend = 24;                    // parked deep walks one LANE can hold (4 bytes each) before its warp must drain
 constexpr int ilog2_c(int v) { return v <= 1 ? 0 : 1 + ilog2_c(v >> 1); }
 
 constexpr int kSparseWarps = 16;                 // k_sparse_smem: warps per persistent CTA
@@ -56,6 +58,8 @@ struct HostPack {
   std::vector<uint2> sp_full;         // [total] breadth-first S8 nodes, same tree_offsets
   std::vector<int32_t> sp_orig;       // [total] breadth-first index -> caller's node index inside the tree
   std::vector<uint2> sp_top;          // [sp_chunks * sp_tpc][sp_cut]; short trees padded with leaf 0.0
+  // QT (sparse forests, quantised tops): qwords / leaf_origin hold the dense top of depth qt_depth;
+  std::vector<uint2> sp_deepq;        // [total] breadth-first nodes in rank form {rank word | leaf value, child delta | leaf<<31}
   // I8
   int tpad = 0;                       // trees padded to a multiple of 32
   std::vector<uint2> inter;           // [N][tpad]
@@ -127,6 +131,13 @@ struct tahoe_forest {
   int sp_cut = 0, sp_tpc = 0, sp_chunks = 0;
   size_t sp_smem = 0;
   double sp_overflow = 0.0;      // expected walks per (row, tree) that leave the top, children equally likely
+  // QT plan (plan_sparse_qtop): the top qt_depth levels of every sparse tree as a dense Q4 heap served by
+  // k_smem_forest<DEEP>; walks still on an internal node at that level are parked and finished in L2
+  bool qt = false;
+  bool sp_use_qt = false;        // QT is the path SHARED_FOREST / SPLIT take (else T8: TAHOE_SPARSE_PATH=t8 or a forced cut)
+  int qt_depth = 0;
+  double qt_overflow = 0.0;      // expected parked walks per (row, tree)
+  int qdepth = 0;                // depth of the trees in d_qwords (dense: depth; sparse QT: qt_depth)
 
   // SHARED_DATA plan (plan_shared_data, at create): teams of team_warps warps share a row
   int sd_teams = 0, sd_team_warps = 1, sd_group = 1;
@@ -143,6 +154,7 @@ struct tahoe_forest {
   uint2* d_sp_full = nullptr;
   int32_t* d_sp_orig = nullptr;
   uint2* d_sp_top = nullptr;
+  uint2* d_sp_deepq = nullptr;
   int64_t* d_tree_offsets = nullptr;
   uint2* d_inter = nullptr;
   int32_t* d_tree_order = nullptr;

@@ -149,7 +149,7 @@ TAHOE_DEPTH_DECL(11) TAHOE_DEPTH_DECL(12) TAHOE_DEPTH_DECL(13) TAHOE_DEPTH_DECL(
 #undef TAHOE_DEPTH_DECL
 
 int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
-  if (!f->quant || f->trees_per_chunk < 1) {
+  if (!(f->quant || f->qt) || f->trees_per_chunk < 1) {
     set_error("shared-memory forest strategies need a dense forest of depth 1..14, <= 64 columns, "
               "whose rank+column code fits 32 bits and whose trees fit shared memory");
     return TAHOE_ERR_NOT_APPLICABLE;
@@ -195,6 +195,8 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.col_stride = f->tile_col_stride; p.slot_stride = f->tile_slot_stride; p.tile_region = f->tile_region;
   p.preds = a.preds; p.leaf_ids = a.leaf_ids;
   p.leaf_origin = f->d_leaf_origin;
+  p.deep = f->d_sp_deepq; p.tree_offsets = f->d_tree_offsets; p.deep_orig = f->d_sp_orig;
+  if (const char* e = std::getenv("TAHOE_QTOP_NODRAIN")) p.debug_no_drain = std::atoi(e);
   p.tf = Transform{f->params.output, (float)f->params.num_trees, f->params.threshold,
                    f->params.global_bias};
   // Row batches (tuning knob, off by default): walk the rows in batches whose rank tiles stay
@@ -217,7 +219,7 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
     if (p.leaf_ids) b.leaf_ids = p.leaf_ids + t0 * 32 * (size_t)p.num_trees;
     const unsigned grid = (unsigned)std::min<size_t>((size_t)f->sm_count,
                                                      (b.num_tiles + f->warps - 1) / f->warps);
-    switch (f->depth) {
+    switch (f->qdepth) {
 #define TAHOE_DEPTH_CASE(D) case D: rc = launch_smem_depth_##D(f, b, grid, a.stream); break;
       TAHOE_DEPTH_CASE(1) TAHOE_DEPTH_CASE(2) TAHOE_DEPTH_CASE(3) TAHOE_DEPTH_CASE(4)
       TAHOE_DEPTH_CASE(5) TAHOE_DEPTH_CASE(6) TAHOE_DEPTH_CASE(7) TAHOE_DEPTH_CASE(8)

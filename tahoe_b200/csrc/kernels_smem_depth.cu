@@ -21,6 +21,30 @@ int TAHOE_CAT(launch_smem_depth_, TAHOE_DEPTH)(tahoe_forest* f, const SmemParams
     TAHOE_CUDA(cudaGetLastError());
     return TAHOE_OK;
   };
+#if TAHOE_DEPTH <= 12
+  // sparse forests (QT layout): dense tops of depth D, deep walks parked and finished in L2
+  if (f->sparse) {
+    const bool wide = f->staged && p.cols > kStagedMaxCols;     // 64-column register staging, <= 8 warps
+    if (wide && f->warps > 8) { set_error("64-column staged tiles need a plan of <= 8 warps"); return TAHOE_ERR_INVALID; }
+    if (p.leaf_ids) {
+      if (wide) return go(k_smem_forest<D, 2, true, true, true, kStagedMaxColsDeep / 4>);
+      return f->staged ? go(k_smem_forest<D, 2, true, true, true>) : go(k_smem_forest<D, 2, true, false, true>);
+    }
+#define TAHOE_DEEP_CASE(G)                                                                  \
+  case G:                                                                                   \
+    if (wide) return go(k_smem_forest<D, G, false, true, true, kStagedMaxColsDeep / 4>);    \
+    return f->staged ? go(k_smem_forest<D, G, false, true, true>) : go(k_smem_forest<D, G, false, false, true>);
+    switch (f->group) {
+      TAHOE_DEEP_CASE(2) TAHOE_DEEP_CASE(4) TAHOE_DEEP_CASE(6)
+      default: break;
+    }
+#undef TAHOE_DEEP_CASE
+    set_error("unsupported traversal group size for a sparse forest");
+    return TAHOE_ERR_INVALID;
+  }
+#else
+  if (f->sparse) { set_error("sparse tops deeper than 12 levels are not built"); return TAHOE_ERR_INVALID; }
+#endif
   // the leaf-id instantiation is the checking path: one tree at a time keeps the build small
   if (p.leaf_ids) return f->staged ? go(k_smem_forest<D, 1, true, true>) : go(k_smem_forest<D, 1, true, false>);
 #define TAHOE_G_CASE(G) \

@@ -71,6 +71,8 @@ static void swap_subtrees(TreeScratch& t, int64_t a, int64_t b, int64_t npt) {
 
 static int build_quant(tahoe_forest* f, const tahoe_dense_node_t* nodes);
 static void plan_sparse_smem(tahoe_forest* f, const tahoe_sparse_node_t* nodes);
+static void plan_sparse_qtop(tahoe_forest* f);
+static double plan_chunks_for(tahoe_forest* f, int depth, bool deep);
 
 int pack_dense(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
   const int T = f->params.num_trees, d = f->params.depth, C = f->params.num_cols;
@@ -280,32 +282,13 @@ void plan_shared_data(tahoe_forest* f) {
 }
 
 // ---- Q4: rank-quantised heap ------------------------------------------------------
-static int build_quant(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
-  const int T = f->params.num_trees, d = f->depth, C = f->params.num_cols;
+// Rank tables shared by the dense Q4 layout and the sparse quantised tops (QT): per column the sorted
+// distinct thresholds (k_quantize turns a feature into rank(v) = #{thr <= v}) and the bucket index
+// that narrows the search.  Sets rank_bits / col_bits / rank_shift; false when rank + column + the
+// 7 lane/word bits do not fit a 32-bit node word.
+static bool build_rank_tables(tahoe_forest* f, std::vector<std::vector<float>>& thr) {
   HostPack& h = f->host;
-  f->quant = false;
-  if (d < 1 || d > kQuantMaxDepth || C > kQuantMaxCols || T < 1) return TAHOE_OK;
-  const int64_t npt = ((int64_t)1 << (d + 1)) - 1;
-  const int64_t W = (int64_t)1 << (d + 1);
-  const int64_t L = (int64_t)1 << d;
-
-  // state per 1-based heap position: 0 = reachable internal, >0 = under/at leaf (origin+1)
-  std::vector<int32_t> origin((size_t)W);
-  std::vector<std::vector<float>> thr(C);
-  for (int t = 0; t < T; ++t) {
-    const tahoe_dense_node_t* tr = nodes + (int64_t)t * npt;
-    origin[1] = (tr[0].bits < 0) ? 1 : 0;
-    for (int64_t i = 1; i < L; ++i) {
-      int32_t o = origin[i];
-      if (o == 0) {
-        float v = tr[i - 1].val;
-        if (!std::isnan(v)) thr[tr[i - 1].bits & 0x3FFFFFFF].push_back(v);
-        for (int c = 0; c < 2; ++c) origin[2 * i + c] = (tr[2 * i + c - 1].bits < 0) ? (int32_t)(2 * i + c) : 0;
-      } else {
-        origin[2 * i] = origin[2 * i + 1] = o;
-      }
-    }
-  }
+  const int C = f->params.num_cols;
   h.qoffsets.assign(C + 1, 0);
   size_t max_n = 0;
   for (int c = 0; c < C; ++c) {
@@ -316,7 +299,7 @@ static int build_quant(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
   }
   const int rb = std::max(1, ceil_log2(max_n + 2));  // ranks 0..n, sentinel code 2^rb-1 > n
   const int cb = std::max(1, ceil_log2((uint64_t)C));
-  if (rb + cb + kQuantColShift > 32) return TAHOE_OK;  // does not fit one word: no Q4 layout
+  if (rb + cb + kQuantColShift > 32) return false;
   h.qtable.clear();
   h.qtable.reserve(h.qoffsets[C]);
   for (int c = 0; c < C; ++c) h.qtable.insert(h.qtable.end(), thr[c].begin(), thr[c].end());
@@ -357,13 +340,44 @@ static int build_quant(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
   f->rank_bits = rb;
   f->col_bits = cb;
   f->rank_shift = 32 - rb;
+  return true;
+}
+
+static int build_quant(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
+  const int T = f->params.num_trees, d = f->depth, C = f->params.num_cols;
+  HostPack& h = f->host;
+  f->quant = false;
+  if (d < 1 || d > kQuantMaxDepth || C > kQuantMaxCols || T < 1) return TAHOE_OK;
+  const int64_t npt = ((int64_t)1 << (d + 1)) - 1;
+  const int64_t W = (int64_t)1 << (d + 1);
+  const int64_t L = (int64_t)1 << d;
+
+  // state per 1-based heap position: 0 = reachable internal, >0 = under/at leaf (origin+1)
+  std::vector<int32_t> origin((size_t)W);
+  std::vector<std::vector<float>> thr(C);
+  for (int t = 0; t < T; ++t) {
+    const tahoe_dense_node_t* tr = nodes + (int64_t)t * npt;
+    origin[1] = (tr[0].bits < 0) ? 1 : 0;
+    for (int64_t i = 1; i < L; ++i) {
+      int32_t o = origin[i];
+      if (o == 0) {
+        float v = tr[i - 1].val;
+        if (!std::isnan(v)) thr[tr[i - 1].bits & 0x3FFFFFFF].push_back(v);
+        for (int c = 0; c < 2; ++c) origin[2 * i + c] = (tr[2 * i + c - 1].bits < 0) ? (int32_t)(2 * i + c) : 0;
+      } else {
+        origin[2 * i] = origin[2 * i + 1] = o;
+      }
+    }
+  }
+  if (!build_rank_tables(f, thr)) return TAHOE_OK;  // rank + column code does not fit one word: no Q4 layout
   f->quant = true;            // plan_chunks needs it; cleared again if no tree fits shared memory
+  f->qdepth = d;
   plan_chunks(f);
   if (!f->quant) return TAHOE_OK;   // not even one tree fits beside the sample tiles
   // col_shift was chosen with the plan: the column field of a node word is always the byte offset of
   // the column row in the plan's tile region
-  f->col_mask = ((1u << cb) - 1u) << f->col_shift;
-  f->miss_code = ((1u << rb) - 1u) << f->rank_shift;
+  f->col_mask = ((1u << f->col_bits) - 1u) << f->col_shift;
+  f->miss_code = ((1u << f->rank_bits) - 1u) << f->rank_shift;
 
   h.qwords.assign((size_t)T * W, 0u);
   h.leaf_origin.assign((size_t)T * L, 0);
@@ -473,6 +487,7 @@ int pack_sparse(tahoe_forest* f, const tahoe_sparse_node_t* nodes, const float* 
   f->mean_depth = T ? depth_acc / T : 0.0;
   f->quant = false;
   plan_sparse_smem(f, nodes);
+  plan_sparse_qtop(f);
   return TAHOE_OK;
 }
 
@@ -585,6 +600,154 @@ static void plan_sparse_smem(tahoe_forest* f, const tahoe_sparse_node_t* nodes) 
   }
 }
 
+// ---- QT: sparse forests as rank-quantised dense tops + deep walks in L2 ----------------------
+// The top `D` levels of every sparse tree are laid out as a dense Q4 heap (leaves pushed down, one
+// 32-bit word per node: the six-instruction visit of k_smem_forest applies unchanged).  A bottom slot
+// holds either the float bits of the leaf the walk has reached or, when the walk is still on an
+// internal node at level D, a continuation marker: a negative quiet NaN whose low 22 bits are the
+// node's breadth-first index relative to the first node of its chunk's first tree.  The kernel parks
+// such walks (lane-private lists) and every lane finishes its own, four at a time, in L2 on `sp_deepq`
+// -- the breadth-first nodes in rank form {rank word, child delta | leaf}, compared against the same
+// rank tile in shared memory.  Thresholds of ALL internal nodes go into the
+// rank tables, so one quantise pass serves both parts.
+constexpr uint32_t kContMask = 0xFFC00000u;
+constexpr double kDeepWalkVisits = 60.0;   // one parked deep walk, in shared-memory node-visit units
+
+static void plan_sparse_qtop(tahoe_forest* f) {
+  HostPack& h = f->host;
+  const int T = f->params.num_trees, C = f->params.num_cols;
+  f->qt = false;
+  f->sp_use_qt = false;
+  f->qt_depth = 0;
+  if (h.sp_full.empty() || T < 1 || C > kQuantMaxCols || f->depth < 1) return;
+  if (const char* e = std::getenv("TAHOE_SPARSE_QTOP")) if (std::atoi(e) == 0) return;
+  const int fb = h.sparse_fid_bits;
+  const uint32_t fmask = (1u << fb) - 1u;
+  const int64_t total = h.tree_offsets[T];
+  auto u2f = [](uint32_t u) { float x; std::memcpy(&x, &u, 4); return x; };
+
+  std::vector<std::vector<float>> thr(C);
+  int64_t max_n = 0;
+  for (int t = 0; t < T; ++t) max_n = std::max(max_n, h.tree_offsets[t + 1] - h.tree_offsets[t]);
+  if (max_n >= (int64_t)1 << 22) return;                       // the marker keeps 22 bits of node index
+  for (int64_t q = 0; q < total; ++q) {
+    const uint2 e = h.sp_full[q];
+    if (e.y & kMetaLeaf) {
+      if ((e.x & kContMask) == kContMask) return;              // a leaf value that looks like a marker
+    } else {
+      const float v = u2f(e.x);
+      if (!std::isnan(v)) thr[e.y & fmask].push_back(v);
+    }
+  }
+  auto give_up = [&]() {
+    h.qtable.clear(); h.qoffsets.clear(); h.qlut.clear(); h.qlut_min.clear(); h.qlut_scale.clear();
+    h.qwords.clear(); h.leaf_origin.clear(); h.sp_deepq.clear();
+    f->qt = false; f->sp_use_qt = false; f->qt_depth = 0; f->trees_per_chunk = 0; f->num_chunks = 0;
+  };
+  if (!build_rank_tables(f, thr)) { give_up(); return; }
+
+  // walks still on an internal node at level D, per (row, forest), children taken as equally likely
+  const int max_d = std::min(std::min(f->depth, kQuantMaxDepth), 12);
+  std::vector<double> over((size_t)max_d + 2, 0.0);
+  {
+    std::vector<double> pr;
+    std::vector<int32_t> lev;
+    for (int t = 0; t < T; ++t) {
+      const int64_t base = h.tree_offsets[t], n = h.tree_offsets[t + 1] - base;
+      pr.assign((size_t)n, 0.0);
+      lev.assign((size_t)n, 0);
+      pr[0] = 1.0;
+      for (int64_t q = 0; q < n; ++q) {
+        const uint2 e = h.sp_full[base + q];
+        if ((e.y & kMetaLeaf) || pr[q] == 0.0) continue;
+        if (lev[q] <= max_d) over[lev[q]] += pr[q];
+        const int64_t nl = q + ((e.y & 0x3FFFFFFFu) >> fb);
+        pr[nl] = pr[nl + 1] = 0.5 * pr[q];
+        lev[nl] = lev[nl + 1] = lev[q] + 1;
+      }
+    }
+  }
+  int want_d = 0;
+  if (const char* e = std::getenv("TAHOE_QTOP_DEPTH")) want_d = std::atoi(e);
+  int best_d = 0;
+  double best_cost = 0.0;
+  for (int D = 1; D <= max_d; ++D) {
+    if (want_d && D != want_d) continue;
+    const double c = plan_chunks_for(f, D, true);
+    if (c < 0.0) continue;
+    const double cost = c + over[D] * kDeepWalkVisits;
+    if (!best_d || cost < best_cost) { best_d = D; best_cost = cost; }
+  }
+  if (!best_d || plan_chunks_for(f, best_d, true) < 0.0) { give_up(); return; }
+  const int D = best_d;
+  if (const char* e = std::getenv("TAHOE_QTOP_TPC")) {          // test knob: force several chunks
+    const int G = std::max(f->group, 1);
+    const int cap = std::max(G, std::atoi(e) / G * G);
+    if (cap < f->trees_per_chunk) {
+      f->trees_per_chunk = cap;
+      f->num_chunks = (f->qwords_trees + cap - 1) / cap;
+    }
+  }
+  f->qt = true;
+  {
+    const char* path = std::getenv("TAHOE_SPARSE_PATH");
+    f->sp_use_qt = !(path && std::strcmp(path, "t8") == 0) && !std::getenv("TAHOE_SPARSE_CUT");
+  }
+  f->qt_depth = D;
+  f->qdepth = D;
+  f->qt_overflow = over[D] / T;
+  f->col_mask = ((1u << f->col_bits) - 1u) << f->col_shift;
+  f->miss_code = ((1u << f->rank_bits) - 1u) << f->rank_shift;
+
+  auto rank_word = [&](uint2 e) -> uint32_t {
+    const uint32_t fid = e.y & fmask;
+    const float v = u2f(e.x);
+    const std::vector<float>& tv = thr[fid];
+    const uint32_t k = std::isnan(v) ? (uint32_t)tv.size()       // val >= NaN is never true
+                                     : (uint32_t)(std::lower_bound(tv.begin(), tv.end(), v) - tv.begin());
+    return (k << f->rank_shift) | (fid << f->col_shift) | ((e.y & kMetaDefLeft) ? 1u : 0u);
+  };
+  const int64_t W = (int64_t)1 << (D + 1), L = (int64_t)1 << D;
+  h.qwords.assign((size_t)T * W, 0u);
+  h.leaf_origin.assign((size_t)T * L, -1);
+  h.sp_deepq.assign((size_t)total, make_uint2(0u, kMetaLeaf));
+  std::vector<int32_t> at((size_t)W);
+  for (int t = 0; t < T; ++t) {
+    const int64_t base = h.tree_offsets[t], n = h.tree_offsets[t + 1] - base;
+    const int64_t chunk_base = h.tree_offsets[t / f->trees_per_chunk * f->trees_per_chunk];
+    if (base + n - chunk_base > (int64_t)1 << 22) { give_up(); return; }   // the marker keeps 22 bits of node index
+    uint32_t* out = h.qwords.data() + (int64_t)t * W;
+    int32_t* lo = h.leaf_origin.data() + (int64_t)t * L;
+    at[1] = 0;
+    for (int64_t i = 1; i < W; ++i) {
+      const int32_t q = at[i];
+      const uint2 e = h.sp_full[base + q];
+      const bool leaf = (e.y & kMetaLeaf) != 0;
+      if (i < L) {
+        if (leaf) {
+          out[i] = 0u;                                   // below a leaf: both children lead to it
+          at[2 * i] = at[2 * i + 1] = q;
+        } else {
+          out[i] = rank_word(e);
+          const int32_t nl = q + (int32_t)((e.y & 0x3FFFFFFFu) >> fb);
+          at[2 * i] = nl;
+          at[2 * i + 1] = nl + 1;
+        }
+      } else if (leaf) {
+        out[i] = e.x;
+        lo[i - L] = h.sp_orig[base + q];
+      } else {
+        out[i] = kContMask | (uint32_t)(base - chunk_base + q);   // the walk goes on below the top
+      }
+    }
+    for (int64_t q = 0; q < n; ++q) {
+      const uint2 e = h.sp_full[base + q];
+      h.sp_deepq[base + q] = (e.y & kMetaLeaf) ? make_uint2(e.x, kMetaLeaf)
+                                               : make_uint2(rank_word(e), (e.y & 0x3FFFFFFFu) >> fb);
+    }
+  }
+}
+
 // ---- shared-memory chunk plan ------------------------------------------------------------
 // Shared memory of one persistent CTA (227 KB opt-in, vs the reference's 0.8 * 48 KB,
 // Struct.h:215-220): [warp tiles][forest chunk][mbarriers].
@@ -611,7 +774,13 @@ double smem_tile_cost(int cols, bool staged, int trees_per_chunk, int depth) {
   return 8.0 + ((double)trees_per_chunk * depth < 100.0 ? 45.0 : 0.0);
 }
 
-void plan_chunks(tahoe_forest* f) {
+void plan_chunks(tahoe_forest* f) { plan_chunks_for(f, f->depth, false); }
+
+// The plan for trees of `depth` levels.  deep: the sparse quantised-tops variant -- every warp also
+// keeps a list of parked deep walks in shared memory, and register-staged tiles may be up to
+// kStagedMaxColsDeep columns wide at <= 8 warps (256 threads: 255 registers each).
+// Returns the modelled cost per sample in node-visit units (< 0: nothing fits).
+static double plan_chunks_for(tahoe_forest* f, int depth, bool deep) {
   f->trees_per_chunk = 0;
   f->num_chunks = 0;
   f->smem_bytes = 0;
@@ -620,11 +789,10 @@ void plan_chunks(tahoe_forest* f) {
   f->quant_stride = 1;
   f->quant_smem = 0;
   f->qwords_trees = f->params.num_trees;
-  if (!f->quant) return;
+  if (!f->quant && !deep) return -1.0;
   const int T = f->params.num_trees, C = f->params.num_cols;
   const size_t tile_bytes = (size_t)C * 128;
-  const size_t bars = 1024;
-  const size_t tree_bytes = ((size_t)1 << (f->depth + 1)) * 4;
+  const size_t tree_bytes = ((size_t)1 << (depth + 1)) * 4;
   int want_warps = 0, want_staged = -1, want_group = 0;   // TAHOE_SMEM_PLAN="warps,staged,group"
   if (const char* e = std::getenv("TAHOE_SMEM_PLAN")) std::sscanf(e, "%d,%d,%d", &want_warps, &want_staged, &want_group);
 
@@ -634,9 +802,10 @@ void plan_chunks(tahoe_forest* f) {
   bool found = false;
   for (int warps = kSmemMaxWarps; warps >= 4; warps >>= 1) {
     if (want_warps && warps != want_warps) continue;
+    const size_t bars = 1024 + (deep ? (size_t)warps * kDeepPend * 128 : 0);   // + lane-private parking lists
     for (int staged = 0; staged <= 1; ++staged) {
       if (want_staged >= 0 && staged != want_staged) continue;
-      if (staged && C > kStagedMaxCols) continue;
+      if (staged && C > ((deep && warps <= 8) ? kStagedMaxColsDeep : kStagedMaxCols)) continue;
       const int slots = warps * (staged ? 1 : 2);
       // wide column field (column-major tile region) when rank + column bits leave room for it,
       // else the compact field with a slot-major region whose columns are padded to a power of two
@@ -648,12 +817,13 @@ void plan_chunks(tahoe_forest* f) {
       const int max_tpc = (int)std::min<size_t>(avail / tree_bytes, (size_t)T + kMaxGroup);   // padding trees count
       for (int G = 1; G <= std::min(kMaxGroup, max_tpc); ++G) {
         if (want_group && G != want_group) continue;
+        if (deep && (G & 1)) continue;                 // the deep variant is built for 2, 4, 6 trees per group
         const int tpad = (T + G - 1) / G * G;          // all-zero trees pad the forest to whole groups
         int tpc = std::min(max_tpc / G * G, tpad);
         const int chunks = (tpad + tpc - 1) / tpc;     // balance: same chunk count, even whole groups
         tpc = ((tpad + chunks - 1) / chunks + G - 1) / G * G;
-        const double visits = (double)tpad * std::max(f->depth, 1) * smem_visit_cost(warps, G, staged != 0);
-        const double cost = visits + (double)chunks * smem_tile_cost(C, staged != 0, tpc, std::max(f->depth, 1));
+        const double visits = (double)tpad * std::max(depth, 1) * smem_visit_cost(warps, G, staged != 0);
+        const double cost = visits + (double)chunks * smem_tile_cost(C, staged != 0, tpc, std::max(depth, 1));
         if (!found || cost < best) {
           found = true; best = cost;
           f->warps = warps; f->staged = staged != 0; f->slots = slots; f->group = G;
@@ -668,7 +838,7 @@ void plan_chunks(tahoe_forest* f) {
       }
     }
   }
-  if (!found) { f->quant = false; return; }
+  if (!found) { f->quant = false; return -1.0; }
 
   // k_quantize: one column's sorted thresholds (every quant_stride-th of them when the column is
   // too long) + its bucket index live in shared memory
@@ -682,6 +852,7 @@ void plan_chunks(tahoe_forest* f) {
   if (S == 2) S = 4;   // the in-block count reads whole float4s
   f->quant_stride = S;
   f->quant_smem = lut_bytes + (max_n / S + 1) * 4 + 16;
+  return best;
 }
 
 int query_device(tahoe_forest* f) {
@@ -723,6 +894,7 @@ int upload(tahoe_forest* f) {
   if ((rc = to_device(&f->d_sp_full, h.sp_full))) return rc;
   if ((rc = to_device(&f->d_sp_orig, h.sp_orig))) return rc;
   if ((rc = to_device(&f->d_sp_top, h.sp_top))) return rc;
+  if ((rc = to_device(&f->d_sp_deepq, h.sp_deepq))) return rc;
   if ((rc = to_device(&f->d_tree_offsets, h.tree_offsets))) return rc;
   if ((rc = to_device(&f->d_inter, h.inter))) return rc;
   if ((rc = to_device(&f->d_tree_order, h.tree_order))) return rc;
@@ -731,7 +903,7 @@ int upload(tahoe_forest* f) {
   if ((rc = to_device(&f->d_sd_blocks, h.sd_blocks))) return rc;
   if ((rc = to_device(&f->d_sd_orig_bottom, h.sd_orig_bottom))) return rc;
   if (!h.qwords.empty()) {   // padded with all-zero trees to whole traversal groups
-    const size_t W = (size_t)1 << (f->depth + 1);
+    const size_t W = (size_t)1 << (f->qdepth + 1);
     const size_t words = (size_t)f->qwords_trees * W;
     TAHOE_CUDA(cudaMalloc((void**)&f->d_qwords, words * 4));
     TAHOE_CUDA(cudaMemset(f->d_qwords, 0, words * 4));

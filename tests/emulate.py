@@ -202,3 +202,53 @@ def sparse_bfs_traverse(nodes8, orig, offsets, fid_bits, cut, data, missing):
         vals[:, t] = nd[base + n, 0].view(np.float32)
         ids[:, t] = orig[base + n]
     return vals, ids, deep
+
+
+CONT = 0xFFC00000
+
+
+def qtop_traverse(qwords, leaf_origin, deepq, deep_orig, offsets, T, depth, F, col_mask, miss_code, col_shift, tpc):
+    """QT (k_smem_forest<DEEP>): dense rank-quantised tops [T'][2^(depth+1)] + breadth-first rank-form
+    nodes for the walks that leave them.  F = rank words [R,C].
+    -> (values [R,T], caller's leaf node index [R,T], walks parked [R,T] bool)"""
+    W, L = 1 << (depth + 1), 1 << depth
+    q = qwords.reshape(-1, W)
+    lo = leaf_origin.reshape(T, L)
+    dq = deepq.reshape(-1, 2)
+    R = F.shape[0]
+    rows = np.arange(R)
+    vals = np.zeros((R, T), np.float32)
+    ids = np.zeros((R, T), np.int32)
+    parked = np.zeros((R, T), bool)
+
+    def right(Fv, N):
+        c = Fv > N
+        return np.where(Fv == np.uint32(miss_code), (N & np.uint32(1)) == 0, c)
+
+    for t in range(T):
+        n = np.ones(R, np.int64)
+        for _ in range(depth):
+            N = q[t, n]
+            col = ((N & np.uint32(col_mask)) >> np.uint32(col_shift)).astype(np.int64)
+            n = 2 * n + right(F[rows, col], N)
+        v = q[t, n]
+        cont = (v & np.uint32(CONT)) == np.uint32(CONT)
+        parked[:, t] = cont
+        vals[~cont, t] = v[~cont].view(np.float32)
+        ids[~cont, t] = lo[t, n[~cont] - L]
+        assert np.all(lo[t, n[~cont] - L] >= 0)
+        # the parked walks go on in the rank-form breadth-first nodes
+        r = np.nonzero(cont)[0]
+        # the marker's index is relative to the first node of the chunk's first tree
+        base = int(offsets[t // tpc * tpc])
+        node = (v[r] & np.uint32(~CONT & 0xFFFFFFFF)).astype(np.int64)
+        assert np.all(base + node >= offsets[t]) and np.all(base + node < offsets[t + 1])
+        while r.size:
+            e = dq[base + node]
+            leaf = (e[:, 1] >> 31) != 0
+            vals[r[leaf], t] = e[leaf, 0].view(np.float32)
+            ids[r[leaf], t] = deep_orig[base + node[leaf]]
+            r, node, e = r[~leaf], node[~leaf], e[~leaf]
+            col = ((e[:, 0] & np.uint32(col_mask)) >> np.uint32(col_shift)).astype(np.int64)
+            node = node + e[:, 1].astype(np.int64) + right(F[r, col], e[:, 0])
+    return vals, ids, parked

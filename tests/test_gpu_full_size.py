@@ -98,9 +98,10 @@ def test_sparse_config_full_size(oracle):
     f.predict(sub, strategy=api.DIRECT, leaf_ids=ids)
     torch.cuda.synchronize()
     assert np.array_equal(ids.cpu().numpy(), wids)
-    # tree tops in shared memory, deep walks finished in L2: exact leaves, re-ordered float sum
+    # quantised tree tops in shared memory (QT), deep walks finished in L2: exact leaves, re-ordered float sum
     info = f.info()
-    assert f.applicable(api.SPLIT_SHARED_FOREST, R) and info.num_chunks > 1 and info.sparse_deep_walks > 0
+    assert f.applicable(api.SPLIT_SHARED_FOREST, R) and info.sparse_top_active == 1
+    assert info.sparse_top_chunks > 1 and info.sparse_top_deep_walks > 0
     s = f.predict(data, strategy=api.SPLIT_SHARED_FOREST).cpu().numpy()
     mass_all = 2000.0          # |leaf| <= 1 in the generator: a bound on every row's L1 mass
     assert np.all(np.abs(s.astype(np.float64) - a.astype(np.float64)) <= 1e-5 * mass_all)

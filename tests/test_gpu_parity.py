@@ -115,6 +115,7 @@ def test_sparse_forest_through_shared_memory(oracle, monkeypatch, cut, tpc, rows
     """k_sparse_smem: tree tops in shared memory, deep walks parked and finished in L2.  Small cuts and
     chunk sizes force many parked walks, partial drains and several chunks; leaf ids stay exact, the
     score is a re-ordered float sum."""
+    monkeypatch.setenv("TAHOE_SPARSE_PATH", "t8")      # the quantised tops (QT) are the default path now
     if cut is not None:
         monkeypatch.setenv("TAHOE_SPARSE_CUT", str(cut))
         monkeypatch.setenv("TAHOE_SPARSE_TPC", str(tpc))
@@ -135,6 +136,48 @@ def test_sparse_forest_through_shared_memory(oracle, monkeypatch, cut, tpc, rows
     assert score_close(got2, want, leafvals)
     got2b, _ = _run(f, data, api.SPLIT_SHARED_FOREST, want_ids=False)
     assert bits_equal(got2, got2b)                                        # reproducible run to run
+    if f.applicable(api.SHARED_FOREST, rows):
+        got3, _ = _run(f, data, api.SHARED_FOREST, want_ids=False)
+        assert bits_equal(got2, got3)
+
+
+@pytest.mark.parametrize("depth,tpc,plan,rows", [(None, None, None, 3000), (2, 6, "16,0,6", 3000), (5, 12, "8,1,6", 33),
+                                                 (1, 2, "8,0,2", 2368 * 32 + 5), (8, 64, "4,1,4", 1),
+                                                 (12, None, "8,1,2", 700), (3, 4, "16,0,4", 40_000)])
+def test_sparse_forest_quantised_tops(oracle, monkeypatch, depth, tpc, plan, rows):
+    """k_smem_forest<DEEP> on the QT layout: dense rank-quantised tops in shared memory, walks still on an
+    internal node below them parked and finished 64 at a time in L2.  Shallow tops and small chunks force
+    many parked walks, full and partial drains and several chunks; every tile plan (TMA double-buffered,
+    register-staged 64 columns wide); leaf ids stay exact, the score is a re-ordered float sum."""
+    if depth is not None:
+        monkeypatch.setenv("TAHOE_QTOP_DEPTH", str(depth))
+    if tpc is not None:
+        monkeypatch.setenv("TAHOE_QTOP_TPC", str(tpc))
+    if plan is not None:
+        monkeypatch.setenv("TAHOE_SMEM_PLAN", plan)
+    sp, offs, w, lv = synth.gen_sparse_forest(4242, 64, 12, 50)
+    data = synth.gen_data(4343, rows, 50, miss_frac=0.01, nan_frac=0.005)
+    want, wids = oracle.predict_sparse(sp, offs, data, -999.0, want_leaf_ids=True)
+    f = api.Forest.from_sparse(sp, offs, 50, weights=w, missing=-999.0)
+    info = f.info()
+    assert info.sparse_top_active == 1
+    if depth is not None:
+        assert info.sparse_top_depth == depth
+    if plan is not None:
+        assert (info.smem_warps, info.smem_staged, info.smem_group) == tuple(int(x) for x in plan.split(","))
+    if tpc is not None:
+        assert info.sparse_top_trees_per_chunk <= max(tpc, info.smem_group) and info.sparse_top_chunks > 1
+    assert f.applicable(api.SPLIT_SHARED_FOREST, rows)
+    leafvals = np.abs(sp["val"][offs[:-1][None, :] + wids]).sum(1)       # L1 mass of each row's summands
+    got, ids = _run(f, data, api.SPLIT_SHARED_FOREST)
+    assert np.array_equal(ids, wids)
+    assert score_close(got, want, leafvals)
+    got2, _ = _run(f, data, api.SPLIT_SHARED_FOREST, want_ids=False)      # the perf instantiation
+    assert score_close(got2, want, leafvals)
+    got2b, _ = _run(f, data, api.SPLIT_SHARED_FOREST, want_ids=False)
+    assert bits_equal(got2, got2b)                                        # reproducible run to run
+    if depth == 12:                                                        # whole trees in the tops: tree order, CPU bits
+        assert info.sparse_top_deep_walks == 0.0 and bits_equal(got2, want)
     if f.applicable(api.SHARED_FOREST, rows):
         got3, _ = _run(f, data, api.SHARED_FOREST, want_ids=False)
         assert bits_equal(got2, got3)

@@ -241,3 +241,58 @@ def test_sparse_breadth_first_layout(oracle, cut, monkeypatch):
         assert np.all(top[t, n:, 1] == 1) and np.all(top[t, n:, 0] == 0)
     # uniform random features: the measured share of deep walks is near the planner's estimate
     assert abs(deep.mean() - info.sparse_deep_walks) < 0.05
+
+
+@pytest.mark.parametrize("depth,tpc", [(None, None), (1, None), (3, 6), (6, 12), (12, None)])
+def test_sparse_quantised_tops_layout(oracle, depth, tpc, monkeypatch):
+    """QT (sparse forests through k_smem_forest<DEEP>): the dense rank-quantised tops plus the rank-form
+    breadth-first nodes walk to the oracle's leaves; continuation markers sit exactly where a walk is
+    still on an internal node at the top's bottom level; the planner's parked-walk estimate is sane."""
+    if depth is not None:
+        monkeypatch.setenv("TAHOE_QTOP_DEPTH", str(depth))
+    if tpc is not None:                      # several chunks: the markers are chunk-relative
+        monkeypatch.setenv("TAHOE_QTOP_TPC", str(tpc))
+    sp, offs, w, lv = synth.gen_sparse_forest(99, 24, 12, 50)
+    data = synth.gen_data(98, 600, 50, miss_frac=0.02, nan_frac=0.01)
+    want, wids = oracle.predict_sparse(sp, offs, data, -999.0, want_leaf_ids=True)
+    f = api.Forest.from_sparse(sp, offs, 50, weights=w, missing=-999.0)
+    info = f.info()
+    assert info.quantized == 0 and info.sparse_top_active == 1
+    D = info.sparse_top_depth
+    assert 1 <= D <= 12 and (depth is None or D == depth)
+    assert info.sparse_top_trees_per_chunk >= 2 and info.sparse_top_trees_per_chunk % info.smem_group == 0
+    assert tpc is None or (info.sparse_top_trees_per_chunk <= tpc and info.sparse_top_chunks >= 2)
+    assert info.rank_bits + info.col_bits + 7 <= 32 and info.col_shift >= 7
+    shift = 32 - info.rank_bits
+    miss_code = ((1 << info.rank_bits) - 1) << shift
+    col_mask = ((1 << info.col_bits) - 1) << info.col_shift
+    table = f.export(api.EXPORT_QUANT_TABLE, np.float32)
+    qoffs = f.export(api.EXPORT_QUANT_OFFSETS, np.int32)
+    F = emulate.quantize_rows(data, table, qoffs, shift, miss_code, -999.0)
+    qwords = f.export(api.EXPORT_QUANT_WORDS, np.uint32)
+    assert qwords.size == 24 * (1 << (D + 1))     # (the padding trees of the last group exist on the device only)
+    vals, ids, parked = emulate.qtop_traverse(qwords, f.export(api.EXPORT_LEAF_ORIGIN, np.int32),
+                                              f.export(api.EXPORT_SPARSE_DEEPQ, np.uint32),
+                                              f.export(api.EXPORT_SPARSE_BFS_ORIG, np.int32), offs, 24, D, F,
+                                              col_mask, miss_code, info.col_shift, info.sparse_top_trees_per_chunk)
+    assert np.array_equal(ids, wids)
+    np.testing.assert_allclose(vals.sum(1, dtype=np.float64), want.astype(np.float64), rtol=1e-5, atol=1e-5)
+    # a walk is parked exactly when its leaf lies deeper than the top
+    leaf_level = lv[offs[:-1][None, :] + wids]
+    assert np.array_equal(parked, leaf_level > D)
+    assert abs(parked.mean() - info.sparse_top_deep_walks) < 0.05
+    if D == 12:
+        assert info.sparse_top_deep_walks == 0.0 and not parked.any()
+
+
+def test_sparse_quantised_tops_refused_for_marker_like_leaves():
+    """A leaf value whose bits look like a continuation marker (negative quiet NaN) keeps the forest on
+    the 8-byte breadth-first tops."""
+    sp, offs, w, lv = synth.gen_sparse_forest(7, 4, 6, 10)
+    leaf = np.nonzero(sp["bits"] < 0)[0][0]
+    sp = sp.copy()
+    sp["val"][leaf] = np.array([0xFFC00123], np.uint32).view(np.float32)[0]
+    f = api.Forest.from_sparse(sp, offs, 10, weights=w, missing=-999.0)
+    info = f.info()
+    assert info.sparse_top_depth == 0 and info.sparse_top_active == 0 and info.sparse_cut >= 32
+    assert f.applicable(api.SPLIT_SHARED_FOREST, 10)
