@@ -34,7 +34,7 @@ constexpr int kSmemMaxWarps = 16;                // 512 threads, one persistent 
 constexpr int kMaxGroup = 6;                     // trees traversed together by one thread (ILP): 1..6
 constexpr int kStagedMaxCols = 32;               // register-staged tiles keep one word per column per lane
 constexpr int kStagedMaxColsDeep = 64;           // ... the sparse (deep) variant at <= 8 warps: 255 registers per thread
-constexpr int kDeepPend = 24;                    // parked deep walks one LANE can hold (4 bytes each) before its warp must drain
+constexpr int kDeepPend = 16;                    // ring of parked deep walks per LANE (4 bytes each, power of two): k_smem_forest_deep
 constexpr int ilog2_c(int v) { return v <= 1 ? 0 : 1 + ilog2_c(v >> 1); }
 
 constexpr int kSparseWarps = 16;                 // k_sparse_smem: warps per persistent CTA

@@ -1,0 +1,242 @@
+// kernels_smem_deep.cuh -- k_smem_forest_deep: SHARED_FOREST / SPLIT_SHARED_FOREST on SPARSE forests
+// (QT layout, packer.cu plan_sparse_qtop).  The reference's sparse forest is disabled
+// (BaseTahoeTest.h:727-846); its walk is Struct.h:2231-2244, its shared-forest strategies are
+// Struct.h:1245-1606.  Included by kernels_smem_depth.cu (one translation unit per top depth).
+//
+// The top DEPTH levels of every tree are a dense rank-quantised heap in shared memory, walked by
+// the six-instruction visit of k_smem_forest (traverse_group).  A walk that is still on an internal
+// node at the bottom of the top reads a continuation marker there and is PARKED in a lane-private
+// ring; it is finished in L2 on the breadth-first rank-form nodes (`deep`).
+//
+// The L2 round trips of those deep walks never stall the warp: every lane keeps K deep walks in
+// flight and advances each by ONE level per traversal group -- the node loads are issued before the
+// group's shared-memory walk (~1.5 k cycles) and consumed after it.  So that a deep walk may outlive
+// the tile that parked it, a warp owns TWO tile buffers (current and previous tile; the next tile
+// waits in registers): a walk reads its features from the buffer of its own tile, the score of tile
+// n is written at the end of tile n + 1, and only the walks of tile n - 1 that are STILL unfinished
+// then (few: they had a whole tile of groups to run) are finished with the latency exposed.
+#pragma once
+#include "kernels_smem_traverse.cuh"
+
+namespace tahoe {
+
+// 8-byte read-only load; volatile so that it is issued where it is written (before the
+// shared-memory walk that hides its latency), not sunk to its first use
+__device__ __forceinline__ uint2 ldg_nc_u2(uint64_t addr) {
+  uint2 v;
+  asm volatile("ld.global.nc.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(addr));
+  return v;
+}
+
+// Shared-memory map (byte offsets from smem[]):
+//   [0, tile_region)               tile region, TWO buffers per warp (slot = warp*2 + parity of the tile)
+//   [.., + trees_per_chunk*W*4)    the resident chunk of dense tops
+//   [.., + 512)                    the chunk mbarrier
+//   [.., + warps*kDeepPend*128)    parked walks: lane-private rings, entry i of lane l at (i*32 + l)*4
+// PIECES: 16-byte pieces of the staged (next) tile one lane keeps in registers (8: <= 32 columns;
+// 16: <= 64 columns, plans of <= 8 warps).  K: deep walks in flight per lane.
+template <int DEPTH, int G, bool LEAF_IDS, int PIECES, int K>
+__global__ void __launch_bounds__(PIECES > kStagedMaxCols / 4 ? 256 : kSmemMaxThreads, 1)
+k_smem_forest_deep(SmemParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  constexpr uint32_t W = 1u << (DEPTH + 1);      // words per tree
+  constexpr uint32_t L = 1u << DEPTH;            // bottom slots per tree
+  constexpr uint32_t kOffMask = kDeepPend * 128 - 1;   // ring positions are byte offsets, 128 apart
+  static_assert((kDeepPend & (kDeepPend - 1)) == 0, "ring size must be a power of two");
+  static_assert(kDeepPend > kMaxGroup + 1, "a traversal group must fit the ring");
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nwarps = blockDim.x >> 5;
+  const uint32_t forest_off = p.tile_region;
+  const uint32_t bars_off = forest_off + (uint32_t)p.trees_per_chunk * W * 4u;
+  const uint32_t s_base = smem_u32(smem);
+  const uint32_t bar_chunk = s_base + bars_off;
+  uint8_t* ring = smem + bars_off + 512 + warp * (kDeepPend * 128) + lane * 4;   // entry at ring + offset
+
+  if (threadIdx.x == 0) {
+    mbar_init(bar_chunk, 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  const size_t warp_global = (size_t)blockIdx.x * nwarps + warp;
+  const size_t warp_stride = (size_t)gridDim.x * nwarps;
+  uint32_t chunk_phase = 0;
+
+  // the next tile waits in registers: cols*8 consecutive 16-byte pieces of [col][32 lanes]
+  uint4 st[PIECES];
+  const int npieces = p.cols * 8;
+  auto fetch_tile = [&](size_t tile) {
+    const uint4* src = reinterpret_cast<const uint4*>(p.qtiles + tile * (size_t)p.cols * 32) + lane;
+#pragma unroll
+    for (int j = 0; j < PIECES; ++j)
+      if (lane + 32 * j < npieces) st[j] = __ldg(src + 32 * j);
+  };
+  auto commit_tile = [&](int b) {
+    const uint32_t dst = s_base + (uint32_t)(warp * 2 + b) * p.slot_stride + (uint32_t)(lane & 7) * 16u +
+                         (uint32_t)(lane >> 3) * p.col_stride;
+#pragma unroll
+    for (int j = 0; j < PIECES; ++j)
+      if (lane + 32 * j < npieces) sts_u128(dst + (uint32_t)(4 * j) * p.col_stride, st[j]);
+  };
+
+  // ---- deep walks of this lane -----------------------------------------------------------
+  // A slot always walks something: an idle slot sits on the DUMMY leaf the packer appends after the
+  // last node (value +0.0f), so a step needs no "slot in use" state -- reaching a leaf, real or
+  // dummy, adds its value and frees the slot for the next parked walk.
+  const uint32_t sl0 = (uint32_t)(warp * 2) * p.slot_stride + lane * 4u;   // this lane in the warp's buffer 0
+  uint32_t node[K];            // breadth-first node index, relative to the chunk's first node
+  uint32_t fb[K];              // sl0 or sl0 + slot_stride: the tile buffer the walk's row lives in
+  uint2 e[K];                  // the node `node[w]`, loaded by the previous step
+#pragma unroll
+  for (int w = 0; w < K; ++w) { node[w] = 0; fb[w] = sl0; e[w] = make_uint2(0u, kMetaLeaf); }
+  // ring of parked walks {node index | tile parity << 31}: pop at head, push at tail (byte offsets;
+  // at most kDeepPend - 1 entries, so head == tail means empty)
+  uint32_t head = 0, tail = 0;
+
+  for (int chunk = 0; chunk < p.num_chunks; ++chunk) {
+    const int tree0 = chunk * p.trees_per_chunk;
+    const int ntrees = min(p.trees_per_chunk, p.padded_trees - tree0);   // a multiple of G
+    __syncthreads();                         // everyone is done reading the previous chunk
+    if (threadIdx.x == 0) {
+      fence_proxy_async();
+      const uint32_t bytes = (uint32_t)ntrees * W * 4u;
+      mbar_expect_tx(bar_chunk, bytes);
+      const uint8_t* src = (const uint8_t*)(p.qwords + (size_t)tree0 * W);
+      uint32_t done = 0;
+      while (done < bytes) {
+        const uint32_t piece = min(bytes - done, 65536u);
+        bulk_g2s(s_base + forest_off + done, src + done, piece, bar_chunk);
+        done += piece;
+      }
+    }
+    size_t tile = warp_global;
+    if (tile < p.num_tiles) fetch_tile(tile);
+    mbar_wait(bar_chunk, chunk_phase);
+    chunk_phase ^= 1;
+
+    const bool first = (chunk == 0), last = (chunk == p.num_chunks - 1);
+    const int64_t chunk_first = __ldg(p.tree_offsets + min(tree0, p.num_trees));
+    const uint32_t dummy = (uint32_t)(__ldg(p.tree_offsets + p.num_trees) - chunk_first);
+    uint64_t cdv = (uint64_t)(p.deep + chunk_first);   // kept as one 64-bit register: node address = one IMAD.WIDE
+    asm volatile("" : "+l"(cdv));
+#pragma unroll
+    for (int w = 0; w < K; ++w) node[w] = dummy;       // nothing is in flight at a chunk boundary
+    int buf = 0;
+    // the tile's missing flag and this lane's partial sum are fetched one tile ahead
+    uint32_t flag_next = 0;
+    float acc_next = 0.0f;
+    if (tile < p.num_tiles) {
+      flag_next = __ldg(p.tile_flags + tile);
+      const size_t r0 = tile * 32 + lane;
+      if (!first && r0 < p.rows) acc_next = p.preds[r0];
+    }
+
+    // current / previous tile of this warp
+    uint32_t cur_sl = sl0, prev_sl = 0xFFFFFFFFu, prev_par = 0;
+    size_t row = 0, row_prev = 0;
+    bool have_prev = false, live_prev = false;
+    float acc_prev = 0.0f;       // top part of the previous tile's sum
+    float dacc_prev = 0.0f, dacc_cur = 0.0f;   // leaf values the deep walks of each tile have reached
+
+    // one level of every walk in flight: consume the node loaded by the previous step, start a
+    // parked walk in a slot that reached its leaf, issue the next node load
+    auto deep_step = [&]() {
+#pragma unroll
+      for (int w = 0; w < K; ++w) {
+        const uint32_t x = e[w].x, y = e[w].y;
+        const bool leaf = (int32_t)y < 0;
+        // (a leaf's x is its float value: keep its bits out of the address)
+        const uint32_t F = lds_u32(s_base + (((leaf ? 0u : x) & p.col_mask) | fb[w]));
+        bool c = F > x;
+        if (F == p.miss_code) c = !(x & 1u);                     // sentinel: !def_left (BaseTahoeTest.h:452)
+        const float v = leaf ? __uint_as_float(x) : 0.0f;
+        const bool pv = fb[w] == prev_sl;
+        if (pv) dacc_prev += v; else dacc_cur += v;
+        if (LEAF_IDS && leaf && node[w] != dummy) {
+          const int64_t nd = chunk_first + (int64_t)node[w];
+          int lo = tree0, hi = min(tree0 + ntrees, p.num_trees);   // tree_offsets[lo] <= nd < tree_offsets[hi]
+          while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (__ldg(p.tree_offsets + mid) <= nd) lo = mid; else hi = mid;
+          }
+          p.leaf_ids[(pv ? row_prev : row) * (size_t)p.num_trees + lo] = __ldg(p.deep_orig + nd);
+        }
+        const bool can = leaf && head != tail;
+        const uint32_t ent = *reinterpret_cast<const uint32_t*>(ring + head);   // (stale when !can: unused)
+        head = can ? (head + 128u) & kOffMask : head;
+        const uint32_t stepped = node[w] + y + (c ? 1u : 0u);
+        node[w] = can ? (ent & 0x7FFFFFFFu) : (leaf ? dummy : stepped);
+        fb[w] = can ? sl0 + (ent >> 31) * p.slot_stride : fb[w];
+        e[w] = ldg_nc_u2(cdv + (uint64_t)node[w] * 8u);
+      }
+    };
+    // finish what is left of the previous tile's walks (latency exposed), then write its score
+    auto retire_prev = [&]() {
+      while (true) {
+        // the ring is first-in first-out: entries of the previous tile, if any, are at its head
+        bool mine = head != tail && (*reinterpret_cast<const uint32_t*>(ring + head) >> 31) == prev_par;
+#pragma unroll
+        for (int w = 0; w < K; ++w) mine |= node[w] != dummy && fb[w] == prev_sl;
+        if (!__any_sync(0xffffffffu, mine)) break;
+        deep_step();
+      }
+      if (live_prev) {
+        const float s = acc_prev + dacc_prev;
+        p.preds[row_prev] = last ? apply_transform(s, p.tf) : s;
+      }
+    };
+
+    for (; tile < p.num_tiles; tile += warp_stride) {
+      const size_t next = tile + warp_stride;
+      __syncwarp();
+      float acc = acc_next;
+      const bool has_missing = flag_next != 0;
+      commit_tile(buf);                      // buffer `buf` held tile n-2: all of its walks are retired
+      __syncwarp();
+      if (next < p.num_tiles) {
+        fetch_tile(next);                    // lands while this tile is traversed
+        flag_next = __ldg(p.tile_flags + next);
+        const size_t rn = next * 32 + lane;
+        acc_next = (!first && rn < p.rows) ? p.preds[rn] : 0.0f;
+      }
+      row = tile * 32 + lane;
+      const bool live = row < p.rows;
+      cur_sl = sl0 + (uint32_t)buf * p.slot_stride;
+      const uint32_t park_tag = (uint32_t)buf << 31;
+      const bool park = live && !p.debug_no_drain;   // (TAHOE_QTOP_NODRAIN: timing experiments, wrong scores)
+
+      for (int t = 0; t < ntrees; t += G) {
+        // room for G more parked walks in every lane's ring (rarely taken)
+        while (__any_sync(0xffffffffu, ((tail - head) & kOffMask) > (uint32_t)(kDeepPend - 1 - G) * 128u)) deep_step();
+        deep_step();
+        uint32_t a[G];
+        const uint32_t tree_abs = s_base + forest_off + (uint32_t)t * W * 4u;
+        if (has_missing) traverse_group<DEPTH, G, true>(tree_abs, s_base, cur_sl, p.col_mask, p.miss_code, a);
+        else traverse_group<DEPTH, G, false>(tree_abs, s_base, cur_sl, p.col_mask, p.miss_code, a);
+        uint32_t v[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) v[g] = lds_u32(a[g]);
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          const bool cont = park && v[g] >= kContMask;           // marker: all of the top ten bits set
+          acc += cont ? 0.0f : __uint_as_float(v[g]);
+          // the slot at tail is free: write it anyway, keep it only for a parked walk
+          *reinterpret_cast<uint32_t*>(ring + tail) = (v[g] & ~kContMask) | park_tag;
+          tail = cont ? (tail + 128u) & kOffMask : tail;
+          if (LEAF_IDS && live && !cont && tree0 + t + g < p.num_trees)
+            p.leaf_ids[row * (size_t)p.num_trees + tree0 + t + g] =
+                __ldg(p.leaf_origin + (size_t)(tree0 + t + g) * L + ((a[g] - tree_abs - g * W * 4u) / 4 - L));
+        }
+      }
+      if (have_prev) retire_prev();
+      // this tile becomes the previous one
+      have_prev = true; live_prev = live; row_prev = row; prev_sl = cur_sl;
+      acc_prev = acc; dacc_prev = dacc_cur; dacc_cur = 0.0f;
+      prev_par = (uint32_t)buf;
+      buf ^= 1;
+    }
+    if (have_prev) retire_prev();            // end of the chunk: nothing stays in flight
+  }
+}
+
+}  // namespace tahoe

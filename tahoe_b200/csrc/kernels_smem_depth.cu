@@ -3,6 +3,11 @@
 // object exports launch_smem_depth_<N>(), which picks the instantiation the handle's plan names:
 // trees per group (1..6), TMA double-buffered or register-staged tiles.
 #include "kernels_smem_traverse.cuh"
+#include "kernels_smem_deep.cuh"
+
+#ifndef TAHOE_DEEP_WALKS
+#define TAHOE_DEEP_WALKS 4   // deep walks in flight per lane (k_smem_forest_deep)
+#endif
 
 #ifndef TAHOE_DEPTH
 #error "compile with -DTAHOE_DEPTH=<1..14>"
@@ -22,18 +27,16 @@ int TAHOE_CAT(launch_smem_depth_, TAHOE_DEPTH)(tahoe_forest* f, const SmemParams
     return TAHOE_OK;
   };
 #if TAHOE_DEPTH <= 12
-  // sparse forests (QT layout): dense tops of depth D, deep walks parked and finished in L2
+  // sparse forests (QT layout): dense tops of depth D, deep walks pipelined through L2 (kernels_smem_deep.cuh)
   if (f->sparse) {
-    const bool wide = f->staged && p.cols > kStagedMaxCols;     // 64-column register staging, <= 8 warps
+    constexpr int K = TAHOE_DEEP_WALKS;
+    constexpr int P8 = kStagedMaxCols / 4, P16 = kStagedMaxColsDeep / 4;
+    const bool wide = p.cols > kStagedMaxCols;     // 64-column register staging, <= 8 warps
     if (wide && f->warps > 8) { set_error("64-column staged tiles need a plan of <= 8 warps"); return TAHOE_ERR_INVALID; }
-    if (p.leaf_ids) {
-      if (wide) return go(k_smem_forest<D, 2, true, true, true, kStagedMaxColsDeep / 4>);
-      return f->staged ? go(k_smem_forest<D, 2, true, true, true>) : go(k_smem_forest<D, 2, true, false, true>);
-    }
-#define TAHOE_DEEP_CASE(G)                                                                  \
-  case G:                                                                                   \
-    if (wide) return go(k_smem_forest<D, G, false, true, true, kStagedMaxColsDeep / 4>);    \
-    return f->staged ? go(k_smem_forest<D, G, false, true, true>) : go(k_smem_forest<D, G, false, false, true>);
+    if (p.leaf_ids)
+      return wide ? go(k_smem_forest_deep<D, 2, true, P16, K>) : go(k_smem_forest_deep<D, 2, true, P8, K>);
+#define TAHOE_DEEP_CASE(G) \
+  case G: return wide ? go(k_smem_forest_deep<D, G, false, P16, K>) : go(k_smem_forest_deep<D, G, false, P8, K>);
     switch (f->group) {
       TAHOE_DEEP_CASE(2) TAHOE_DEEP_CASE(4) TAHOE_DEEP_CASE(6)
       default: break;

@@ -30,8 +30,8 @@ struct SmemParams {
   int32_t* leaf_ids;
   const int32_t* leaf_origin;  // [T][2^d]
   Transform tf;
-  // DEEP (sparse forests, QT layout): the trees in qwords are the dense tops; a bottom slot that is a
-  // continuation marker parks the walk, which is finished in L2 on the rank-form breadth-first nodes
+  // k_smem_forest_deep (sparse forests, QT layout): the trees in qwords are the dense tops; a bottom slot that
+  // is a continuation marker parks the walk, which is finished in L2 on the rank-form breadth-first nodes
   const uint2* deep;           // [total] {rank word | leaf value, child delta | leaf<<31}
   const int64_t* tree_offsets; // [T+1]
   const int32_t* deep_orig;    // breadth-first index -> caller's node index
@@ -39,7 +39,6 @@ struct SmemParams {
 };
 
 constexpr uint32_t kContMask = 0xFFC00000u;   // packer.cu: marker = kContMask | node index relative to the chunk's first node
-constexpr int kDeepWalks = 4;                 // parked walks one lane keeps in flight while draining
 
 constexpr int kSmemMaxThreads = kSmemMaxWarps * 32;
 
@@ -98,10 +97,8 @@ __device__ __forceinline__ void sts_u128(uint32_t addr, uint4 v) {
   asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
-// DEEP: see SmemParams.  PIECES: 16-byte pieces of a staged tile one lane keeps in registers (8: up to
-// 32 columns; 16: up to 64 columns, plans of <= 8 warps only).
-template <int DEPTH, int G, bool LEAF_IDS, bool STAGED, bool DEEP = false, int PIECES = kStagedMaxCols / 4>
-__global__ void __launch_bounds__(PIECES > kStagedMaxCols / 4 ? 256 : kSmemMaxThreads, 1) k_smem_forest(SmemParams p) {
+template <int DEPTH, int G, bool LEAF_IDS, bool STAGED>
+__global__ void __launch_bounds__(kSmemMaxThreads, 1) k_smem_forest(SmemParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr uint32_t W = 1u << (DEPTH + 1);      // words per tree
   constexpr uint32_t L = 1u << DEPTH;            // bottom slots per tree
@@ -115,8 +112,6 @@ __global__ void __launch_bounds__(PIECES > kStagedMaxCols / 4 ? 256 : kSmemMaxTh
   const uint32_t s_base = smem_u32(smem);
   const uint32_t bar_chunk = s_base + bars_off;
   const uint32_t bar_tile0 = bar_chunk + 8 + warp * (8 * kBufs);
-  // DEEP: this lane's list of parked walks (after the mbarriers), entry i at pend[i * 32]
-  uint32_t* pend = reinterpret_cast<uint32_t*>(smem + bars_off + 512) + warp * (kDeepPend * 32) + lane;
 
   if (threadIdx.x == 0) {
     mbar_init(bar_chunk, 1);
@@ -144,7 +139,7 @@ __global__ void __launch_bounds__(PIECES > kStagedMaxCols / 4 ? 256 : kSmemMaxTh
   };
   // STAGED path: the tile is cols*8 consecutive 16-byte pieces in global memory ([col][32 lanes]);
   // lane l keeps pieces l, l+32, ... in registers and stores each to its column row
-  constexpr int kPieces = PIECES;                        // per lane
+  constexpr int kPieces = kStagedMaxCols / 4;            // per lane
   uint4 st[STAGED ? kPieces : 1];
   const int npieces = p.cols * 8;
   auto fetch_tile = [&](size_t tile) {
@@ -188,7 +183,6 @@ __global__ void __launch_bounds__(PIECES > kStagedMaxCols / 4 ? 256 : kSmemMaxTh
     chunk_phase ^= 1;
 
     const bool first = (chunk == 0), last = (chunk == p.num_chunks - 1);
-    const uint2* chunk_deep = DEEP ? p.deep + __ldg(p.tree_offsets + min(tree0, p.num_trees)) : nullptr;
     int buf = 0;
     // the tile's missing flag and this lane's partial sum are fetched one tile ahead, so that their
     // global-memory latency hides behind the traversal of the tile before
@@ -225,59 +219,6 @@ __global__ void __launch_bounds__(PIECES > kStagedMaxCols / 4 ? 256 : kSmemMaxTh
       const bool live = row < p.rows;
       const uint32_t slot_lane = (uint32_t)(warp * kBufs + buf) * p.slot_stride + lane * 4u;
 
-      // DEEP: walks still on an internal node below the top are parked in LANE-PRIVATE lists
-      // (pend[slot][lane]: no vote to park, bank = lane) and finished by their own lane in L2 on the
-      // rank-form breadth-first nodes, kDeepWalks at a time, free-running: a walk that reaches its
-      // leaf is replaced by the lane's next parked one.  Features come from this lane's bank of the
-      // warp's rank tile.  The leaf values go straight into the lane's own sum (reproducible).
-      int cnt = 0;                           // parked walks of this lane
-      float acc_deep = 0.0f;
-      auto drain = [&]() {
-        const uint2* ptr[kDeepWalks];
-        bool on[kDeepWalks];
-        int next = 0;
-        if (p.debug_no_drain) cnt = 0;       // timing experiments only (TAHOE_QTOP_NODRAIN): wrong scores
-#pragma unroll
-        for (int w = 0; w < kDeepWalks; ++w) {
-          on[w] = next < cnt;
-          ptr[w] = chunk_deep + (on[w] ? pend[next * 32] : 0u);
-          next += on[w] ? 1 : 0;
-        }
-        while (true) {
-          bool any = false;
-#pragma unroll
-          for (int w = 0; w < kDeepWalks; ++w) any |= on[w];
-          if (!__any_sync(0xffffffffu, any)) break;
-          uint2 e[kDeepWalks];
-#pragma unroll
-          for (int w = 0; w < kDeepWalks; ++w) e[w] = on[w] ? __ldg(ptr[w]) : make_uint2(0u, 0u);
-#pragma unroll
-          for (int w = 0; w < kDeepWalks; ++w) {
-            if (!on[w]) continue;
-            if (e[w].y >> 31) {              // leaf: take the value, start this lane's next parked walk
-              acc_deep += __uint_as_float(e[w].x);
-              if (LEAF_IDS) {
-                const int64_t node = ptr[w] - p.deep;
-                int lo = tree0, hi = min(tree0 + ntrees, p.num_trees);   // tree_offsets[lo] <= node < tree_offsets[hi]
-                while (hi - lo > 1) {
-                  const int mid = (lo + hi) >> 1;
-                  if (__ldg(p.tree_offsets + mid) <= node) lo = mid; else hi = mid;
-                }
-                p.leaf_ids[row * (size_t)p.num_trees + lo] = __ldg(p.deep_orig + node);
-              }
-              on[w] = next < cnt;
-              if (on[w]) { ptr[w] = chunk_deep + pend[next * 32]; ++next; }
-            } else {
-              const uint32_t F = lds_u32(s_base + ((e[w].x & p.col_mask) | slot_lane));
-              bool c = F > e[w].x;
-              if (F == p.miss_code) c = !(e[w].x & 1u);
-              ptr[w] += e[w].y + (c ? 1u : 0u);
-            }
-          }
-        }
-        cnt = 0;
-      };
-
       for (int t = 0; t < ntrees; t += G) {
         uint32_t a[G];
         const uint32_t tree_abs = s_base + forest_off + (uint32_t)t * W * 4u;
@@ -285,26 +226,11 @@ __global__ void __launch_bounds__(PIECES > kStagedMaxCols / 4 ? 256 : kSmemMaxTh
         else traverse_group<DEPTH, G, false>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a);
 #pragma unroll
         for (int g = 0; g < G; ++g) {
-          const uint32_t v = lds_u32(a[g]);
-          bool cont = false;
-          if (DEEP) {
-            cont = live && (v & kContMask) == kContMask;
-            acc += cont ? 0.0f : __uint_as_float(v);
-            if (cont) { pend[cnt * 32] = v & ~kContMask; ++cnt; }   // chunk-relative breadth-first node
-          } else {
-            acc += __uint_as_float(v);             // a padding tree adds +0.0f: the sum keeps its bits
-          }
-          if (LEAF_IDS && live && !cont && tree0 + t + g < p.num_trees)
+          acc += __uint_as_float(lds_u32(a[g]));   // a padding tree adds +0.0f: the sum keeps its bits
+          if (LEAF_IDS && live && tree0 + t + g < p.num_trees)
             p.leaf_ids[row * (size_t)p.num_trees + tree0 + t + g] =
                 __ldg(p.leaf_origin + (size_t)(tree0 + t + g) * L + ((a[g] - tree_abs - g * W * 4u) / 4 - L));
         }
-        if (DEEP) {
-          if (__any_sync(0xffffffffu, cnt > kDeepPend - G)) drain();   // some lane's list could overflow in the next group
-        }
-      }
-      if (DEEP) {
-        drain();
-        acc += acc_deep;
       }
       if (live) p.preds[row] = last ? apply_transform(acc, p.tf) : acc;
       if (!STAGED) buf ^= 1;

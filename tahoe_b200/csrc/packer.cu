@@ -606,12 +606,15 @@ static void plan_sparse_smem(tahoe_forest* f, const tahoe_sparse_node_t* nodes) 
 // holds either the float bits of the leaf the walk has reached or, when the walk is still on an
 // internal node at level D, a continuation marker: a negative quiet NaN whose low 22 bits are the
 // node's breadth-first index relative to the first node of its chunk's first tree.  The kernel parks
-// such walks (lane-private lists) and every lane finishes its own, four at a time, in L2 on `sp_deepq`
+// such walks (lane-private rings) and every lane advances its own, one level per traversal group, in L2 on `sp_deepq`
 // -- the breadth-first nodes in rank form {rank word, child delta | leaf}, compared against the same
 // rank tile in shared memory.  Thresholds of ALL internal nodes go into the
 // rank tables, so one quantise pass serves both parts.
 constexpr uint32_t kContMask = 0xFFC00000u;
-constexpr double kDeepWalkVisits = 60.0;   // one parked deep walk, in shared-memory node-visit units
+// one parked deep walk, in shared-memory node-visit units: its L2 round trips hide behind the traversal
+// groups (k_smem_forest_deep), what is left is ~35 instructions per level of the walk.  Config 4 on B200,
+// 1M rows: top depth 6 / 7 / 8 -> 10.9 / 10.5 / 12.4 ms with 385 / 273 / 194 deep walks per row
+constexpr double kDeepWalkVisits = 20.0;
 
 static void plan_sparse_qtop(tahoe_forest* f) {
   HostPack& h = f->host;
@@ -710,7 +713,7 @@ static void plan_sparse_qtop(tahoe_forest* f) {
   const int64_t W = (int64_t)1 << (D + 1), L = (int64_t)1 << D;
   h.qwords.assign((size_t)T * W, 0u);
   h.leaf_origin.assign((size_t)T * L, -1);
-  h.sp_deepq.assign((size_t)total, make_uint2(0u, kMetaLeaf));
+  h.sp_deepq.assign((size_t)total + 1, make_uint2(0u, kMetaLeaf));   // + the dummy leaf (+0.0f) idle walk slots sit on
   std::vector<int32_t> at((size_t)W);
   for (int t = 0; t < T; ++t) {
     const int64_t base = h.tree_offsets[t], n = h.tree_offsets[t + 1] - base;
@@ -805,8 +808,9 @@ static double plan_chunks_for(tahoe_forest* f, int depth, bool deep) {
     const size_t bars = 1024 + (deep ? (size_t)warps * kDeepPend * 128 : 0);   // + lane-private parking lists
     for (int staged = 0; staged <= 1; ++staged) {
       if (want_staged >= 0 && staged != want_staged) continue;
+      if (deep && !staged) continue;                   // k_smem_forest_deep: the next tile always waits in registers
       if (staged && C > ((deep && warps <= 8) ? kStagedMaxColsDeep : kStagedMaxCols)) continue;
-      const int slots = warps * (staged ? 1 : 2);
+      const int slots = warps * ((staged && !deep) ? 1 : 2);   // deep: current + previous tile per warp
       // wide column field (column-major tile region) when rank + column bits leave room for it,
       // else the compact field with a slot-major region whose columns are padded to a power of two
       const bool wide = f->rank_bits + f->col_bits + kQuantColShift + ilog2_c(slots) <= 32;
@@ -823,7 +827,8 @@ static double plan_chunks_for(tahoe_forest* f, int depth, bool deep) {
         const int chunks = (tpad + tpc - 1) / tpc;     // balance: same chunk count, even whole groups
         tpc = ((tpad + chunks - 1) / chunks + G - 1) / G * G;
         const double visits = (double)tpad * std::max(depth, 1) * smem_visit_cost(warps, G, staged != 0);
-        const double cost = visits + (double)chunks * smem_tile_cost(C, staged != 0, tpc, std::max(depth, 1));
+        // (deep: the tile of a pass is committed from registers under the deep walks of the tile before)
+        const double cost = visits + (double)chunks * (deep ? 10.0 : smem_tile_cost(C, staged != 0, tpc, std::max(depth, 1)));
         if (!found || cost < best) {
           found = true; best = cost;
           f->warps = warps; f->staged = staged != 0; f->slots = slots; f->group = G;
