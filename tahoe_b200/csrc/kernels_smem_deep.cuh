@@ -28,14 +28,23 @@ __device__ __forceinline__ uint2 ldg_nc_u2(uint64_t addr) {
   return v;
 }
 
+// PAIR: rows wider than 32 columns need 64 staging registers per lane, which caps a CTA at 8 warps --
+// two per scheduler, too few to cover the fixed-latency dependencies of the walk.  PAIR runs 16 warps
+// with the shared memory of 8: the two warps of a pair work on the SAME tile (each stages half of its
+// pieces and walks every other traversal group of the chunk), meet at a named barrier before and after
+// the tile is committed, and warp 1 hands its part of a row's sum to warp 0 through shared memory
+// (fixed order: the score stays reproducible).
+//
 // Shared-memory map (byte offsets from smem[]):
-//   [0, tile_region)               tile region, TWO buffers per warp (slot = warp*2 + parity of the tile)
+//   [0, tile_region)               tile region, TWO buffers per unit (unit = warp, or pair of warps;
+//                                  slot = unit*2 + parity of the tile)
 //   [.., + trees_per_chunk*W*4)    the resident chunk of dense tops
 //   [.., + 512)                    the chunk mbarrier
 //   [.., + warps*kDeepPend*128)    parked walks: lane-private rings, entry i of lane l at (i*32 + l)*4
-// PIECES: 16-byte pieces of the staged (next) tile one lane keeps in registers (8: <= 32 columns;
-// 16: <= 64 columns, plans of <= 8 warps).  K: deep walks in flight per lane.
-template <int DEPTH, int G, bool LEAF_IDS, int PIECES, int K>
+//   [.., + 1024)                   PAIR: one float per lane per pair, warp 1 -> warp 0
+// PIECES: 16-byte pieces of the staged (next) tile one lane keeps in registers (8: <= 32 columns, or
+// <= 64 as a pair; 16: <= 64 columns, plans of <= 8 warps).  K: deep walks in flight per lane.
+template <int DEPTH, int G, bool LEAF_IDS, int PIECES, int K, bool PAIR>
 __global__ void __launch_bounds__(PIECES > kStagedMaxCols / 4 ? 256 : kSmemMaxThreads, 1)
 k_smem_forest_deep(SmemParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -46,11 +55,20 @@ k_smem_forest_deep(SmemParams p) {
   static_assert(kDeepPend > kMaxGroup + 1, "a traversal group must fit the ring");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nwarps = blockDim.x >> 5;
+  const int unit = PAIR ? warp >> 1 : warp, half = PAIR ? warp & 1 : 0;
+  const int nunits = PAIR ? nwarps >> 1 : nwarps;
+  constexpr int kSplit = PAIR ? 2 : 1;           // warps that share a tile
   const uint32_t forest_off = p.tile_region;
   const uint32_t bars_off = forest_off + (uint32_t)p.trees_per_chunk * W * 4u;
   const uint32_t s_base = smem_u32(smem);
   const uint32_t bar_chunk = s_base + bars_off;
   uint8_t* ring = smem + bars_off + 512 + warp * (kDeepPend * 128) + lane * 4;   // entry at ring + offset
+  float* xch = reinterpret_cast<float*>(smem + bars_off + 512 + nwarps * (kDeepPend * 128)) + unit * 32 + lane;
+  // the two warps of a pair meet here (named barrier 1 + pair); one warp alone only re-converges
+  auto unit_sync = [&]() {
+    if (PAIR) asm volatile("bar.sync %0, 64;" ::"r"(1 + unit) : "memory");
+    else __syncwarp();
+  };
 
   if (threadIdx.x == 0) {
     mbar_init(bar_chunk, 1);
@@ -58,32 +76,35 @@ k_smem_forest_deep(SmemParams p) {
   }
   __syncthreads();
 
-  const size_t warp_global = (size_t)blockIdx.x * nwarps + warp;
-  const size_t warp_stride = (size_t)gridDim.x * nwarps;
+  const size_t warp_global = (size_t)blockIdx.x * nunits + unit;   // tiles are dealt to units
+  const size_t warp_stride = (size_t)gridDim.x * nunits;
   uint32_t chunk_phase = 0;
 
-  // the next tile waits in registers: cols*8 consecutive 16-byte pieces of [col][32 lanes]
+  // the next tile waits in registers: cols*8 consecutive 16-byte pieces of [col][32 lanes]; this warp
+  // keeps pieces lane + 32 * (kSplit * j + half)
   uint4 st[PIECES];
   const int npieces = p.cols * 8;
   auto fetch_tile = [&](size_t tile) {
     const uint4* src = reinterpret_cast<const uint4*>(p.qtiles + tile * (size_t)p.cols * 32) + lane;
 #pragma unroll
     for (int j = 0; j < PIECES; ++j)
-      if (lane + 32 * j < npieces) st[j] = __ldg(src + 32 * j);
+      if (lane + 32 * (kSplit * j + half) < npieces) st[j] = __ldg(src + 32 * (kSplit * j + half));
   };
   auto commit_tile = [&](int b) {
-    const uint32_t dst = s_base + (uint32_t)(warp * 2 + b) * p.slot_stride + (uint32_t)(lane & 7) * 16u +
+    // piece i: column i / 8, bytes (i % 8) * 16 of that column's 128-byte row
+    const uint32_t dst = s_base + (uint32_t)(unit * 2 + b) * p.slot_stride + (uint32_t)(lane & 7) * 16u +
                          (uint32_t)(lane >> 3) * p.col_stride;
 #pragma unroll
     for (int j = 0; j < PIECES; ++j)
-      if (lane + 32 * j < npieces) sts_u128(dst + (uint32_t)(4 * j) * p.col_stride, st[j]);
+      if (lane + 32 * (kSplit * j + half) < npieces)
+        sts_u128(dst + (uint32_t)(4 * (kSplit * j + half)) * p.col_stride, st[j]);
   };
 
   // ---- deep walks of this lane -----------------------------------------------------------
   // A slot always walks something: an idle slot sits on the DUMMY leaf the packer appends after the
   // last node (value +0.0f), so a step needs no "slot in use" state -- reaching a leaf, real or
   // dummy, adds its value and frees the slot for the next parked walk.
-  const uint32_t sl0 = (uint32_t)(warp * 2) * p.slot_stride + lane * 4u;   // this lane in the warp's buffer 0
+  const uint32_t sl0 = (uint32_t)(unit * 2) * p.slot_stride + lane * 4u;   // this lane in the unit's buffer 0
   uint32_t node[K];            // breadth-first node index, relative to the chunk's first node
   uint32_t fb[K];              // sl0 or sl0 + slot_stride: the tile buffer the walk's row lives in
   uint2 e[K];                  // the node `node[w]`, loaded by the previous step
@@ -128,7 +149,7 @@ k_smem_forest_deep(SmemParams p) {
     if (tile < p.num_tiles) {
       flag_next = __ldg(p.tile_flags + tile);
       const size_t r0 = tile * 32 + lane;
-      if (!first && r0 < p.rows) acc_next = p.preds[r0];
+      if (!first && half == 0 && r0 < p.rows) acc_next = p.preds[r0];
     }
 
     // current / previous tile of this warp
@@ -137,6 +158,17 @@ k_smem_forest_deep(SmemParams p) {
     bool have_prev = false, live_prev = false;
     float acc_prev = 0.0f;       // top part of the previous tile's sum
     float dacc_prev = 0.0f, dacc_cur = 0.0f;   // leaf values the deep walks of each tile have reached
+    // PAIR, warp 0: its part of a retired tile's sum, written once warp 1's part has crossed the barrier
+    float out_sum = 0.0f;
+    size_t out_row = 0;
+    bool out_have = false;
+    auto flush_out = [&]() {
+      if (PAIR && half == 0 && out_have) {
+        const float s = out_sum + *xch;
+        p.preds[out_row] = last ? apply_transform(s, p.tf) : s;
+        out_have = false;
+      }
+    };
 
     // one level of every walk in flight: consume the node loaded by the previous step, start a
     // parked walk in a slot that reached its leaf, issue the next node load
@@ -180,24 +212,29 @@ k_smem_forest_deep(SmemParams p) {
         if (!__any_sync(0xffffffffu, mine)) break;
         deep_step();
       }
-      if (live_prev) {
-        const float s = acc_prev + dacc_prev;
-        p.preds[row_prev] = last ? apply_transform(s, p.tf) : s;
+      const float s = acc_prev + dacc_prev;
+      if (!PAIR) {
+        if (live_prev) p.preds[row_prev] = last ? apply_transform(s, p.tf) : s;
+      } else if (half == 1) {
+        *xch = s;                                // read by warp 0 after the pair's next barrier
+      } else {
+        out_sum = s; out_row = row_prev; out_have = live_prev;
       }
     };
 
     for (; tile < p.num_tiles; tile += warp_stride) {
       const size_t next = tile + warp_stride;
-      __syncwarp();
+      unit_sync();                           // buffer `buf` held tile n-2: all of its walks are retired
+      flush_out();
       float acc = acc_next;
       const bool has_missing = flag_next != 0;
-      commit_tile(buf);                      // buffer `buf` held tile n-2: all of its walks are retired
-      __syncwarp();
+      commit_tile(buf);
+      unit_sync();
       if (next < p.num_tiles) {
         fetch_tile(next);                    // lands while this tile is traversed
         flag_next = __ldg(p.tile_flags + next);
         const size_t rn = next * 32 + lane;
-        acc_next = (!first && rn < p.rows) ? p.preds[rn] : 0.0f;
+        acc_next = (!first && half == 0 && rn < p.rows) ? p.preds[rn] : 0.0f;
       }
       row = tile * 32 + lane;
       const bool live = row < p.rows;
@@ -205,7 +242,7 @@ k_smem_forest_deep(SmemParams p) {
       const uint32_t park_tag = (uint32_t)buf << 31;
       const bool park = live && !p.debug_no_drain;   // (TAHOE_QTOP_NODRAIN: timing experiments, wrong scores)
 
-      for (int t = 0; t < ntrees; t += G) {
+      for (int t = half * G; t < ntrees; t += kSplit * G) {
         // room for G more parked walks in every lane's ring (rarely taken)
         while (__any_sync(0xffffffffu, ((tail - head) & kOffMask) > (uint32_t)(kDeepPend - 1 - G) * 128u)) deep_step();
         deep_step();
@@ -235,7 +272,17 @@ k_smem_forest_deep(SmemParams p) {
       prev_par = (uint32_t)buf;
       buf ^= 1;
     }
-    if (have_prev) retire_prev();            // end of the chunk: nothing stays in flight
+    // end of the chunk: nothing stays in flight
+    if (PAIR) {
+      unit_sync();
+      flush_out();                           // the tile before the last one
+      unit_sync();
+    }
+    if (have_prev) retire_prev();
+    if (PAIR) {
+      unit_sync();
+      flush_out();
+    }
   }
 }
 

@@ -31,12 +31,20 @@ int TAHOE_CAT(launch_smem_depth_, TAHOE_DEPTH)(tahoe_forest* f, const SmemParams
   if (f->sparse) {
     constexpr int K = TAHOE_DEEP_WALKS;
     constexpr int P8 = kStagedMaxCols / 4, P16 = kStagedMaxColsDeep / 4;
-    const bool wide = p.cols > kStagedMaxCols;     // 64-column register staging, <= 8 warps
-    if (wide && f->warps > 8) { set_error("64-column staged tiles need a plan of <= 8 warps"); return TAHOE_ERR_INVALID; }
+    // rows of <= 32 columns: one warp per tile, 8 staging registers; wider rows: 8 warps with 16
+    // staging registers, or 16 warps in pairs that share a tile (8 each)
+    const bool wide = p.cols > kStagedMaxCols;
+    const bool pair = wide && f->warps > 8;
+    const int v = !wide ? 0 : (pair ? 2 : 1);
     if (p.leaf_ids)
-      return wide ? go(k_smem_forest_deep<D, 2, true, P16, K>) : go(k_smem_forest_deep<D, 2, true, P8, K>);
-#define TAHOE_DEEP_CASE(G) \
-  case G: return wide ? go(k_smem_forest_deep<D, G, false, P16, K>) : go(k_smem_forest_deep<D, G, false, P8, K>);
+      return v == 0 ? go(k_smem_forest_deep<D, 2, true, P8, K, false>)
+           : v == 1 ? go(k_smem_forest_deep<D, 2, true, P16, K, false>)
+                    : go(k_smem_forest_deep<D, 2, true, P8, K, true>);
+#define TAHOE_DEEP_CASE(G)                                                   \
+  case G:                                                                    \
+    return v == 0 ? go(k_smem_forest_deep<D, G, false, P8, K, false>)        \
+         : v == 1 ? go(k_smem_forest_deep<D, G, false, P16, K, false>)       \
+                  : go(k_smem_forest_deep<D, G, false, P8, K, true>);
     switch (f->group) {
       TAHOE_DEEP_CASE(2) TAHOE_DEEP_CASE(4) TAHOE_DEEP_CASE(6)
       default: break;

@@ -805,12 +805,15 @@ static double plan_chunks_for(tahoe_forest* f, int depth, bool deep) {
   bool found = false;
   for (int warps = kSmemMaxWarps; warps >= 4; warps >>= 1) {
     if (want_warps && warps != want_warps) continue;
-    const size_t bars = 1024 + (deep ? (size_t)warps * kDeepPend * 128 : 0);   // + lane-private parking lists
+    // deep: + lane-private rings of parked walks + the pairs' exchange floats
+    const size_t bars = 1024 + (deep ? (size_t)warps * kDeepPend * 128 + 512 : 0);
     for (int staged = 0; staged <= 1; ++staged) {
       if (want_staged >= 0 && staged != want_staged) continue;
       if (deep && !staged) continue;                   // k_smem_forest_deep: the next tile always waits in registers
-      if (staged && C > ((deep && warps <= 8) ? kStagedMaxColsDeep : kStagedMaxCols)) continue;
-      const int slots = warps * ((staged && !deep) ? 1 : 2);   // deep: current + previous tile per warp
+      if (staged && C > (deep ? kStagedMaxColsDeep : kStagedMaxCols)) continue;
+      // deep: current + previous tile per warp; rows wider than 32 columns at 16 warps: per PAIR of warps
+      const bool paired = deep && C > kStagedMaxCols && warps > 8;
+      const int slots = deep ? (paired ? warps : warps * 2) : warps * (staged ? 1 : 2);
       // wide column field (column-major tile region) when rank + column bits leave room for it,
       // else the compact field with a slot-major region whose columns are padded to a power of two
       const bool wide = f->rank_bits + f->col_bits + kQuantColShift + ilog2_c(slots) <= 32;

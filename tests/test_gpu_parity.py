@@ -144,14 +144,16 @@ def test_sparse_forest_through_shared_memory(oracle, monkeypatch, cut, tpc, rows
 @pytest.mark.parametrize("depth,tpc,plan,rows,cols", [
     (None, None, None, 3000, 50), (2, 6, "16,1,6", 3000, 18), (5, 12, "8,1,6", 33, 50), (1, 2, "8,1,2", 2368 * 32 + 5, 50),
     (8, 64, "4,1,4", 1, 50), (12, None, "8,1,2", 700, 50), (3, 4, "16,1,4", 40_000, 24), (4, 6, "16,1,6", 5000, 28),
-    (2, 6, "4,1,6", 3000, 64), (6, 12, "8,1,4", 148 * 8 * 32 * 3 + 17, 50)])
+    (2, 6, "4,1,6", 3000, 64), (6, 12, "8,1,4", 148 * 8 * 32 * 3 + 17, 50),
+    # 16 warps on rows wider than 32 columns: pairs of warps share a tile
+    (3, 12, "16,1,6", 148 * 8 * 32 * 2 + 33, 50), (2, 4, "16,1,2", 5000, 64), (5, 24, "16,1,4", 31, 40), (7, None, "16,1,6", 70_000, 50)])
 def test_sparse_forest_quantised_tops(oracle, monkeypatch, depth, tpc, plan, rows, cols):
     """k_smem_forest_deep on the QT layout: dense rank-quantised tops in shared memory, walks still on an
     internal node below them parked in lane-private rings and advanced one level per traversal group in
     L2, across the tile boundary (two tile buffers per warp).  Shallow tops and small chunks force many
     parked walks, full rings, leftovers at tile and chunk ends, several tiles per warp and several
-    chunks; 16 / 8 / 4 warps, 32- and 64-column register staging; leaf ids stay exact, the score is a
-    re-ordered float sum."""
+    chunks; 16 / 8 / 4 warps, 32- and 64-column register staging, pairs of warps sharing a tile; leaf ids
+    stay exact, the score is a re-ordered float sum."""
     if depth is not None:
         monkeypatch.setenv("TAHOE_QTOP_DEPTH", str(depth))
     if tpc is not None:
