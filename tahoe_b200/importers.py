@@ -1,0 +1,175 @@
+"""Importers: trained tree ensembles -> Tahoe compact nodes.
+
+The reference loads forests only from its own text format, written by an external trainer repository
+(README.md:32-33).  These importers go straight from a trained model to the compact (sparse) node
+array `tahoe_forest_create_sparse` takes -- {val, bits, left_idx}, children adjacent
+(Struct.h:50-54, 2244) -- with the reference's exact branch semantics (BaseTahoeTest.h:450-453):
+
+    missing (|v - sentinel| <= 1e-6)  ->  default_left ? left : right
+    otherwise                          ->  v >= val ? right : left           (NaN goes left)
+
+* scikit-learn (`from_sklearn`): its trees test `x <= threshold -> left` on float32 features against
+  a float64 threshold.  For float32 x that is exactly `x < t'` with t' = the smallest float32 above
+  the threshold, so the converted forest selects the same leaves as `model.apply(X)`, row by row.
+* XGBoost JSON (`from_xgboost_json`): `x < split_condition -> left`, missing -> `default_left`, all in
+  float32 -- the reference's rule as it stands.  Leaf values are the `split_conditions` of leaf nodes.
+
+Every importer returns an `Imported` record; `Imported.forest()` packs it through the C ABI.
+"""
+from __future__ import annotations
+
+import json
+import math
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from .synth import SPARSE_NODE
+
+DEF_LEFT = 1 << 30           # Struct.h:58
+IS_LEAF = 1 << 31            # Struct.h:59
+OUT_RAW, OUT_AVG, OUT_SIGMOID, OUT_THRESHOLD = 0x0, 0x1, 0x10, 0x100   # Struct.h:37-42
+
+
+@dataclass
+class Imported:
+    nodes: np.ndarray            # SPARSE_NODE [total]
+    tree_offsets: np.ndarray     # int64 [T+1]
+    weights: np.ndarray          # float32 [total]: training cover of every node (split-probability reorder)
+    num_cols: int
+    output: int = OUT_RAW
+    global_bias: float = 0.0
+    threshold: float = 0.0
+    # per tree: compact index -> the trainer's own node id (compare leaf ids with e.g. model.apply)
+    source_ids: list = field(default_factory=list)
+
+    @property
+    def num_trees(self) -> int:
+        return int(self.tree_offsets.shape[0] - 1)
+
+    def forest(self, missing: float = float("-inf")):
+        """Pack through the C ABI.  `missing` is the sentinel value the data uses for absent features
+        (data-file header line 3 in the reference, BaseTahoeTest.h:370-371)."""
+        from . import api
+        return api.Forest.from_sparse(self.nodes, self.tree_offsets, self.num_cols, weights=self.weights,
+                                      missing=missing, output=self.output, threshold=self.threshold,
+                                      global_bias=self.global_bias)
+
+
+def _f32_strictly_above(thr: np.ndarray) -> np.ndarray:
+    """Smallest float32 t' with (x <= thr) == (x < t') for every float32 x."""
+    thr = np.asarray(thr, dtype=np.float64)
+    t32 = thr.astype(np.float32)
+    over = t32.astype(np.float64) > thr                    # rounded up: step back below the threshold
+    t32 = np.where(over, np.nextafter(t32, np.float32(-np.inf)), t32)
+    return np.nextafter(t32, np.float32(np.inf)).astype(np.float32)
+
+
+def _compact_tree(left, right, feature, split_val, leaf_val, def_left, cover):
+    """One tree given as child-index arrays (-1 = leaf) -> compact nodes in breadth-first order with
+    the two children of a node adjacent.  Returns (nodes, weights, source ids)."""
+    order, left_idx, head = [0], [], 0
+    while head < len(order):
+        k = order[head]
+        if left[k] < 0:
+            left_idx.append(0)
+        else:
+            left_idx.append(len(order))
+            order.append(int(left[k]))
+            order.append(int(right[k]))
+        head += 1
+    order = np.asarray(order, dtype=np.int64)
+    is_leaf = np.asarray(left)[order] < 0
+    sp = np.zeros(len(order), dtype=SPARSE_NODE)
+    sp["val"] = np.where(is_leaf, np.asarray(leaf_val, dtype=np.float32)[order],
+                         np.asarray(split_val, dtype=np.float32)[order])
+    fid = np.where(is_leaf, 0, np.asarray(feature)[order]).astype(np.int64)
+    bits = fid | np.where(np.asarray(def_left, dtype=bool)[order] & ~is_leaf, DEF_LEFT, 0) | np.where(is_leaf, IS_LEAF, 0)
+    sp["bits"] = (bits & 0xFFFFFFFF).astype(np.uint32).view(np.int32)
+    sp["left_idx"] = np.asarray(left_idx, dtype=np.int32)
+    return sp, np.asarray(cover, dtype=np.float32)[order], order.astype(np.int32)
+
+
+def _assemble(trees, num_cols, **kw) -> Imported:
+    nodes = np.concatenate([t[0] for t in trees])
+    weights = np.concatenate([t[1] for t in trees])
+    offs = np.zeros(len(trees) + 1, dtype=np.int64)
+    offs[1:] = np.cumsum([len(t[0]) for t in trees])
+    return Imported(nodes, offs, weights, int(num_cols), source_ids=[t[2] for t in trees], **kw)
+
+
+# ---- scikit-learn ------------------------------------------------------------------------------
+def from_sklearn(model) -> Imported:
+    """RandomForestRegressor / ExtraTreesRegressor (mean of the trees: output AVG), DecisionTreeRegressor,
+    GradientBoostingRegressor (init + learning_rate * sum: RAW + bias), GradientBoostingClassifier with
+    two classes (the same raw score through a sigmoid = predict_proba[:, 1])."""
+    name = type(model).__name__
+    scale, bias, output = 1.0, 0.0, OUT_RAW
+    if name in ("RandomForestRegressor", "ExtraTreesRegressor"):
+        estimators, output = list(model.estimators_), OUT_AVG
+    elif name == "DecisionTreeRegressor":
+        estimators = [model]
+    elif name in ("GradientBoostingRegressor", "GradientBoostingClassifier"):
+        if model.estimators_.shape[1] != 1:
+            raise ValueError("multi-class gradient boosting sums one forest per class; Tahoe's predict has one output")
+        estimators = [e[0] for e in model.estimators_]
+        scale = float(model.learning_rate)
+        init = model.init_
+        if init == "zero":
+            bias = 0.0
+        elif name == "GradientBoostingRegressor":
+            bias = float(np.ravel(init.constant_)[0])
+        else:                                                # log-odds of the class prior
+            p1 = float(init.class_prior_[1])
+            bias = math.log(p1 / (1.0 - p1))
+            output = OUT_SIGMOID
+    else:
+        raise TypeError(f"from_sklearn: unsupported model {name}")
+    trees = []
+    for est in estimators:
+        t = est.tree_
+        if t.value.shape[1] != 1 or t.value.shape[2] != 1:
+            raise ValueError("only single-output regression trees carry one value per leaf")
+        left, right = t.children_left, t.children_right
+        go_left = getattr(t, "missing_go_to_left", None)
+        def_left = np.zeros(t.node_count, dtype=bool) if go_left is None else np.asarray(go_left, dtype=bool)
+        split = _f32_strictly_above(np.where(left < 0, 0.0, t.threshold))
+        trees.append(_compact_tree(left, right, np.maximum(t.feature, 0), split, t.value[:, 0, 0] * scale,
+                                   def_left, t.weighted_n_node_samples))
+    return _assemble(trees, model.n_features_in_, output=output, global_bias=bias)
+
+
+# ---- XGBoost JSON --------------------------------------------------------------------------------
+def from_xgboost_json(model) -> Imported:
+    """`Booster.save_model("m.json")` schema: learner.gradient_booster.model.trees[*] with the arrays
+    left_children / right_children (-1 = leaf), split_indices, split_conditions (threshold, or the leaf
+    value of a leaf), default_left, sum_hessian.  Objectives: reg:* (RAW + base_score) and
+    binary:logistic (sigmoid of the margin; base_score is a probability).  `model`: path or parsed dict."""
+    if not isinstance(model, dict):
+        with open(model) as f:
+            model = json.load(f)
+    learner = model["learner"]
+    gb = learner["gradient_booster"]
+    if gb.get("name", "gbtree") not in ("gbtree", "dart"):
+        raise ValueError(f"unsupported booster {gb.get('name')}")
+    gbm = gb["gbtree"]["model"] if "gbtree" in gb else gb["model"]
+    lmp = learner["learner_model_param"]
+    if int(lmp.get("num_class", "0")) > 1:
+        raise ValueError("multi-class boosters sum one forest per class; Tahoe's predict has one output")
+    objective = learner.get("objective", {}).get("name", "reg:squarederror")
+    base_score = float(lmp.get("base_score", "0.5"))
+    if objective == "binary:logistic":
+        output, bias = OUT_SIGMOID, math.log(base_score / (1.0 - base_score))
+    elif objective.startswith("reg:") and objective not in ("reg:gamma", "reg:tweedie", "reg:logistic"):
+        output, bias = OUT_RAW, base_score
+    else:
+        raise ValueError(f"unsupported objective {objective}")
+    trees = []
+    for t in gbm["trees"]:
+        left = np.asarray(t["left_children"], dtype=np.int64)
+        cond = np.asarray(t["split_conditions"], dtype=np.float32)
+        trees.append(_compact_tree(left, np.asarray(t["right_children"], dtype=np.int64),
+                                   np.asarray(t["split_indices"], dtype=np.int64), cond, cond,
+                                   np.asarray(t["default_left"], dtype=bool),
+                                   np.asarray(t.get("sum_hessian", np.ones(len(left))), dtype=np.float32)))
+    return _assemble(trees, int(lmp["num_feature"]), output=output, global_bias=bias)
