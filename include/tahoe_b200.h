@@ -209,8 +209,11 @@ enum {
   TAHOE_EXPORT_SPARSE_BFS = 15,      /* uint2 [nodes] sparse trees renumbered breadth-first: {val, leaf<<31|def_left<<30|delta<<fid_bits|fid} */
   TAHOE_EXPORT_SPARSE_BFS_ORIG = 16, /* int32 [nodes] breadth-first index -> caller's node index inside its tree */
   TAHOE_EXPORT_SPARSE_TOP = 17,      /* uint2 [chunks * trees_per_chunk][sparse_cut] shared-memory image of the tree tops */
-  TAHOE_EXPORT_SPARSE_DEEPQ = 18     /* uint2 [total] breadth-first sparse nodes in rank form {rank word | leaf value, child delta | leaf<<31};
-                                        the dense tops of the QT layout are exported as QUANT_WORDS / LEAF_ORIGIN */
+  TAHOE_EXPORT_SPARSE_DEEP_BLOCKS = 18,  /* uint32 [blocks + 1][8] QT layout below the dense tops: two-level blocks {root, left, right, -} x
+                                            {rank word | leaf value, leaf<<31 | block delta}; the last block is the dummy leaf (+0.0f);
+                                            the dense tops themselves are exported as QUANT_WORDS / LEAF_ORIGIN */
+  TAHOE_EXPORT_SPARSE_BLOCK_ORIG = 19,   /* int32 [blocks + 1][3] caller's node index (inside its tree) of root / left / right, -1 = none */
+  TAHOE_EXPORT_SPARSE_BLOCK_OFFSETS = 20 /* int64 [T+1] first block of every tree */
 };
 int tahoe_forest_export(const tahoe_forest_t* f, int which, void* buf, size_t* bytes);
 

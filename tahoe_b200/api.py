@@ -27,7 +27,7 @@ ALL_STRATEGIES = list(STRATEGY_NAMES)
  EXPORT_QUANT_TABLE, EXPORT_QUANT_OFFSETS, EXPORT_LEAF_ORIGIN, EXPORT_SIMHASH, EXPORT_QUANT_LUT,
  EXPORT_QUANT_LUT_MIN, EXPORT_QUANT_LUT_SCALE, EXPORT_SD_TOP_NODES, EXPORT_SD_BLOCKS,
  EXPORT_SD_ORIG_BOTTOM, EXPORT_SPARSE_BFS, EXPORT_SPARSE_BFS_ORIG, EXPORT_SPARSE_TOP,
- EXPORT_SPARSE_DEEPQ) = range(19)
+ EXPORT_SPARSE_DEEP_BLOCKS, EXPORT_SPARSE_BLOCK_ORIG, EXPORT_SPARSE_BLOCK_OFFSETS) = range(21)
 
 
 class TahoeError(RuntimeError):

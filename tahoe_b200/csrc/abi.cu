@@ -79,7 +79,7 @@ constexpr double kSparseVisit = 2.3e-12;      // s per node visit, sparse tree t
 constexpr double kSparseChunkRow = 1.0e-10;   // s per row per chunk: tile re-stream + refill latency share
 constexpr double kSparseDeep = 3.1e-11;       // s per walk that leaves the tops and is finished in L2
 constexpr double kSparseStep = 300e-9;        // one step of a lane's two interleaved sequences (latency)
-constexpr double kDeepWalk = 2.0e-11;          // s per parked walk of the QT layout (64 finished together in L2)
+constexpr double kDeepWalk = 1.3e-11;          // s per parked walk of the QT layout (two-level blocks in L2, pipelined behind the traversal)
 constexpr double kSparseTileFixed = 8e-6;     // refill a warp's tile buffer + final drain
 }  // namespace model
 
@@ -233,7 +233,8 @@ void tahoe_forest_destroy(tahoe_forest_t* f) {
   if (!f) return;
   cudaFree(f->d_heap); cudaFree(f->d_sparse); cudaFree(f->d_sparse8); cudaFree(f->d_tree_offsets); cudaFree(f->d_inter);
   cudaFree(f->d_tree_order); cudaFree(f->d_orig_ids);
-  cudaFree(f->d_sp_full); cudaFree(f->d_sp_orig); cudaFree(f->d_sp_top); cudaFree(f->d_sp_deepq);
+  cudaFree(f->d_sp_full); cudaFree(f->d_sp_orig); cudaFree(f->d_sp_top); cudaFree(f->d_sp_qblocks);
+  cudaFree(f->d_sp_qblock_orig); cudaFree(f->d_sp_qblock_offsets);
   cudaFree(f->d_sd_top_nodes); cudaFree(f->d_sd_blocks); cudaFree(f->d_sd_orig_bottom); cudaFree(f->d_qwords); cudaFree(f->d_qtable);
   cudaFree(f->d_qoffsets); cudaFree(f->d_leaf_origin);
   cudaFree(f->d_qlut_min); cudaFree(f->d_qlut_scale); cudaFree(f->d_qlut);
@@ -374,7 +375,9 @@ int tahoe_forest_export(const tahoe_forest_t* f, int which, void* buf, size_t* b
     case TAHOE_EXPORT_SPARSE_BFS: src = h.sp_full.data(); n = h.sp_full.size() * sizeof(uint2); break;
     case TAHOE_EXPORT_SPARSE_BFS_ORIG: src = h.sp_orig.data(); n = h.sp_orig.size() * 4; break;
     case TAHOE_EXPORT_SPARSE_TOP: src = h.sp_top.data(); n = h.sp_top.size() * sizeof(uint2); break;
-    case TAHOE_EXPORT_SPARSE_DEEPQ: src = h.sp_deepq.data(); n = h.sp_deepq.size() * sizeof(uint2); break;
+    case TAHOE_EXPORT_SPARSE_DEEP_BLOCKS: src = h.sp_qblocks.data(); n = h.sp_qblocks.size() * sizeof(uint4); break;
+    case TAHOE_EXPORT_SPARSE_BLOCK_ORIG: src = h.sp_qblock_orig.data(); n = h.sp_qblock_orig.size() * 4; break;
+    case TAHOE_EXPORT_SPARSE_BLOCK_OFFSETS: src = h.sp_qblock_offsets.data(); n = h.sp_qblock_offsets.size() * 8; break;
     default: set_error("unknown export id"); return TAHOE_ERR_INVALID;
   }
   if (buf) {

@@ -59,7 +59,10 @@ struct HostPack {
   std::vector<int32_t> sp_orig;       // [total] breadth-first index -> caller's node index inside the tree
   std::vector<uint2> sp_top;          // [sp_chunks * sp_tpc][sp_cut]; short trees padded with leaf 0.0
   // QT (sparse forests, quantised tops): qwords / leaf_origin hold the dense top of depth qt_depth;
-  std::vector<uint2> sp_deepq;        // [total] breadth-first nodes in rank form {rank word | leaf value, child delta | leaf<<31}
+  // ... below them two-level blocks of 32 bytes {root, left, right, -} x {rank word | leaf value, leaf<<31 | block delta}
+  std::vector<uint4> sp_qblocks;      // [blocks + 1][2]; the last one is the dummy leaf block (+0.0f)
+  std::vector<int32_t> sp_qblock_orig;   // [blocks + 1][3] caller's node index of root / left / right (-1: none)
+  std::vector<int64_t> sp_qblock_offsets;   // [T+1] first block of every tree
   // I8
   int tpad = 0;                       // trees padded to a multiple of 32
   std::vector<uint2> inter;           // [N][tpad]
@@ -154,7 +157,9 @@ struct tahoe_forest {
   uint2* d_sp_full = nullptr;
   int32_t* d_sp_orig = nullptr;
   uint2* d_sp_top = nullptr;
-  uint2* d_sp_deepq = nullptr;
+  uint4* d_sp_qblocks = nullptr;
+  int32_t* d_sp_qblock_orig = nullptr;
+  int64_t* d_sp_qblock_offsets = nullptr;
   int64_t* d_tree_offsets = nullptr;
   uint2* d_inter = nullptr;
   int32_t* d_tree_order = nullptr;

@@ -195,7 +195,7 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.col_stride = f->tile_col_stride; p.slot_stride = f->tile_slot_stride; p.tile_region = f->tile_region;
   p.preds = a.preds; p.leaf_ids = a.leaf_ids;
   p.leaf_origin = f->d_leaf_origin;
-  p.deep = f->d_sp_deepq; p.tree_offsets = f->d_tree_offsets; p.deep_orig = f->d_sp_orig;
+  p.deep_blocks = f->d_sp_qblocks; p.block_offsets = f->d_sp_qblock_offsets; p.block_orig = f->d_sp_qblock_orig;
   if (const char* e = std::getenv("TAHOE_QTOP_NODRAIN")) p.debug_no_drain = std::atoi(e);
   p.tf = Transform{f->params.output, (float)f->params.num_trees, f->params.threshold,
                    f->params.global_bias};

@@ -20,12 +20,12 @@
 
 namespace tahoe {
 
-// 8-byte read-only load; volatile so that it is issued where it is written (before the
-// shared-memory walk that hides its latency), not sunk to its first use
-__device__ __forceinline__ uint2 ldg_nc_u2(uint64_t addr) {
-  uint2 v;
-  asm volatile("ld.global.nc.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(addr));
-  return v;
+// one 32-byte block, read-only (LDG.E.256); volatile so that it is issued where it is written (before
+// the shared-memory walk that hides its latency), not sunk to its first use
+__device__ __forceinline__ void ldg_nc_block(uint64_t addr, uint4& a, uint4& b) {
+  asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+               : "l"(addr));
 }
 
 // PAIR: rows wider than 32 columns need 64 staging registers per lane, which caps a CTA at 8 warps --
@@ -105,11 +105,14 @@ k_smem_forest_deep(SmemParams p) {
   // last node (value +0.0f), so a step needs no "slot in use" state -- reaching a leaf, real or
   // dummy, adds its value and frees the slot for the next parked walk.
   const uint32_t sl0 = (uint32_t)(unit * 2) * p.slot_stride + lane * 4u;   // this lane in the unit's buffer 0
-  uint32_t node[K];            // breadth-first node index, relative to the chunk's first node
+  uint32_t node[K];            // block index, relative to the chunk's first block
   uint32_t fb[K];              // sl0 or sl0 + slot_stride: the tile buffer the walk's row lives in
-  uint2 e[K];                  // the node `node[w]`, loaded by the previous step
+  uint4 ea[K], eb[K];          // block `node[w]`, loaded by the previous step: {root.x, root.y, left.x, left.y}, {right.x, right.y, -, -}
 #pragma unroll
-  for (int w = 0; w < K; ++w) { node[w] = 0; fb[w] = sl0; e[w] = make_uint2(0u, kMetaLeaf); }
+  for (int w = 0; w < K; ++w) {
+    node[w] = 0; fb[w] = sl0;
+    ea[w] = make_uint4(0u, kMetaLeaf, 0u, kMetaLeaf); eb[w] = make_uint4(0u, kMetaLeaf, 0u, 0u);
+  }
   // ring of parked walks {node index | tile parity << 31}: pop at head, push at tail (byte offsets;
   // at most kDeepPend - 1 entries, so head == tail means empty)
   uint32_t head = 0, tail = 0;
@@ -136,9 +139,9 @@ k_smem_forest_deep(SmemParams p) {
     chunk_phase ^= 1;
 
     const bool first = (chunk == 0), last = (chunk == p.num_chunks - 1);
-    const int64_t chunk_first = __ldg(p.tree_offsets + min(tree0, p.num_trees));
-    const uint32_t dummy = (uint32_t)(__ldg(p.tree_offsets + p.num_trees) - chunk_first);
-    uint64_t cdv = (uint64_t)(p.deep + chunk_first);   // kept as one 64-bit register: node address = one IMAD.WIDE
+    const int64_t chunk_first = __ldg(p.block_offsets + min(tree0, p.num_trees));
+    const uint32_t dummy = (uint32_t)(__ldg(p.block_offsets + p.num_trees) - chunk_first);
+    uint64_t cdv = (uint64_t)(p.deep_blocks + 2 * chunk_first);   // kept as one 64-bit register: block address = one IMAD.WIDE
     asm volatile("" : "+l"(cdv));
 #pragma unroll
     for (int w = 0; w < K; ++w) node[w] = dummy;       // nothing is in flight at a chunk boundary
@@ -170,36 +173,42 @@ k_smem_forest_deep(SmemParams p) {
       }
     };
 
-    // one level of every walk in flight: consume the node loaded by the previous step, start a
-    // parked walk in a slot that reached its leaf, issue the next node load
+    // two levels of every walk in flight: consume the block loaded by the previous step (root, then the
+    // child it picks), start a parked walk in a slot that reached its leaf, issue the next block load
     auto deep_step = [&]() {
 #pragma unroll
       for (int w = 0; w < K; ++w) {
-        const uint32_t x = e[w].x, y = e[w].y;
-        const bool leaf = (int32_t)y < 0;
+        const uint4 a = ea[w], b = eb[w];
+        const bool root_leaf = (int32_t)a.y < 0;
         // (a leaf's x is its float value: keep its bits out of the address)
-        const uint32_t F = lds_u32(s_base + (((leaf ? 0u : x) & p.col_mask) | fb[w]));
-        bool c = F > x;
-        if (F == p.miss_code) c = !(x & 1u);                     // sentinel: !def_left (BaseTahoeTest.h:452)
-        const float v = leaf ? __uint_as_float(x) : 0.0f;
+        const uint32_t F0 = lds_u32(s_base + (((root_leaf ? 0u : a.x) & p.col_mask) | fb[w]));
+        bool c0 = F0 > a.x;
+        if (F0 == p.miss_code) c0 = !(a.x & 1u);                 // sentinel: !def_left (BaseTahoeTest.h:452)
+        const uint32_t cx = c0 ? b.x : a.z, cy = c0 ? b.y : a.w; // the child the root picks
+        const bool done = root_leaf || (int32_t)cy < 0;
+        const uint32_t F1 = lds_u32(s_base + (((done ? 0u : cx) & p.col_mask) | fb[w]));
+        bool c1 = F1 > cx;
+        if (F1 == p.miss_code) c1 = !(cx & 1u);
+        const float v = done ? __uint_as_float(root_leaf ? a.x : cx) : 0.0f;
         const bool pv = fb[w] == prev_sl;
         if (pv) dacc_prev += v; else dacc_cur += v;
-        if (LEAF_IDS && leaf && node[w] != dummy) {
-          const int64_t nd = chunk_first + (int64_t)node[w];
-          int lo = tree0, hi = min(tree0 + ntrees, p.num_trees);   // tree_offsets[lo] <= nd < tree_offsets[hi]
+        if (LEAF_IDS && done && node[w] != dummy) {
+          const int64_t blk = chunk_first + (int64_t)node[w];
+          int lo = tree0, hi = min(tree0 + ntrees, p.num_trees);   // block_offsets[lo] <= blk < block_offsets[hi]
           while (hi - lo > 1) {
             const int mid = (lo + hi) >> 1;
-            if (__ldg(p.tree_offsets + mid) <= nd) lo = mid; else hi = mid;
+            if (__ldg(p.block_offsets + mid) <= blk) lo = mid; else hi = mid;
           }
-          p.leaf_ids[(pv ? row_prev : row) * (size_t)p.num_trees + lo] = __ldg(p.deep_orig + nd);
+          p.leaf_ids[(pv ? row_prev : row) * (size_t)p.num_trees + lo] =
+              __ldg(p.block_orig + 3 * blk + (root_leaf ? 0 : (c0 ? 2 : 1)));
         }
-        const bool can = leaf && head != tail;
+        const bool can = done && head != tail;
         const uint32_t ent = *reinterpret_cast<const uint32_t*>(ring + head);   // (stale when !can: unused)
         head = can ? (head + 128u) & kOffMask : head;
-        const uint32_t stepped = node[w] + y + (c ? 1u : 0u);
-        node[w] = can ? (ent & 0x7FFFFFFFu) : (leaf ? dummy : stepped);
+        const uint32_t stepped = node[w] + cy + (c1 ? 1u : 0u);   // (!done: cy is the block delta)
+        node[w] = can ? (ent & 0x7FFFFFFFu) : (done ? dummy : stepped);
         fb[w] = can ? sl0 + (ent >> 31) * p.slot_stride : fb[w];
-        e[w] = ldg_nc_u2(cdv + (uint64_t)node[w] * 8u);
+        ldg_nc_block(cdv + (uint64_t)node[w] * 32u, ea[w], eb[w]);
       }
     };
     // finish what is left of the previous tile's walks (latency exposed), then write its score

@@ -5,8 +5,15 @@
 #include "kernels_smem_traverse.cuh"
 #include "kernels_smem_deep.cuh"
 
+// deep walks in flight per lane (k_smem_forest_deep; each holds a 32-byte block in registers), for the
+// 256-thread and the 512-thread instantiations.  Config 4 on B200, 1M rows, top depth 6 / 7:
+// 16 warps in pairs: 1 -> 9.60 / 9.79 ms, 2 -> 9.00 / 9.38, 3 -> 9.18 / 9.95;
+// 8 warps: 2 -> 11.21 / 10.54, 3 -> 11.12 / 10.87, 4 -> 11.76 / 11.55
 #ifndef TAHOE_DEEP_WALKS
-#define TAHOE_DEEP_WALKS 4   // deep walks in flight per lane (k_smem_forest_deep)
+#define TAHOE_DEEP_WALKS 2
+#endif
+#ifndef TAHOE_DEEP_WALKS_512
+#define TAHOE_DEEP_WALKS_512 2
 #endif
 
 #ifndef TAHOE_DEPTH
@@ -29,7 +36,7 @@ int TAHOE_CAT(launch_smem_depth_, TAHOE_DEPTH)(tahoe_forest* f, const SmemParams
 #if TAHOE_DEPTH <= 12
   // sparse forests (QT layout): dense tops of depth D, deep walks pipelined through L2 (kernels_smem_deep.cuh)
   if (f->sparse) {
-    constexpr int K = TAHOE_DEEP_WALKS;
+    constexpr int K = TAHOE_DEEP_WALKS, K5 = TAHOE_DEEP_WALKS_512;
     constexpr int P8 = kStagedMaxCols / 4, P16 = kStagedMaxColsDeep / 4;
     // rows of <= 32 columns: one warp per tile, 8 staging registers; wider rows: 8 warps with 16
     // staging registers, or 16 warps in pairs that share a tile (8 each)
@@ -37,14 +44,14 @@ int TAHOE_CAT(launch_smem_depth_, TAHOE_DEPTH)(tahoe_forest* f, const SmemParams
     const bool pair = wide && f->warps > 8;
     const int v = !wide ? 0 : (pair ? 2 : 1);
     if (p.leaf_ids)
-      return v == 0 ? go(k_smem_forest_deep<D, 2, true, P8, K, false>)
+      return v == 0 ? go(k_smem_forest_deep<D, 2, true, P8, K5, false>)
            : v == 1 ? go(k_smem_forest_deep<D, 2, true, P16, K, false>)
-                    : go(k_smem_forest_deep<D, 2, true, P8, K, true>);
+                    : go(k_smem_forest_deep<D, 2, true, P8, K5, true>);
 #define TAHOE_DEEP_CASE(G)                                                   \
   case G:                                                                    \
-    return v == 0 ? go(k_smem_forest_deep<D, G, false, P8, K, false>)        \
+    return v == 0 ? go(k_smem_forest_deep<D, G, false, P8, K5, false>)       \
          : v == 1 ? go(k_smem_forest_deep<D, G, false, P16, K, false>)       \
-                  : go(k_smem_forest_deep<D, G, false, P8, K, true>);
+                  : go(k_smem_forest_deep<D, G, false, P8, K5, true>);
     switch (f->group) {
       TAHOE_DEEP_CASE(2) TAHOE_DEEP_CASE(4) TAHOE_DEEP_CASE(6)
       default: break;

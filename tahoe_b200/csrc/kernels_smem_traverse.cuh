@@ -32,9 +32,9 @@ struct SmemParams {
   Transform tf;
   // k_smem_forest_deep (sparse forests, QT layout): the trees in qwords are the dense tops; a bottom slot that
   // is a continuation marker parks the walk, which is finished in L2 on the rank-form breadth-first nodes
-  const uint2* deep;           // [total] {rank word | leaf value, child delta | leaf<<31}
-  const int64_t* tree_offsets; // [T+1]
-  const int32_t* deep_orig;    // breadth-first index -> caller's node index
+  const uint4* deep_blocks;      // [blocks + 1][2] two-level blocks {root, left, right, -} x {rank word | leaf value, leaf<<31 | block delta}
+  const int64_t* block_offsets;  // [T+1] first block of every tree
+  const int32_t* block_orig;     // [blocks + 1][3] caller's node index of root / left / right
   int debug_no_drain;          // TAHOE_QTOP_NODRAIN=1: skip the deep walks (timing experiments; scores are wrong)
 };
 

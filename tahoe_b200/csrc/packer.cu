@@ -606,15 +606,19 @@ static void plan_sparse_smem(tahoe_forest* f, const tahoe_sparse_node_t* nodes) 
 // holds either the float bits of the leaf the walk has reached or, when the walk is still on an
 // internal node at level D, a continuation marker: a negative quiet NaN whose low 22 bits are the
 // node's breadth-first index relative to the first node of its chunk's first tree.  The kernel parks
-// such walks (lane-private rings) and every lane advances its own, one level per traversal group, in L2 on `sp_deepq`
-// -- the breadth-first nodes in rank form {rank word, child delta | leaf}, compared against the same
-// rank tile in shared memory.  Thresholds of ALL internal nodes go into the
+// such walks (lane-private rings) and every lane advances its own, one 32-byte two-level block per traversal
+// group, in L2 on `sp_qblocks` -- nodes in rank form {rank word, block delta | leaf}, compared against the
+// same rank tile in shared memory.  Thresholds of ALL internal nodes go into the
 // rank tables, so one quantise pass serves both parts.
 constexpr uint32_t kContMask = 0xFFC00000u;
 // one parked deep walk, in shared-memory node-visit units: its L2 round trips hide behind the traversal
-// groups (k_smem_forest_deep), what is left is ~35 instructions per level of the walk.  Config 4 on B200,
-// 1M rows: top depth 6 / 7 / 8 -> 10.9 / 10.5 / 12.4 ms with 385 / 273 / 194 deep walks per row
-constexpr double kDeepWalkVisits = 20.0;
+// groups (k_smem_forest_deep), what is left is the instructions and the 32-byte gathers of ~2.3 two-level
+// blocks.  Config 4 on B200, 1M rows, 16 warps in pairs: top depth 5 / 6 / 7 -> 10.0 / 9.2 / 9.95 ms with
+// 540 / 385 / 273 deep walks per row
+constexpr double kDeepWalkVisits = 15.0;
+// one traversal group of the deep kernel beyond its visits (deep step, parking), in node-visit units:
+// 6 trees per group 9.2 ms, 4 per group 10.7 ms on the same forest
+constexpr double kDeepGroupVisits = 18.0;
 
 static void plan_sparse_qtop(tahoe_forest* f) {
   HostPack& h = f->host;
@@ -644,7 +648,7 @@ static void plan_sparse_qtop(tahoe_forest* f) {
   }
   auto give_up = [&]() {
     h.qtable.clear(); h.qoffsets.clear(); h.qlut.clear(); h.qlut_min.clear(); h.qlut_scale.clear();
-    h.qwords.clear(); h.leaf_origin.clear(); h.sp_deepq.clear();
+    h.qwords.clear(); h.leaf_origin.clear(); h.sp_qblocks.clear(); h.sp_qblock_orig.clear(); h.sp_qblock_offsets.clear();
     f->qt = false; f->sp_use_qt = false; f->qt_depth = 0; f->trees_per_chunk = 0; f->num_chunks = 0;
   };
   if (!build_rank_tables(f, thr)) { give_up(); return; }
@@ -713,12 +717,29 @@ static void plan_sparse_qtop(tahoe_forest* f) {
   const int64_t W = (int64_t)1 << (D + 1), L = (int64_t)1 << D;
   h.qwords.assign((size_t)T * W, 0u);
   h.leaf_origin.assign((size_t)T * L, -1);
-  h.sp_deepq.assign((size_t)total + 1, make_uint2(0u, kMetaLeaf));   // + the dummy leaf (+0.0f) idle walk slots sit on
-  std::vector<int32_t> at((size_t)W);
+  // Below the top: TWO-LEVEL BLOCKS of 32 bytes {root, left child, right child, -}, each node
+  // {rank word | leaf value, leaf << 31 | block delta}: one L2 sector decides two levels of a deep
+  // walk.  Block roots are the nodes at levels D, D+2, ...; a child's delta is the distance from its
+  // block to the block of ITS left child (the right child's block follows it).  Blocks of one tree are
+  // numbered breadth-first from the internal nodes at level D, in bottom-slot order.
+  h.sp_qblocks.clear();
+  h.sp_qblock_orig.clear();
+  h.sp_qblock_offsets.assign((size_t)T + 1, 0);
+  auto deep_node = [&](int64_t base, int32_t q, uint32_t delta) -> uint2 {
+    const uint2 e = h.sp_full[base + q];
+    return (e.y & kMetaLeaf) ? make_uint2(e.x, kMetaLeaf) : make_uint2(rank_word(e), delta);
+  };
+  auto left_child = [&](int64_t base, int32_t q) -> int32_t {
+    return q + (int32_t)((h.sp_full[base + q].y & 0x3FFFFFFFu) >> fb);
+  };
+  std::vector<int32_t> at((size_t)W), roots;
+  int64_t chunk_first_block = 0;
   for (int t = 0; t < T; ++t) {
-    const int64_t base = h.tree_offsets[t], n = h.tree_offsets[t + 1] - base;
-    const int64_t chunk_base = h.tree_offsets[t / f->trees_per_chunk * f->trees_per_chunk];
-    if (base + n - chunk_base > (int64_t)1 << 22) { give_up(); return; }   // the marker keeps 22 bits of node index
+    const int64_t base = h.tree_offsets[t];
+    const int64_t block0 = (int64_t)h.sp_qblocks.size() / 2;       // first block of this tree
+    h.sp_qblock_offsets[t] = block0;
+    if (t % f->trees_per_chunk == 0) chunk_first_block = block0;
+    roots.clear();
     uint32_t* out = h.qwords.data() + (int64_t)t * W;
     int32_t* lo = h.leaf_origin.data() + (int64_t)t * L;
     at[1] = 0;
@@ -740,15 +761,51 @@ static void plan_sparse_qtop(tahoe_forest* f) {
         out[i] = e.x;
         lo[i - L] = h.sp_orig[base + q];
       } else {
-        out[i] = kContMask | (uint32_t)(base - chunk_base + q);   // the walk goes on below the top
+        // the walk goes on below the top, in the block rooted here (index relative to the chunk's first block)
+        const int64_t rel = block0 - chunk_first_block + (int64_t)roots.size();
+        if (rel >= (int64_t)1 << 22) { give_up(); return; }    // the marker keeps 22 bits
+        out[i] = kContMask | (uint32_t)rel;
+        roots.push_back(q);
       }
     }
-    for (int64_t q = 0; q < n; ++q) {
-      const uint2 e = h.sp_full[base + q];
-      h.sp_deepq[base + q] = (e.y & kMetaLeaf) ? make_uint2(e.x, kMetaLeaf)
-                                               : make_uint2(rank_word(e), (e.y & 0x3FFFFFFFu) >> fb);
+    // breadth-first over block roots: roots[b] is the root of block block0 + b
+    for (size_t b = 0; b < roots.size(); ++b) {
+      const int32_t q = roots[b];
+      const bool leaf = (h.sp_full[base + q].y & kMetaLeaf) != 0;
+      uint4 w0 = make_uint4(0u, kMetaLeaf, 0u, kMetaLeaf), w1 = make_uint4(0u, kMetaLeaf, 0u, 0u);
+      int32_t orig[3] = {h.sp_orig[base + q], -1, -1};
+      if (leaf) {
+        w0.x = h.sp_full[base + q].x;
+      } else {
+        const uint2 r = deep_node(base, q, 0u);
+        w0.x = r.x; w0.y = 0u;
+        const int32_t kid = left_child(base, q);
+        uint2 k[2];
+        for (int c = 0; c < 2; ++c) {
+          const int32_t qc = kid + c;
+          orig[1 + c] = h.sp_orig[base + qc];
+          uint32_t delta = 0;
+          if (!(h.sp_full[base + qc].y & kMetaLeaf)) {         // its two children root the next blocks
+            delta = (uint32_t)(roots.size() - b);
+            const int32_t g = left_child(base, qc);
+            roots.push_back(g);
+            roots.push_back(g + 1);
+          }
+          k[c] = deep_node(base, qc, delta);
+        }
+        w0.z = k[0].x; w0.w = k[0].y; w1.x = k[1].x; w1.y = k[1].y;
+      }
+      h.sp_qblocks.push_back(w0);
+      h.sp_qblocks.push_back(w1);
+      h.sp_qblock_orig.insert(h.sp_qblock_orig.end(), orig, orig + 3);
     }
+    if ((int64_t)h.sp_qblocks.size() / 2 - chunk_first_block >= (int64_t)1 << 30) { give_up(); return; }
   }
+  h.sp_qblock_offsets[T] = (int64_t)h.sp_qblocks.size() / 2;
+  // the dummy block idle walk slots sit on: a leaf root worth +0.0f
+  h.sp_qblocks.push_back(make_uint4(0u, kMetaLeaf, 0u, kMetaLeaf));
+  h.sp_qblocks.push_back(make_uint4(0u, kMetaLeaf, 0u, 0u));
+  h.sp_qblock_orig.insert(h.sp_qblock_orig.end(), {-1, -1, -1});
 }
 
 // ---- shared-memory chunk plan ------------------------------------------------------------
@@ -829,7 +886,9 @@ static double plan_chunks_for(tahoe_forest* f, int depth, bool deep) {
         int tpc = std::min(max_tpc / G * G, tpad);
         const int chunks = (tpad + tpc - 1) / tpc;     // balance: same chunk count, even whole groups
         tpc = ((tpad + chunks - 1) / chunks + G - 1) / G * G;
-        const double visits = (double)tpad * std::max(depth, 1) * smem_visit_cost(warps, G, staged != 0);
+        double visits = (double)tpad * std::max(depth, 1) * smem_visit_cost(warps, G, staged != 0);
+        // deep: the per-group work, and 8 warps (64 staging registers) cover less of it than 16 (measured 1.17x)
+        if (deep) visits = visits * (warps <= 8 ? 1.12 : 1.0) + (double)tpad / G * kDeepGroupVisits;
         // (deep: the tile of a pass is committed from registers under the deep walks of the tile before)
         const double cost = visits + (double)chunks * (deep ? 10.0 : smem_tile_cost(C, staged != 0, tpc, std::max(depth, 1)));
         if (!found || cost < best) {
@@ -902,7 +961,9 @@ int upload(tahoe_forest* f) {
   if ((rc = to_device(&f->d_sp_full, h.sp_full))) return rc;
   if ((rc = to_device(&f->d_sp_orig, h.sp_orig))) return rc;
   if ((rc = to_device(&f->d_sp_top, h.sp_top))) return rc;
-  if ((rc = to_device(&f->d_sp_deepq, h.sp_deepq))) return rc;
+  if ((rc = to_device(&f->d_sp_qblocks, h.sp_qblocks))) return rc;
+  if ((rc = to_device(&f->d_sp_qblock_orig, h.sp_qblock_orig))) return rc;
+  if ((rc = to_device(&f->d_sp_qblock_offsets, h.sp_qblock_offsets))) return rc;
   if ((rc = to_device(&f->d_tree_offsets, h.tree_offsets))) return rc;
   if ((rc = to_device(&f->d_inter, h.inter))) return rc;
   if ((rc = to_device(&f->d_tree_order, h.tree_order))) return rc;

@@ -207,48 +207,68 @@ def sparse_bfs_traverse(nodes8, orig, offsets, fid_bits, cut, data, missing):
 CONT = 0xFFC00000
 
 
-def qtop_traverse(qwords, leaf_origin, deepq, deep_orig, offsets, T, depth, F, col_mask, miss_code, col_shift, tpc):
-    """QT (k_smem_forest<DEEP>): dense rank-quantised tops [T'][2^(depth+1)] + breadth-first rank-form
-    nodes for the walks that leave them.  F = rank words [R,C].
-    -> (values [R,T], caller's leaf node index [R,T], walks parked [R,T] bool)"""
+def qtop_traverse(qwords, leaf_origin, blocks, block_orig, block_offsets, T, depth, F, col_mask, miss_code, col_shift, tpc):
+    """QT (k_smem_forest_deep): dense rank-quantised tops [T'][2^(depth+1)] + two-level blocks
+    {root, left, right, -} x {rank word | leaf value, leaf<<31 | block delta} for the walks that leave
+    them.  F = rank words [R,C].
+    -> (values [R,T], caller's leaf node index [R,T], walks parked [R,T] bool, block loads [R,T])"""
     W, L = 1 << (depth + 1), 1 << depth
     q = qwords.reshape(-1, W)
     lo = leaf_origin.reshape(T, L)
-    dq = deepq.reshape(-1, 2)
+    bl = blocks.reshape(-1, 8)
+    bo = block_orig.reshape(-1, 3)
     R = F.shape[0]
     rows = np.arange(R)
     vals = np.zeros((R, T), np.float32)
     ids = np.zeros((R, T), np.int32)
     parked = np.zeros((R, T), bool)
+    loads = np.zeros((R, T), np.int32)
+    # the dummy block idle slots sit on: a leaf root worth +0.0f
+    assert bl.shape[0] == block_offsets[T] + 1 and bl[-1, 0] == 0 and (bl[-1, 1] >> 31) == 1
 
     def right(Fv, N):
         c = Fv > N
         return np.where(Fv == np.uint32(miss_code), (N & np.uint32(1)) == 0, c)
 
+    def feat(r, N):
+        return F[r, ((N & np.uint32(col_mask)) >> np.uint32(col_shift)).astype(np.int64)]
+
     for t in range(T):
         n = np.ones(R, np.int64)
         for _ in range(depth):
             N = q[t, n]
-            col = ((N & np.uint32(col_mask)) >> np.uint32(col_shift)).astype(np.int64)
-            n = 2 * n + right(F[rows, col], N)
+            n = 2 * n + right(feat(rows, N), N)
         v = q[t, n]
         cont = (v & np.uint32(CONT)) == np.uint32(CONT)
         parked[:, t] = cont
         vals[~cont, t] = v[~cont].view(np.float32)
         ids[~cont, t] = lo[t, n[~cont] - L]
         assert np.all(lo[t, n[~cont] - L] >= 0)
-        # the parked walks go on in the rank-form breadth-first nodes
+        # the parked walks go on in the blocks; the marker's index is relative to the first block of
+        # the chunk's first tree
         r = np.nonzero(cont)[0]
-        # the marker's index is relative to the first node of the chunk's first tree
-        base = int(offsets[t // tpc * tpc])
-        node = (v[r] & np.uint32(~CONT & 0xFFFFFFFF)).astype(np.int64)
-        assert np.all(base + node >= offsets[t]) and np.all(base + node < offsets[t + 1])
+        base = int(block_offsets[t // tpc * tpc])
+        b = base + (v[r] & np.uint32(~CONT & 0xFFFFFFFF)).astype(np.int64)
+        first = True
         while r.size:
-            e = dq[base + node]
-            leaf = (e[:, 1] >> 31) != 0
-            vals[r[leaf], t] = e[leaf, 0].view(np.float32)
-            ids[r[leaf], t] = deep_orig[base + node[leaf]]
-            r, node, e = r[~leaf], node[~leaf], e[~leaf]
-            col = ((e[:, 0] & np.uint32(col_mask)) >> np.uint32(col_shift)).astype(np.int64)
-            node = node + e[:, 1].astype(np.int64) + right(F[r, col], e[:, 0])
-    return vals, ids, parked
+            assert np.all(b >= block_offsets[t]) and np.all(b < block_offsets[t + 1])
+            loads[r, t] += 1
+            e = bl[b]
+            root_leaf = (e[:, 1] >> 31) != 0
+            assert not (first and root_leaf.any())        # a marker only stands for an internal node
+            first = False
+            rx = np.where(root_leaf, np.uint32(0), e[:, 0])   # (a leaf's word is its float value, not a node)
+            c0 = right(feat(r, rx), rx)
+            cx = np.where(c0, e[:, 4], e[:, 2])
+            cy = np.where(c0, e[:, 5], e[:, 3])
+            child_leaf = (cy >> 31) != 0
+            done = root_leaf | child_leaf
+            vals[r[done], t] = np.where(root_leaf, e[:, 0], cx)[done].view(np.float32)
+            pos = np.where(root_leaf, 0, np.where(c0, 2, 1))
+            ids[r[done], t] = bo[b[done], pos[done]]
+            assert np.all(bo[b[done], pos[done]] >= 0)
+            cxm = np.where(done, np.uint32(0), cx)
+            c1 = right(feat(r, cxm), cxm)
+            b = b + cy.astype(np.int64) + c1
+            r, b = r[~done], b[~done]
+    return vals, ids, parked, loads

@@ -245,8 +245,8 @@ def test_sparse_breadth_first_layout(oracle, cut, monkeypatch):
 
 @pytest.mark.parametrize("depth,tpc", [(None, None), (1, None), (3, 6), (6, 12), (12, None)])
 def test_sparse_quantised_tops_layout(oracle, depth, tpc, monkeypatch):
-    """QT (sparse forests through k_smem_forest<DEEP>): the dense rank-quantised tops plus the rank-form
-    breadth-first nodes walk to the oracle's leaves; continuation markers sit exactly where a walk is
+    """QT (sparse forests through k_smem_forest_deep): the dense rank-quantised tops plus the two-level
+    rank-form blocks below them walk to the oracle's leaves; continuation markers sit exactly where a walk is
     still on an internal node at the top's bottom level; the planner's parked-walk estimate is sane."""
     if depth is not None:
         monkeypatch.setenv("TAHOE_QTOP_DEPTH", str(depth))
@@ -271,15 +271,17 @@ def test_sparse_quantised_tops_layout(oracle, depth, tpc, monkeypatch):
     F = emulate.quantize_rows(data, table, qoffs, shift, miss_code, -999.0)
     qwords = f.export(api.EXPORT_QUANT_WORDS, np.uint32)
     assert qwords.size == 24 * (1 << (D + 1))     # (the padding trees of the last group exist on the device only)
-    vals, ids, parked = emulate.qtop_traverse(qwords, f.export(api.EXPORT_LEAF_ORIGIN, np.int32),
-                                              f.export(api.EXPORT_SPARSE_DEEPQ, np.uint32),
-                                              f.export(api.EXPORT_SPARSE_BFS_ORIG, np.int32), offs, 24, D, F,
-                                              col_mask, miss_code, info.col_shift, info.sparse_top_trees_per_chunk)
+    vals, ids, parked, loads = emulate.qtop_traverse(
+        qwords, f.export(api.EXPORT_LEAF_ORIGIN, np.int32), f.export(api.EXPORT_SPARSE_DEEP_BLOCKS, np.uint32),
+        f.export(api.EXPORT_SPARSE_BLOCK_ORIG, np.int32), f.export(api.EXPORT_SPARSE_BLOCK_OFFSETS, np.int64),
+        24, D, F, col_mask, miss_code, info.col_shift, info.sparse_top_trees_per_chunk)
     assert np.array_equal(ids, wids)
     np.testing.assert_allclose(vals.sum(1, dtype=np.float64), want.astype(np.float64), rtol=1e-5, atol=1e-5)
     # a walk is parked exactly when its leaf lies deeper than the top
     leaf_level = lv[offs[:-1][None, :] + wids]
     assert np.array_equal(parked, leaf_level > D)
+    # one 32-byte block decides two levels: a walk whose leaf is k >= 1 levels below the top's bottom loads k // 2 + 1 blocks
+    assert np.array_equal(loads, np.where(parked, (leaf_level - D) // 2 + 1, 0))
     assert abs(parked.mean() - info.sparse_top_deep_walks) < 0.05
     if D == 12:
         assert info.sparse_top_deep_walks == 0.0 and not parked.any()
