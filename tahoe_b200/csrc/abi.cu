@@ -281,8 +281,19 @@ int tahoe_predict_host(tahoe_forest_t* f, int strategy, const float* h_data, siz
   if (num_rows == 0) return TAHOE_OK;
   const int C = f->params.num_cols;
   if (strategy == TAHOE_STRATEGY_AUTO) strategy = select_strategy(f, num_rows, nullptr);
+  // Slabs: copy of slab i+1 under the kernel of slab i, three slabs in flight.  The shared-memory
+  // strategies deal 32-row tiles to sm_count x warps persistent warps, so their slabs are whole WAVES
+  // of tiles (no ragged last round per chunk pass), growing 2 -> 4 -> 8 waves: the first copy, which
+  // nothing can hide, is short, and the later kernels are long enough to amortise their chunk passes.
   size_t slab = ((num_rows + 7) / 8 + 31) / 32 * 32;
   slab = std::min<size_t>(std::max<size_t>(slab, 65536), 1u << 20);
+  size_t wave = 0;
+  if ((strategy == TAHOE_STRATEGY_SHARED_FOREST || strategy == TAHOE_STRATEGY_SPLIT_SHARED_FOREST) &&
+      (f->quant || (f->qt && f->sp_use_qt)) && f->trees_per_chunk > 0) {
+    const bool paired = f->sparse && C > kStagedMaxCols && f->warps > 8;
+    wave = (size_t)f->sm_count * (size_t)(paired ? f->warps / 2 : f->warps) * 32;
+    slab = std::max<size_t>(wave, std::min<size_t>(8 * wave, (size_t)1 << 20) / wave * wave);
+  }
   int total_launches = 0;
   size_t done = 0;
   for (int i = 0; done < num_rows; ++i) {
@@ -296,7 +307,9 @@ int tahoe_predict_host(tahoe_forest_t* f, int strategy, const float* h_data, siz
       TAHOE_CUDA(cudaMalloc((void**)&w.slab_preds, slab * sizeof(float)));
       w.cap_slab_rows = slab;
     }
-    const size_t n = std::min(slab, num_rows - done);
+    size_t this_slab = slab;
+    if (wave && i < 2) this_slab = std::min(slab, (size_t)(2 << i) * wave);
+    const size_t n = std::min(this_slab, num_rows - done);
     TAHOE_CUDA(cudaMemcpyAsync(w.slab_data, h_data + done * (size_t)C, n * (size_t)C * sizeof(float),
                                cudaMemcpyHostToDevice, w.stream));
     PredictArgs a{w.slab_data, n, w.slab_preds, nullptr, w.stream, &w};
