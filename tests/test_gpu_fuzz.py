@@ -1,0 +1,67 @@
+"""GPU: seeded random shapes through every applicable strategy against the oracle -- forests and
+batches nobody hand-picked (odd column counts, one tree, one row, shallow and deep, mostly-missing
+rows, every transform).  Leaf ids bit-exact; scores within 1e-5 of the L1 mass of the summands."""
+import numpy as np
+import pytest
+
+from tahoe_b200 import api, synth
+from tests.helpers import score_close
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(f, data, s, ids=True):
+    import torch
+    d = torch.from_numpy(np.ascontiguousarray(data)).cuda()
+    out = torch.full((d.shape[0], f.num_trees), -7, dtype=torch.int32, device="cuda") if ids else None
+    p = f.predict(d, strategy=s, leaf_ids=out)
+    torch.cuda.synchronize()
+    return p.cpu().numpy(), (out.cpu().numpy() if ids else None)
+
+
+def _check_all(f, data, want, wids, mass, tag):
+    ran = 0
+    for s in api.ALL_STRATEGIES:
+        if not f.applicable(s, data.shape[0]):
+            continue
+        got, ids = _run(f, data, s)
+        assert np.array_equal(ids, wids), (tag, api.STRATEGY_NAMES[s])
+        assert score_close(got, want, mass), (tag, api.STRATEGY_NAMES[s])
+        got2, _ = _run(f, data, s, ids=False)
+        assert score_close(got2, want, mass), (tag, api.STRATEGY_NAMES[s])
+        ran += 1
+    assert ran >= 1, tag
+
+
+@pytest.mark.parametrize("seed", range(20))
+def test_random_sparse_forests(oracle, seed):
+    rng = np.random.default_rng(1000 + seed)
+    T = int(rng.choice([1, 2, 5, 6, 7, 31, 64, 130]))
+    depth = int(rng.integers(1, 17))
+    cols = int(rng.choice([1, 2, 17, 32, 33, 50, 64]))
+    rows = int(rng.choice([1, 31, 33, 1000, 4097, 148 * 16 * 32 + 1]))
+    leaf_prob = float(rng.choice([0.1, 0.3, 0.6]))
+    miss = float(rng.choice([0.0, 0.02, 0.5]))
+    sp, offs, w, lv = synth.gen_sparse_forest(500 + seed, T, depth, cols, leaf_prob=leaf_prob, spine=bool(seed % 2))
+    data = synth.gen_data(600 + seed, rows, cols, miss_frac=miss, nan_frac=0.01)
+    output = int(rng.choice([0, 0x1, 0x10, 0x11]))
+    want, wids = oracle.predict_sparse(sp, offs, data, -999.0, output=output, global_bias=0.25, want_leaf_ids=True)
+    f = api.Forest.from_sparse(sp, offs, cols, weights=w, missing=-999.0, output=output, global_bias=0.25)
+    mass = np.abs(sp["val"][offs[:-1][None, :] + wids]).sum(1) + 0.25
+    _check_all(f, data, want, wids, mass, (seed, T, depth, cols, rows, leaf_prob, miss, output))
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_random_dense_forests(oracle, seed):
+    rng = np.random.default_rng(2000 + seed)
+    T = int(rng.choice([1, 3, 32, 33, 100, 257]))
+    depth = int(rng.integers(1, 12))
+    cols = int(rng.choice([1, 3, 18, 28, 64, 65, 200]))
+    rows = int(rng.choice([1, 32, 77, 5000, 148 * 16 * 32 + 31]))
+    nodes = synth.gen_dense_forest(700 + seed, T, depth, cols, leaf_prob=float(rng.choice([0.0, 0.05, 0.3])))
+    data = synth.gen_data(800 + seed, rows, cols, miss_frac=float(rng.choice([0.0, 0.05])), nan_frac=0.01)
+    want, wids = oracle.predict_dense(nodes, T, depth, data, -999.0, want_leaf_ids=True)
+    f = api.Forest.from_dense(nodes, T, depth, cols, missing=-999.0)
+    npt = (1 << (depth + 1)) - 1
+    mass = np.abs(nodes["val"].reshape(T, npt)[np.arange(T)[None, :], wids]).sum(1)
+    _check_all(f, data, want, wids, mass, (seed, T, depth, cols, rows))
