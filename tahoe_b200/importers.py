@@ -173,3 +173,108 @@ def from_xgboost_json(model) -> Imported:
                                    np.asarray(t["default_left"], dtype=bool),
                                    np.asarray(t.get("sum_hessian", np.ones(len(left))), dtype=np.float32)))
     return _assemble(trees, int(lmp["num_feature"]), output=output, global_bias=bias)
+
+
+# ---- per-class outputs ---------------------------------------------
+# The reference's predict has ONE output: it sums every tree into one scalar, also for multi-class
+# models (BaseTahoeTest.h:462-466).  A K-class ensemble is K forests over the same rows -- one per
+# class -- so it is composed above the C ABI: K handles, K predicts into the rows of a [K, R] buffer.
+@dataclass
+class ImportedClasses:
+    per_class: list              # K Imported records, class k's trees in training order
+    link: str = "raw"            # "raw": the K scores as they are; "softmax": over the K margins
+
+    @property
+    def num_classes(self) -> int:
+        return len(self.per_class)
+
+    def forests(self, missing: float = float("-inf")):
+        return ClassForests([imp.forest(missing) for imp in self.per_class], self.link)
+
+
+class ClassForests:
+    """K packed forests predicted into one [R, K] tensor (device rows in, device scores out)."""
+
+    def __init__(self, forests, link="raw"):
+        self.forests, self.link = forests, link
+
+    def predict(self, data, *, strategy=None):
+        import torch
+        from . import api
+        rows = data.shape[0]
+        out = torch.empty((len(self.forests), rows), dtype=torch.float32, device=data.device)
+        for k, f in enumerate(self.forests):
+            f.predict(data, out[k], strategy=api.AUTO if strategy is None else strategy)
+        out = out.t()
+        return torch.softmax(out, dim=1) if self.link == "softmax" else out
+
+
+def from_sklearn_classes(model) -> ImportedClasses:
+    """RandomForestClassifier / ExtraTreesClassifier (class k's score = mean over trees of the leaf's
+    class-k fraction = predict_proba[:, k]) and multi-class GradientBoostingClassifier (one regression
+    tree per class and stage; softmax over init + learning_rate * sums = predict_proba)."""
+    name = type(model).__name__
+    K = int(model.n_classes_)
+    per_class = []
+    if name in ("RandomForestClassifier", "ExtraTreesClassifier"):
+        for k in range(K):
+            trees = []
+            for est in model.estimators_:
+                t = est.tree_
+                left = t.children_left
+                go_left = getattr(t, "missing_go_to_left", None)
+                def_left = np.zeros(t.node_count, dtype=bool) if go_left is None else np.asarray(go_left, dtype=bool)
+                val = t.value[:, 0, :]
+                frac = val[:, k] / np.maximum(val.sum(axis=1), 1e-300)      # counts or fractions: normalise
+                split = _f32_strictly_above(np.where(left < 0, 0.0, t.threshold))
+                trees.append(_compact_tree(left, t.children_right, np.maximum(t.feature, 0), split, frac,
+                                           def_left, t.weighted_n_node_samples))
+            per_class.append(_assemble(trees, model.n_features_in_, output=OUT_AVG))
+        return ImportedClasses(per_class, "raw")
+    if name == "GradientBoostingClassifier" and model.estimators_.shape[1] == K and K > 2:
+        prior = np.log(np.asarray(model.init_.class_prior_, dtype=np.float64)) if model.init_ != "zero" else np.zeros(K)
+        for k in range(K):
+            trees = []
+            for est in model.estimators_[:, k]:
+                t = est.tree_
+                left = t.children_left
+                go_left = getattr(t, "missing_go_to_left", None)
+                def_left = np.zeros(t.node_count, dtype=bool) if go_left is None else np.asarray(go_left, dtype=bool)
+                split = _f32_strictly_above(np.where(left < 0, 0.0, t.threshold))
+                trees.append(_compact_tree(left, t.children_right, np.maximum(t.feature, 0), split,
+                                           t.value[:, 0, 0] * float(model.learning_rate), def_left,
+                                           t.weighted_n_node_samples))
+            per_class.append(_assemble(trees, model.n_features_in_, output=OUT_RAW, global_bias=float(prior[k])))
+        return ImportedClasses(per_class, "softmax")
+    raise TypeError(f"from_sklearn_classes: unsupported model {name}")
+
+
+def from_xgboost_json_classes(model) -> ImportedClasses:
+    """multi:softprob / multi:softmax boosters: tree i belongs to class `tree_info[i]`; the K margins
+    (base_score + sums) go through a softmax."""
+    if not isinstance(model, dict):
+        with open(model) as f:
+            model = json.load(f)
+    learner = model["learner"]
+    gb = learner["gradient_booster"]
+    gbm = gb["gbtree"]["model"] if "gbtree" in gb else gb["model"]
+    lmp = learner["learner_model_param"]
+    K = int(lmp.get("num_class", "0"))
+    if K < 2:
+        raise ValueError("not a multi-class booster: use from_xgboost_json")
+    base_score = float(lmp.get("base_score", "0.5"))
+    info = gbm.get("tree_info") or [i % K for i in range(len(gbm["trees"]))]
+    per_class = []
+    for k in range(K):
+        trees = []
+        for t, cls in zip(gbm["trees"], info):
+            if int(cls) != k:
+                continue
+            left = np.asarray(t["left_children"], dtype=np.int64)
+            cond = np.asarray(t["split_conditions"], dtype=np.float32)
+            trees.append(_compact_tree(left, np.asarray(t["right_children"], dtype=np.int64),
+                                       np.asarray(t["split_indices"], dtype=np.int64), cond, cond,
+                                       np.asarray(t["default_left"], dtype=bool),
+                                       np.asarray(t.get("sum_hessian", np.ones(len(left))), dtype=np.float32)))
+        per_class.append(_assemble(trees, int(lmp["num_feature"]), output=OUT_RAW, global_bias=base_score))
+    return ImportedClasses(per_class, "softmax")

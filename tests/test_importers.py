@@ -161,3 +161,61 @@ def test_sklearn_forest_on_the_gpu(oracle):
         assert np.all(np.abs(got - want) <= 1e-5 * np.maximum(_l1(imp, lids) / imp.num_trees, 1.0)), api.STRATEGY_NAMES[s]
         ran += 1
     assert ran >= 2
+
+
+def _class_data(rows=900, cols=10, classes=4, seed=21):
+    rng = np.random.default_rng(seed)
+    X = rng.uniform(-1, 1, size=(rows, cols)).astype(np.float32)
+    y = (np.floor((X[:, 0] + X[:, 1] * X[:, 2] + 1.5) / 3.0 * classes).clip(0, classes - 1)).astype(int)
+    return X, y
+
+
+def _oracle_classes(oracle, imps, X, missing=-np.inf):
+    cols = [oracle.predict_sparse(i.nodes, i.tree_offsets, X, missing, output=i.output, global_bias=i.global_bias)
+            for i in imps.per_class]
+    out = np.stack(cols, axis=1).astype(np.float64)
+    if imps.link == "softmax":
+        out = np.exp(out - out.max(axis=1, keepdims=True))
+        out /= out.sum(axis=1, keepdims=True)
+    return out
+
+
+@pytest.mark.parametrize("kind", ["rf", "gb"])
+def test_sklearn_multiclass_per_class_outputs(oracle, kind):
+    X, y = _class_data()
+    if kind == "rf":
+        m = sk.RandomForestClassifier(n_estimators=20, max_depth=6, random_state=3).fit(X, y)
+    else:
+        m = sk.GradientBoostingClassifier(n_estimators=15, max_depth=3, random_state=3).fit(X, y)
+    imps = importers.from_sklearn_classes(m)
+    assert imps.num_classes == 4
+    got = _oracle_classes(oracle, imps, X)
+    assert np.allclose(got, m.predict_proba(X), rtol=0, atol=5e-6)
+    assert np.array_equal(got.argmax(1), m.predict(X))
+
+
+def test_xgboost_multiclass_trees_go_to_their_class(oracle):
+    base = _xgb_fixture()
+    t0, t1 = base["learner"]["gradient_booster"]["model"]["trees"]
+    model = {"learner": {"learner_model_param": {"base_score": "5E-1", "num_class": "3", "num_feature": "4"},
+                         "objective": {"name": "multi:softprob"},
+                         "gradient_booster": {"name": "gbtree", "model": {"trees": [t0, t1, t0, t1, t1, t0],
+                                                                       "tree_info": [0, 1, 2, 0, 1, 2]}}}}
+    imps = importers.from_xgboost_json_classes(model)
+    assert [i.num_trees for i in imps.per_class] == [2, 2, 2] and imps.link == "softmax"
+    # class 0 = trees {0, 3} = {t0, t1}: the same two trees as the binary fixture
+    two = importers.from_xgboost_json(base)
+    assert np.array_equal(imps.per_class[0].nodes, two.nodes)
+    with pytest.raises(ValueError):
+        importers.from_xgboost_json_classes(base)
+
+
+@pytest.mark.gpu
+def test_multiclass_forest_on_the_gpu(oracle):
+    import torch
+    X, y = _class_data(rows=4000, cols=16, classes=3, seed=5)
+    m = sk.RandomForestClassifier(n_estimators=32, max_depth=8, random_state=1).fit(X[:1500], y[:1500])
+    cf = importers.from_sklearn_classes(m).forests()
+    got = cf.predict(torch.from_numpy(X).cuda()).cpu().numpy()
+    assert got.shape == (4000, 3)
+    assert np.allclose(got, m.predict_proba(X), rtol=0, atol=5e-6)
