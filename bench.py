@@ -159,7 +159,28 @@ def run_reference(args, rank: int, world: int):
         "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
+
+
+_RESULT_FD = None
+
+
+def _claim_stdout():
+    """stdout carries ONE JSON line.  Libraries write there too (NCCL prints its version banner on
+    fd 1), so fd 1 is pointed at stderr for the run and the line goes out on the saved descriptor."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def _emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
 
 
 def main():
@@ -178,6 +199,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    _claim_stdout()
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
@@ -306,7 +328,7 @@ def main():
             v, kind, srows, sdt = cpu_reference_rate(cfg, nodes, 12.0, threads)
             line["cpu_baseline"] = {"value": v, "unit": "samples/s", "cores": threads, "kind": kind,
                                     "sample": f"{srows} rows of the workload in {sdt:.1f} s, OpenMP over rows"}
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if distributed:
         dist.destroy_process_group()
 
