@@ -6,11 +6,12 @@
 // The top DEPTH levels of every tree are a dense rank-quantised heap in shared memory, walked by
 // the six-instruction visit of k_smem_forest (traverse_group).  A walk that is still on an internal
 // node at the bottom of the top reads a continuation marker there and is PARKED in a lane-private
-// ring; it is finished in L2 on the breadth-first rank-form nodes (`deep`).
+// ring; it is finished in L2 on two-level blocks of 32 bytes {root, left, right, -} in rank form
+// (`deep_blocks`): one sector decides two levels.
 //
 // The L2 round trips of those deep walks never stall the warp: every lane keeps K deep walks in
-// flight and advances each by ONE level per traversal group -- the node loads are issued before the
-// group's shared-memory walk (~1.5 k cycles) and consumed after it.  So that a deep walk may outlive
+// flight and advances each by ONE block per traversal group -- the block loads (LDG.256) are issued
+// before the group's shared-memory walk (~1.5 k cycles) and consumed after it.  So that a deep walk may outlive
 // the tile that parked it, a warp owns TWO tile buffers (current and previous tile; the next tile
 // waits in registers): a walk reads its features from the buffer of its own tile, the score of tile
 // n is written at the end of tile n + 1, and only the walks of tile n - 1 that are STILL unfinished
