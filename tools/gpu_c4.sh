@@ -1,5 +1,5 @@
 #!/bin/bash
-# full GPU suite, config-4 probe + sweep, one full ncu capture of k_smem_forest_deep
+# config 4: full GPU suite, probe, one full ncu capture of k_smem_forest_deep, batch sweep
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
 timeout 300 python tools/probe_qtop.py 1000000 2>&1 | tail -1
