@@ -283,19 +283,25 @@ int tahoe_predict_host(tahoe_forest_t* f, int strategy, const float* h_data, siz
   if (strategy == TAHOE_STRATEGY_AUTO) strategy = select_strategy(f, num_rows, nullptr);
   // Slabs: copy of slab i+1 under the kernel of slab i, three slabs in flight.  The shared-memory
   // strategies deal 32-row tiles to sm_count x warps persistent warps, so their slabs are whole WAVES
-  // of tiles (no ragged last round per chunk pass), growing 2 -> 4 -> 8 waves: the first copy, which
-  // nothing can hide, is short, and the later kernels are long enough to amortise their chunk passes.
+  // of tiles (no ragged last round per chunk pass), growing from 2 waves by 1.5x up to 24: the first
+  // copy, which nothing can hide, is short; a slab may only grow as fast as the kernels before it run
+  // ahead of the copy engine (the copy of config 2's rows takes 0.8 of their predict); and the later
+  // kernels are long enough to amortise their chunk passes.  TAHOE_HOST_SLAB="first,growth%,cap" (waves).
   size_t slab = ((num_rows + 7) / 8 + 31) / 32 * 32;
   slab = std::min<size_t>(std::max<size_t>(slab, 65536), 1u << 20);
   size_t wave = 0;
+  int slab_first = 2, slab_growth = 150, slab_cap = 24;
   if ((strategy == TAHOE_STRATEGY_SHARED_FOREST || strategy == TAHOE_STRATEGY_SPLIT_SHARED_FOREST) &&
       (f->quant || (f->qt && f->sp_use_qt)) && f->trees_per_chunk > 0) {
     const bool paired = f->sparse && C > kStagedMaxCols && f->warps > 8;
     wave = (size_t)f->sm_count * (size_t)(paired ? f->warps / 2 : f->warps) * 32;
-    slab = std::max<size_t>(wave, std::min<size_t>(8 * wave, (size_t)1 << 20) / wave * wave);
+    if (const char* e = std::getenv("TAHOE_HOST_SLAB")) std::sscanf(e, "%d,%d,%d", &slab_first, &slab_growth, &slab_cap);
+    slab_first = std::max(slab_first, 1); slab_cap = std::max(slab_cap, slab_first); slab_growth = std::max(slab_growth, 100);
+    slab = (size_t)slab_cap * wave;
   }
   int total_launches = 0;
   size_t done = 0;
+  double slab_waves = slab_first;
   for (int i = 0; done < num_rows; ++i) {
     Workspace& w = f->ws[1 + i % kHostSlots];
     if (!w.stream) TAHOE_CUDA(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
@@ -308,7 +314,10 @@ int tahoe_predict_host(tahoe_forest_t* f, int strategy, const float* h_data, siz
       w.cap_slab_rows = slab;
     }
     size_t this_slab = slab;
-    if (wave && i < 2) this_slab = std::min(slab, (size_t)(2 << i) * wave);
+    if (wave) {
+      this_slab = std::min(slab, (size_t)(slab_waves + 0.5) * wave);
+      slab_waves = std::min((double)slab_cap, slab_waves * slab_growth / 100.0);
+    }
     const size_t n = std::min(this_slab, num_rows - done);
     TAHOE_CUDA(cudaMemcpyAsync(w.slab_data, h_data + done * (size_t)C, n * (size_t)C * sizeof(float),
                                cudaMemcpyHostToDevice, w.stream));
