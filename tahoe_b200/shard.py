@@ -70,3 +70,47 @@ class ShardedForest:
 
     def predict_local(self, data, preds=None, **kw):
         return self.forest.predict(data, preds, **kw)
+
+
+class PeerGather:
+    """Gather of the ranks' score slices WITHOUT a collective: `dst` owns one device
+    buffer for the whole batch, every other rank maps it through CUDA IPC once (the handle travels as
+    a pickled object over the process group -- gloo is enough) and then writes its slice with a plain
+    device-to-device copy over NVLink / NVSwitch.  Per predict: one copy of 4 bytes per row per rank
+    on the rank's own stream; the only synchronisation is the barrier the caller already has.
+
+        pg = PeerGather(total_rows)                  # once
+        forest.predict(x_local, pg.local)            # kernels write this rank's slice buffer
+        pg.push()                                    # slice -> dst's buffer (async, current stream)
+        torch.cuda.synchronize(); dist.barrier()     # dst may now read pg.full
+    """
+
+    def __init__(self, total_rows: int, dst: int = 0):
+        import torch
+        import torch.distributed as dist
+        from torch.multiprocessing.reductions import reduce_tensor
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.dst, self.total = dst, int(total_rows)
+        self.lo, self.hi = row_range(self.rank, self.world, self.total)
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.full = None
+        box = [None]
+        if self.rank == dst:
+            self.full = torch.empty(self.total, dtype=torch.float32, device=dev)
+            box[0] = reduce_tensor(self.full)          # (rebuild function, IPC handle + geometry)
+        if self.world > 1:
+            dist.broadcast_object_list(box, src=dst)
+            if self.rank != dst:
+                rebuild, args = box[0]
+                self.full = rebuild(*args)             # dst's memory, mapped into this process
+        # the kernels read their partial sums back between forest chunks: they write a LOCAL slice
+        # (on dst: a view of the gathered buffer itself), pushed once per predict
+        if self.rank == dst:
+            self.local = self.full[self.lo:self.hi]
+        else:
+            self.local = torch.empty(self.hi - self.lo, dtype=torch.float32, device=dev)
+
+    def push(self):
+        if self.rank != self.dst:
+            self.full[self.lo:self.hi].copy_(self.local, non_blocking=True)
