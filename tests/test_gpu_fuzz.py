@@ -7,7 +7,10 @@ import pytest
 from tahoe_b200 import api, synth
 from tests.helpers import score_close
 
+import os
+
 pytestmark = pytest.mark.gpu
+SOAK = int(os.environ.get("TAHOE_FUZZ_SOAK", "1"))      # x the seed counts (soak runs: TAHOE_FUZZ_SOAK=10)
 
 
 def _run(f, data, s, ids=True):
@@ -33,7 +36,7 @@ def _check_all(f, data, want, wids, mass, tag):
     assert ran >= 1, tag
 
 
-@pytest.mark.parametrize("seed", range(20))
+@pytest.mark.parametrize("seed", range(20 * SOAK))
 def test_random_sparse_forests(oracle, seed):
     rng = np.random.default_rng(1000 + seed)
     T = int(rng.choice([1, 2, 5, 6, 7, 31, 64, 130]))
@@ -51,7 +54,7 @@ def test_random_sparse_forests(oracle, seed):
     _check_all(f, data, want, wids, mass, (seed, T, depth, cols, rows, leaf_prob, miss, output))
 
 
-@pytest.mark.parametrize("seed", range(8))
+@pytest.mark.parametrize("seed", range(8 * SOAK))
 def test_random_dense_forests(oracle, seed):
     rng = np.random.default_rng(2000 + seed)
     T = int(rng.choice([1, 3, 32, 33, 100, 257]))
@@ -65,3 +68,33 @@ def test_random_dense_forests(oracle, seed):
     npt = (1 << (depth + 1)) - 1
     mass = np.abs(nodes["val"].reshape(T, npt)[np.arange(T)[None, :], wids]).sum(1)
     _check_all(f, data, want, wids, mass, (seed, T, depth, cols, rows))
+
+
+@pytest.mark.parametrize("seed", range(6 * SOAK))
+def test_random_deep_sparse_forests(oracle, seed, monkeypatch):
+    """Bigger, deeper sparse forests with random top depths and chunk sizes forced on the planner:
+    many deep walks per row, full rings, several tiles per warp, several chunks, pairs of warps."""
+    rng = np.random.default_rng(3000 + seed)
+    T = int(rng.choice([100, 200, 500]))
+    depth = int(rng.integers(10, 21))
+    cols = int(rng.choice([20, 33, 50, 64]))
+    rows = int(rng.choice([20_000, 60_001, 148 * 16 * 32 * 2 + 7]))
+    leaf_prob = float(rng.choice([0.2, 0.3, 0.45]))
+    if rng.random() < 0.7:
+        monkeypatch.setenv("TAHOE_QTOP_DEPTH", str(int(rng.integers(1, 9))))
+    if rng.random() < 0.5:
+        monkeypatch.setenv("TAHOE_QTOP_TPC", str(int(rng.choice([6, 12, 24, 48]))))
+    sp, offs, w, lv = synth.gen_sparse_forest(900 + seed, T, depth, cols, leaf_prob=leaf_prob)
+    data = synth.gen_data(950 + seed, rows, cols, miss_frac=float(rng.choice([0.0, 0.01, 0.2])), nan_frac=0.002)
+    want, wids = oracle.predict_sparse(sp, offs, data, -999.0, want_leaf_ids=True)
+    f = api.Forest.from_sparse(sp, offs, cols, weights=w, missing=-999.0)
+    assert f.info().sparse_top_active == 1
+    mass = np.abs(sp["val"][offs[:-1][None, :] + wids]).sum(1)
+    for s in (api.SPLIT_SHARED_FOREST, api.DIRECT):
+        got, ids = _run(f, data, s)
+        assert np.array_equal(ids, wids), (seed, api.STRATEGY_NAMES[s])
+        assert score_close(got, want, mass), (seed, api.STRATEGY_NAMES[s])
+        got2, _ = _run(f, data, s, ids=False)
+        assert score_close(got2, want, mass), (seed, api.STRATEGY_NAMES[s])
+        got3, _ = _run(f, data, s, ids=False)
+        assert np.array_equal(got2.view(np.uint32), got3.view(np.uint32))     # reproducible run to run
