@@ -98,3 +98,6 @@ def test_random_deep_sparse_forests(oracle, seed, monkeypatch):
         assert score_close(got2, want, mass), (seed, api.STRATEGY_NAMES[s])
         got3, _ = _run(f, data, s, ids=False)
         assert np.array_equal(got2.view(np.uint32), got3.view(np.uint32))     # reproducible run to run
+    # host buffers in, host scores out: wave-aligned slabs through the same kernels
+    got_h = f.predict_host(data, strategy=api.SPLIT_SHARED_FOREST)
+    assert score_close(got_h, want, mass), seed
