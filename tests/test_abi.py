@@ -186,3 +186,27 @@ def test_binary_cache_round_trip_and_corruption(tmp_path, golden_dir):
     api.save_data_binary(dp, np.zeros((0, 4), np.float32), -1.0)
     x3, m3 = api.load_data_binary(dp)
     assert x3.shape == (0, 4) and m3 == -1.0
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/Struct.h"), reason="needs the reference tree (this container only)")
+def test_integration_stub_compiles_against_the_reference_headers(tmp_path):
+    """the binding a reference maintainer would add (`b200_forest : forest`
+    over the C ABI) is extracted from the document and compiled + linked against the reference's own
+    Struct.h, in place, with the reference's build flags -- the drop-in claim, checked."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    doc = open(os.path.join(root, "INTEGRATION.md")).read()
+    stub = re.search(r"```cpp\n(// tahoe_b200_forest\.h.*?)```", doc, re.S).group(1)
+    (tmp_path / "tahoe_b200_forest.h").write_text(stub)
+    (tmp_path / "main.cu").write_text(
+        '#include "tahoe_b200_forest.h"\n'
+        "int main() { forest_params_t ps{}; b200_forest* f = new b200_forest; (void)ps; delete f; return 0; }\n")
+    from tahoe_b200 import build
+    lib = os.path.dirname(build.build())
+    exe = str(tmp_path / "stub_main")
+    cmd = ["nvcc", "-include", "cfloat", "-include", "algorithm", "-I/root/reference/inc", "-I/root/reference",
+           "-I" + os.path.join(root, "include"), "-std=c++17", "-w", "-gencode", "arch=compute_100a,code=sm_100a",
+           str(tmp_path / "main.cu"), "-o", exe, "-L" + lib, "-ltahoe_b200", "-Xlinker", "-rpath", "-Xlinker", lib]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert os.path.exists(exe)
