@@ -16,10 +16,16 @@ doc = open(sys.argv[1]).read()
 open(sys.argv[2], "w").write(re.search(r"```cpp\n(// tahoe_b200_forest\.h.*?)```", doc, re.S).group(1))
 PY
 # the harness, with the engine type renamed and the stub included after Struct.h
+# ... and the feasibility gates (BaseTahoeTest.h:657-679, the reference's 0.8 x 48 KB budget) replaced
+# by the library's own answer, as INTEGRATION.md says
+GATE='if (tahoe_strategy_applicable(forest->h, loop, ps.num_rows) != TAHOE_OK) { acc[loop] = FLT_MAX; printf("Strategy %d is not suitable for this case.\\n", loop+1); continue; }'
 sed -e 's/dense_adaptive_forest/b200_forest/g' \
     -e 's/#include "Struct.h"/#include "Struct.h"\n#include "tahoe_b200_forest.h"/' \
+    -e "s/selected_algorithm = loop;/selected_algorithm = loop; $GATE/" \
+    -e 's/int max_shm = (int)dev.sharedMemPerBlock \* 0.8;/int max_shm = 1 << 30;/' \
     "$REF/BaseTahoeTest.h" > "$W/BaseTahoeTest.h"
 grep -q 'tahoe_b200_forest.h' "$W/BaseTahoeTest.h" || { echo "could not place the stub include"; exit 1; }
+grep -q 'tahoe_strategy_applicable' "$W/BaseTahoeTest.h" || { echo "could not place the gate"; exit 1; }
 cp "$REF/main.cu" "$W/main.cu"
 mkdir -p "$HERE/_ref"
 nvcc -include cfloat -include algorithm -I"$W" -I"$REF/inc" -I"$REF" -I"$ROOT/include" -O3 --expt-extended-lambda \
