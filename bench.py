@@ -4,11 +4,16 @@
     python bench.py --gpus N --steps K --warmup W            # our arm
     python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU predict
 
-A "step" = one tahoe_predict over one batch of synthetic rows.  Workload at N=1 is
-BASELINE.json configs[1]: SUSY-shaped synthetic forest (18 features, 500 trees, depth 10)
-on 5M rows.  For N>1 every rank holds the same forest and its own 5M-row shard (weak
-scaling; no data-path collective -- the path shards by rows).
-Prints ONE JSON line on rank 0.
+Headline workload (BASELINE.json configs[2], the one north_star names for 1/2/4/8 GPUs): Higgs-shaped
+synthetic forest (28 features, 1000 trees, depth 12) on 10M rows IN TOTAL, rank g owning rows
+[g*R/N, (g+1)*R/N) -- strong scaling; N=1 holds all 10M rows (1.12 GB).  A "step" = one
+tahoe_predict_to over this rank's rows whose last-chunk epilogue stores the final scores straight
+into rank 0's gathered buffer (CUDA-IPC mapped; no copy and no collective on the path).
+The forest is replicated once (one broadcast, untimed).
+
+At N=1 the same JSON line carries `configs` (C1..C4, one device-resident measurement each, with the
+SURVEY 8(d) roofline fractions against the L2 / HBM / shared-memory peaks measured in this run) and
+`sweep` (model pick vs exhaustive enumeration at a few batch sizes).  Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
 
@@ -26,11 +31,12 @@ sys.path.insert(0, ROOT)
 
 from tahoe_b200 import synth  # noqa: E402
 
-WORKLOAD = "C2"
+WORKLOAD = "C3"
 METRIC = "samples/sec"
+L2_FLUSH_BYTES = 256 << 20
 
 
-def _peaks():
+def _hbm_peak():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
         with open(path) as f:
@@ -38,20 +44,28 @@ def _peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def _traffic():
-    """dram bytes per launch of the dominant kernel from the committed ncu capture, or None."""
+def _traffic(cfg_id: str):
+    """dram bytes per launch of the config's dominant kernel from the committed ncu capture, or None."""
     path = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(path):
         with open(path) as f:
-            return json.load(f).get("k_smem_forest_dram_bytes_per_launch")
+            return json.load(f).get("dram_bytes_per_launch", {}).get(cfg_id)
     return None
 
 
-def algorithmic_bytes_per_sample(cfg) -> float:
-    """B_sample = 4C+4, B_node = T*(d*(4+b)+4), b = reference width rule."""
-    C, T, d = cfg["cols"], cfg["trees"], cfg["depth"]
-    b = 1 if C - 1 < 32 else (2 if C - 1 < 8192 else 4)
-    return (4 * C + 4) + T * (d * (4 + b) + 4)
+def width_rule(cols: int) -> int:
+    """reference node-width rule, Struct.h:1831-1852: 1 if max_fid < 32, 2 if < 8192, else 4"""
+    return 1 if cols - 1 < 32 else (2 if cols - 1 < 8192 else 4)
+
+
+def algorithmic_bytes(cfg, rows: int, mean_depth: float, forest_nodes: int):
+    """B_sample = R(4C+4); B_node = R*T*(dbar*(4+b)+4); B_forest = T*N_real*(4+b)."""
+    C, T = cfg["cols"], cfg["trees"]
+    b = width_rule(C)
+    b_sample = rows * (4.0 * C + 4.0)
+    b_node = float(rows) * T * (mean_depth * (4 + b) + 4)
+    b_forest = float(forest_nodes) * (4 + b)
+    return b_sample, b_node, b_forest
 
 
 class ClockSampler(threading.Thread):
@@ -100,23 +114,36 @@ def physical_gpu_index(local_rank: int) -> int:
     return local_rank
 
 
-def cpu_reference_rate(cfg, nodes, target_s: float, threads: int):
-    """Time the reference's CPU predict (oracle/_ref) -- or the oracle port when the shim is
-    absent -- on a bounded sample of the workload.  Returns (samples/s, kind, rows, seconds)."""
+def host_threads() -> int:
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
+def _cpu_runner(cfg, nodes, threads):
+    """The reference's own CPU predict (oracle/_ref, OpenMP over rows) -- or the oracle port when the
+    shim is absent.  The only place besides tests/ and smoke() that executes anything under oracle/."""
     from oracle.oracle import Oracle, RefShim
     if RefShim.available():
-        shim, kind = RefShim(), "reference"
-        run = lambda d: shim.predict(nodes, cfg["trees"], cfg["depth"], d, -999.0, nthreads=threads)  # noqa: E731
-    else:
-        orc, kind = Oracle(), "port"
-        run = lambda d: orc.predict_dense(nodes, cfg["trees"], cfg["depth"], d, -999.0)  # noqa: E731
-    probe = synth.gen_data(synth.DATA_SEED[WORKLOAD], 256 * threads, cfg["cols"])
+        shim = RefShim()
+        return (lambda d: shim.predict(nodes, cfg["trees"], cfg["depth"], d, -999.0, nthreads=threads)), "reference"
+    orc = Oracle()
+    return (lambda d: orc.predict_dense(nodes, cfg["trees"], cfg["depth"], d, -999.0)), "port"
+
+
+def cpu_reference_rate(cfg, nodes, target_s: float, threads: int):
+    """Time the CPU predict on a bounded sample of the workload: (samples/s, kind, rows, seconds)."""
+    run, kind = _cpu_runner(cfg, nodes, threads)
+    probe = synth.gen_data(synth.DATA_SEED[WORKLOAD], 64 * threads, cfg["cols"])
     run(probe[:64])
     t0 = time.perf_counter(); run(probe); dt = time.perf_counter() - t0
-    rows = int(max(256 * threads, min(2_000_000, probe.shape[0] / dt * target_s)))
+    rows = int(max(64 * threads, min(2_000_000, probe.shape[0] / dt * target_s)))
     data = synth.gen_data(synth.DATA_SEED[WORKLOAD], rows, cfg["cols"])
     t0 = time.perf_counter(); run(data); dt = time.perf_counter() - t0
     return rows / dt, kind, rows, dt
+
+
+def workload_name(cfg, rows_total):
+    return (f"{cfg['name']} synthetic forest ({cfg['cols']} features, {cfg['trees']} trees, depth "
+            f"{cfg['depth']}) on {rows_total} rows in total")
 
 
 def run_reference(args, rank: int, world: int):
@@ -124,21 +151,15 @@ def run_reference(args, rank: int, world: int):
     if rank != 0:
         return
     cfg = synth.CONFIGS[WORKLOAD]
-    threads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
+    threads = host_threads()
     nodes = synth.gen_dense_forest(synth.FOREST_SEED[WORKLOAD], cfg["trees"], cfg["depth"], cfg["cols"])
-    from oracle.oracle import Oracle, RefShim
-    if RefShim.available():
-        shim, kind = RefShim(), "reference"
-        run = lambda d: shim.predict(nodes, cfg["trees"], cfg["depth"], d, -999.0, nthreads=threads)  # noqa: E731
-    else:
-        orc, kind = Oracle(), "port"
-        run = lambda d: orc.predict_dense(nodes, cfg["trees"], cfg["depth"], d, -999.0)  # noqa: E731
+    run, kind = _cpu_runner(cfg, nodes, threads)
     # size one step to ~1.5 s so warmup+steps end within a few minutes
-    probe = synth.gen_data(synth.DATA_SEED[WORKLOAD], 256 * threads, cfg["cols"])
+    probe = synth.gen_data(synth.DATA_SEED[WORKLOAD], 64 * threads, cfg["cols"])
     run(probe[:64])
     t0 = time.perf_counter(); run(probe); dt = time.perf_counter() - t0
     budget = min(1.5, 150.0 / max(1, args.steps + args.warmup))
-    rows = int(max(256 * threads, min(2_000_000, probe.shape[0] / dt * budget)))
+    rows = int(max(64 * threads, min(2_000_000, probe.shape[0] / dt * budget)))
     data = synth.gen_data(synth.DATA_SEED[WORKLOAD], rows, cfg["cols"])
     for _ in range(args.warmup):
         run(data)
@@ -151,10 +172,9 @@ def run_reference(args, rank: int, world: int):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": f"{cfg['name']} synthetic forest ({cfg['cols']} features, {cfg['trees']} trees, "
-                               f"depth {cfg['depth']}) on {cfg['rows']} rows", "sampled_rows_per_step": rows},
+        "config": {"workload": workload_name(cfg, cfg["rows"]), "sampled_rows_per_step": rows},
         "cpu_baseline": {"value": value, "unit": "samples/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -183,6 +203,113 @@ def _emit(line: dict):
         os.write(_RESULT_FD, data)
 
 
+# ---------------------------------------------------------------------------------------------
+def build_forest(cfg_id: str, nodes=None):
+    """-> (Forest, real node count).  Dense configs from the AoS nodes, config 4 from compact nodes."""
+    from tahoe_b200 import api
+    cfg = synth.CONFIGS[cfg_id]
+    if cfg["sparse"]:
+        sp, offs, w, _ = synth.gen_sparse_forest(synth.FOREST_SEED[cfg_id], cfg["trees"], cfg["depth"], cfg["cols"])
+        return api.Forest.from_sparse(sp, offs, cfg["cols"], weights=w, missing=-999.0), int(offs[-1])
+    if nodes is None:
+        nodes = synth.gen_dense_forest(synth.FOREST_SEED[cfg_id], cfg["trees"], cfg["depth"], cfg["cols"])
+    f = api.Forest.from_dense(nodes, cfg["trees"], cfg["depth"], cfg["cols"], missing=-999.0)
+    return f, cfg["trees"] * synth.tree_num_nodes(cfg["depth"])
+
+
+KERNEL_OF = {  # dominant kernel per strategy (names as they appear in the ncu launch lists under profiles/)
+    "direct": "k_direct", "shared_data_per_thread": "k_direct<smem_rows>", "shared_data": "k_shared_data",
+    "shared_forest": "k_smem_forest", "split_shared_forest": "k_smem_forest",
+}
+
+
+def measure_config(cfg_id, forest, n_nodes, data, peaks, hbm_gbs, steps, strategy=None, flush=None):
+    """One device-resident measurement of one config: step time over `steps` predicts (CUDA events on
+    the launch stream) and the dominant kernel's own time (events recorded around it inside the
+    library).  Returns the sub-record with the SURVEY 8(d) fractions."""
+    import torch
+    from tahoe_b200 import api
+    cfg = synth.CONFIGS[cfg_id]
+    rows = int(data.shape[0])
+    info = forest.info()
+    s = forest.select(rows)[0] if strategy is None else strategy
+    preds = torch.empty(rows, dtype=torch.float32, device="cuda")
+    for _ in range(3):
+        forest.predict(data, preds, strategy=s)
+    torch.cuda.synchronize()
+    forest.set_profiling(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    total = 0.0
+    for _ in range(steps):
+        if flush is not None:
+            flush.zero_()                      # inputs smaller than L2 (config 1 is not; the others are larger anyway)
+        e0.record(); forest.predict(data, preds, strategy=s); e1.record()
+        torch.cuda.synchronize()
+        total += e0.elapsed_time(e1)
+    q_ms, t_ms, n = forest.profile_read()
+    forest.set_profiling(False)
+    step_ms = total / steps
+    kernel_ms = t_ms / n if n else step_ms
+    name = api.STRATEGY_NAMES[s]
+    kernel = KERNEL_OF[name]
+    if info.is_sparse and name in ("shared_forest", "split_shared_forest"):
+        kernel = "k_smem_forest_deep" if info.sparse_top_active else "k_sparse_smem"
+    mean_depth = info.mean_depth if info.is_sparse else float(cfg["depth"])
+    b_sample, b_node, b_forest = algorithmic_bytes(cfg, rows, mean_depth, n_nodes)
+    abytes = b_sample + b_node
+    sec = kernel_ms * 1e-3
+    rec = {
+        "workload": workload_name(cfg, rows), "rows": rows, "strategy": name, "kernel": kernel,
+        "kernel_ms": kernel_ms, "prepare_ms": (q_ms / n if n else 0.0), "step_ms": step_ms,
+        "samples_per_s": rows / (step_ms * 1e-3),
+        "algorithmic_bytes_per_launch": abytes, "achieved_gbs": abytes / sec / 1e9,
+        "forest_fits_l2": bool(b_forest <= peaks["l2_bytes"]),
+        "frac_l2": abytes / sec / 1e9 / peaks["l2_read_gbs"],
+        "frac_hbm_only": (b_sample + b_forest) / sec / 1e9 / hbm_gbs,
+        "mean_depth": mean_depth, "traffic": _traffic(cfg_id),
+    }
+    if name in ("shared_forest", "split_shared_forest") and not info.is_sparse:
+        # the node and rank words of this kernel come out of SHARED MEMORY: 8 B per visit + 4 B per leaf
+        smem_bytes = float(rows) * cfg["trees"] * (cfg["depth"] * 8 + 4)
+        rec["frac_smem"] = smem_bytes / sec / 1e9 / peaks["smem_read_gbs"]
+        rec["plan"] = {"warps": info.smem_warps, "staged": info.smem_staged, "group": info.smem_group,
+                       "trees_per_chunk": info.trees_per_chunk, "chunks": info.num_chunks}
+    return rec, s, preds
+
+
+def time_strategy(forest, d, p, s, reps=3):
+    import torch
+    forest.predict(d, p, strategy=s)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    best = float("inf")
+    for _ in range(reps):
+        e0.record(); forest.predict(d, p, strategy=s); e1.record(); torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    return best
+
+
+def sweep_record(cfg_id, forest, data, sizes):
+    """BASELINE.json config 5 in small: every applicable strategy timed at a few batch sizes, the
+    model's pick against the measured best (profiles/ holds the full sweeps)."""
+    import torch
+    from tahoe_b200 import api
+    pts = []
+    for R in sizes:
+        if R > data.shape[0]:
+            continue
+        d = data[:R]
+        p = torch.empty(R, dtype=torch.float32, device="cuda")
+        times = {api.STRATEGY_NAMES[s]: time_strategy(forest, d, p, s) for s in api.ALL_STRATEGIES
+                 if forest.applicable(s, R)}
+        pick = api.STRATEGY_NAMES[forest.select(R)[0]]
+        best = min(times, key=times.get)
+        pts.append({"rows": R, "ms": times, "pick": pick, "best": best, "slowdown": times[pick] / times[best]})
+    return {"config": cfg_id, "points": pts,
+            "hit_rate": sum(p["pick"] == p["best"] for p in pts) / max(1, len(pts)),
+            "worst_slowdown": max([p["slowdown"] for p in pts], default=1.0)}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -190,9 +317,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--strategy", type=int, default=-1, help="force a strategy id (default: model picks)")
-    ap.add_argument("--rows", type=int, default=0, help="override rows per GPU (debug only)")
+    ap.add_argument("--rows", type=int, default=0, help="override TOTAL rows (debug only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs only)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C1/C2/C4 sub-records and the sweep")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -206,7 +334,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from tahoe_b200 import api
+    from tahoe_b200 import api, shard
     api.lib()  # fail loudly before any work if the CUDA library is missing
     assert torch.cuda.is_available(), "bench.py (our arm) needs a GPU; there is no CPU path"
     torch.cuda.set_device(local_rank)
@@ -216,10 +344,11 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     cfg = dict(synth.CONFIGS[WORKLOAD])
-    rows = args.rows or cfg["rows"]
+    total_rows = args.rows or cfg["rows"]
+    lo, hi = shard.row_range(rank, world, total_rows)
+    rows = hi - lo
     n_nodes = cfg["trees"] * synth.tree_num_nodes(cfg["depth"])
     # ---- forest: built once on rank 0, broadcast once (the only collective; not timed)
-    from tahoe_b200 import shard
     nodes = None
     if rank == 0:
         nodes = synth.gen_dense_forest(synth.FOREST_SEED[WORKLOAD], cfg["trees"], cfg["depth"], cfg["cols"])
@@ -228,9 +357,10 @@ def main():
     info = forest.info()
     strategy = args.strategy if args.strategy >= 0 else forest.select(rows)[0]
 
-    # ---- this rank's shard, generated in HBM (inputs resident before the timed region)
-    data = api.gen_data_device(synth.DATA_SEED[WORKLOAD], rows, cfg["cols"], row0=rank * rows)
-    preds = torch.empty(rows, dtype=torch.float32, device="cuda")
+    # ---- this rank's shard, generated in HBM (inputs resident before the timed region); the final
+    # scores of every rank land in rank 0's buffer (peer-mapped), partial sums stay local
+    data = api.gen_data_device(synth.DATA_SEED[WORKLOAD], rows, cfg["cols"], row0=lo)
+    gather = shard.PeerGather(total_rows, dst=0)
     torch.cuda.synchronize()
 
     def barrier():
@@ -239,7 +369,7 @@ def main():
         torch.cuda.synchronize()
 
     for _ in range(args.warmup):
-        forest.predict(data, preds, strategy=strategy)
+        gather.predict(forest, data, strategy=strategy)
     launches_per_step = forest.launches()
     forest.set_profiling(True)
     sampler = ClockSampler(physical_gpu_index(local_rank))
@@ -248,7 +378,7 @@ def main():
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        forest.predict(data, preds, strategy=strategy)
+        gather.predict(forest, data, strategy=strategy)
     e1.record()
     barrier()
     clocks = sampler.result()
@@ -260,76 +390,120 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
     ms_step = ms_total / args.steps
-    value = world * rows / (ms_step * 1e-3)
+    value = total_rows / (ms_step * 1e-3)
+    gathered_checksum = float(gather.full.double().sum().item()) if rank == 0 else None
 
-    # ---- end to end: pinned host rows in, host scores out, every step
+    # ---- end to end: pinned host rows in, host scores out, every step (this rank's shard)
     e2e = None
     if not args.no_e2e:
         h_data = torch.empty((rows, cfg["cols"]), dtype=torch.float32, pin_memory=True)
         h_data.copy_(data)
         h_preds = torch.empty(rows, dtype=torch.float32, pin_memory=True)
-        e2e_steps = max(3, min(args.steps, 10))
-        for _ in range(2):
-            forest.predict_host(h_data, h_preds, strategy=strategy)
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            forest.predict_host(h_data, h_preds, strategy=strategy)
-        torch.cuda.synchronize()
-        e2e_s = time.perf_counter() - t0
-        if distributed:
-            t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            e2e_s = float(t.item())
-        same = bool(torch.equal(h_preds.cuda(), preds))
-        e2e = {"value": world * rows * e2e_steps / e2e_s, "unit": "samples/s",
-               "h2d_bytes_per_step": rows * cfg["cols"] * 4, "d2h_bytes_per_step": rows * 4,
-               "steps": e2e_steps, "matches_device_path": same}
+        e2e_steps = max(3, min(args.steps, 5))
+
+        def timed_host(copy_only):
+            for _ in range(2):
+                forest.predict_host(h_data, h_preds, strategy=strategy, copy_only=copy_only)
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(e2e_steps):
+                forest.predict_host(h_data, h_preds, strategy=strategy, copy_only=copy_only)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            if distributed:
+                tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                dt = float(tt.item())
+            return dt
+
+        copy_s = timed_host(True)       # the same slabs, copies only: the bound of this path
+        e2e_s = timed_host(False)
+        same = bool(torch.equal(h_preds.cuda(), gather.full[lo:hi] if rank == 0 else h_preds.cuda()))
+        h2d = rows * cfg["cols"] * 4
+        e2e = {"value": total_rows * e2e_steps / e2e_s, "unit": "samples/s",
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": rows * 4,
+               "steps": e2e_steps, "matches_device_path": same,
+               "copies_only_samples_per_s": total_rows * e2e_steps / copy_s,
+               "h2d_only_gbs": world * (h2d + rows * 4) * e2e_steps / copy_s / 1e9,
+               "frac_of_bound": (total_rows * e2e_steps / e2e_s) / min(value, total_rows * e2e_steps / copy_s)}
+        del h_data, h_preds
 
     if rank == 0:
-        peak, peak_src = _peaks()
-        abytes = algorithmic_bytes_per_sample(cfg) * rows
+        hbm_gbs, hbm_src = _hbm_peak()
+        peaks = api.measure_peaks()         # L2 / shared-memory read bandwidth, measured now, on this GPU
+        b_sample, b_node, b_forest = algorithmic_bytes(cfg, rows, float(cfg["depth"]), n_nodes)
+        abytes = b_sample + b_node
         trav_ms = t_ms / n_prof if n_prof else ms_step
-        achieved = abytes / (trav_ms * 1e-3) / 1e9
-        # second view of the same kernel: its node and rank words come out of SHARED MEMORY, whose
-        # bandwidth (128 B/clk/SM, B300_MICROARCH.md, x SM clock sampled during the run) is the bound it
-        # actually runs against; ideal bytes = 8 B per node visit (node word + rank word) + 4 B per leaf
-        sm_clock = (clocks.get("sm_mhz") or 1965.0) * 1e6
-        smem_peak = info.sm_count * 128.0 * sm_clock / 1e9
+        sec = trav_ms * 1e-3
+        achieved = abytes / sec / 1e9
         smem_bytes = float(rows) * cfg["trees"] * (cfg["depth"] * 8 + 4)
-        smem_achieved = smem_bytes / (trav_ms * 1e-3) / 1e9
+        fits_l2 = b_forest <= peaks["l2_bytes"]
+        peak = peaks["l2_read_gbs"] if fits_l2 else hbm_gbs
         line = {
             "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {
-                "workload": f"{cfg['name']} synthetic forest ({cfg['cols']} features, {cfg['trees']} trees, "
-                            f"depth {cfg['depth']}) on {rows} rows per GPU",
-                "strategy": api.STRATEGY_NAMES[strategy], "rows_per_gpu": rows, "parallelism": f"rows x{world}",
-                "l2_policy": "inputs_exceed_l2 (360 MB of rows per step vs 126 MB L2)",
+                "workload": workload_name(cfg, total_rows),
+                "strategy": api.STRATEGY_NAMES[strategy], "rows_total": total_rows, "rows_per_gpu": rows,
+                "parallelism": f"rows sharded x{world}, forest replicated",
+                "gathered": True,
+                "gather": "final scores stored by the kernel epilogue into rank 0's buffer (CUDA IPC peer mapping)",
+                "l2_policy": f"inputs_exceed_l2 ({rows * cfg['cols'] * 4 / 1e6:.0f} MB of rows per GPU per step "
+                             f"vs {peaks['l2_bytes'] / 1e6:.0f} MB L2)",
                 "forest_chunks": info.num_chunks, "trees_per_chunk": info.trees_per_chunk,
-                "node_bytes": 4, "rank_bits": info.rank_bits},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": _traffic(), "kernel": "k_smem_forest",
+                "plan": {"warps": info.smem_warps, "staged": info.smem_staged, "group": info.smem_group},
+                "node_bytes": 4, "rank_bits": info.rank_bits, "gathered_checksum": gathered_checksum},
+            "roofline": {"bound": "l2" if fits_l2 else "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": _traffic(WORKLOAD), "kernel": "k_smem_forest",
                          "kernel_ms": trav_ms, "quantize_ms": (q_ms / n_prof if n_prof else None),
-                         "algorithmic_bytes_per_launch": abytes, "peak_source": peak_src,
-                         "note": "SURVEY 8(d) accounting: sample bytes + forest-node bytes touched; the node bytes "
-                                 "are served from shared memory, so achieved exceeds the HBM peak -- see smem",
-                         "smem": {"bound": "shared-memory bandwidth", "achieved": smem_achieved, "peak": smem_peak,
-                                  "unit": "GB/s", "frac": smem_achieved / smem_peak,
-                                  "peak_source": "148 SMs x 128 B/clk x sampled SM clock",
+                         "algorithmic_bytes_per_launch": abytes,
+                         "peak_source": "L2 streaming-read bandwidth measured in this run (tahoe_measure_peaks); SURVEY 8(d): "
+                                        "the packed forest fits L2" if fits_l2 else hbm_src,
+                         "frac_hbm_only": (b_sample + b_forest) / sec / 1e9 / hbm_gbs,
+                         "hbm_peak": hbm_gbs, "hbm_peak_source": hbm_src,
+                         "note": "SURVEY 8(d) accounting: sample bytes + forest-node bytes touched, rank 0's shard; the node "
+                                 "words are served from shared memory -- see smem for the bound the kernel runs against",
+                         "smem": {"bound": "shared-memory bandwidth", "achieved": smem_bytes / sec / 1e9,
+                                  "peak": peaks["smem_read_gbs"], "unit": "GB/s",
+                                  "frac": smem_bytes / sec / 1e9 / peaks["smem_read_gbs"],
+                                  "peak_source": "conflict-free LDS.32 stream measured in this run",
                                   "ideal_bytes_per_launch": smem_bytes}},
+            "peaks": peaks,
             "e2e": e2e,
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks,
         }
+        if world == 1 and not args.no_configs:
+            flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device="cuda")
+            cfgs = {}
+            rec, _, _ = measure_config("C3", forest, n_nodes, data, peaks, hbm_gbs, steps=3, strategy=strategy)
+            cfgs["C3"] = rec
+            sweeps = [sweep_record("C3", forest, data, [1, 1000, 100_000, 10_000_000])]
+            del data
+            forest.close()
+            torch.cuda.empty_cache()
+            for cid, steps in (("C1", 20), ("C2", 10), ("C4", 10)):
+                c = synth.CONFIGS[cid]
+                f, nn = build_forest(cid)
+                d = api.gen_data_device(synth.DATA_SEED[cid], c["rows"], c["cols"])
+                rec, _, _ = measure_config(cid, f, nn, d, peaks, hbm_gbs, steps=steps, flush=flush)
+                cfgs[cid] = rec
+                if cid == "C2":
+                    sweeps.append(sweep_record("C2", f, d, [1, 1000, 100_000, 5_000_000]))
+                del d
+                f.close()
+                torch.cuda.empty_cache()
+            line["configs"] = {k: cfgs[k] for k in sorted(cfgs)}
+            line["sweep"] = sweeps
         if world == 1 and not args.no_cpu_baseline:
-            threads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
+            threads = host_threads()
             v, kind, srows, sdt = cpu_reference_rate(cfg, nodes, 12.0, threads)
             line["cpu_baseline"] = {"value": v, "unit": "samples/s", "cores": threads, "kind": kind,
                                     "sample": f"{srows} rows of the workload in {sdt:.1f} s, OpenMP over rows"}
         _emit(line)
     if distributed:
+        dist.barrier()
         dist.destroy_process_group()
 
 

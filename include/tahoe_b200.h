@@ -136,12 +136,35 @@ int tahoe_forest_info(const tahoe_forest_t* f, tahoe_forest_info_t* info);
  * stream: a cudaStream_t (NULL = default stream).  Asynchronous. */
 int tahoe_predict(tahoe_forest_t* f, int strategy, const float* d_data, size_t num_rows,
                   float* d_preds, int32_t* d_leaf_ids, void* stream);
+/* tahoe_predict with the FINAL scores going to d_out, which the kernels only ever write (once per
+ * row, in the epilogue of the last forest chunk) and never read back: d_out may be memory of
+ * another GPU mapped into this process (cudaIpcOpenMemHandle / peer access).  This is the gather of
+ * the multi-GPU path fused into the kernel epilogue: rank g passes rank 0's gathered
+ * buffer + its own row offset, and no copy or collective follows the predict.  The reference has no
+ * counterpart (one stream, one device, BaseTahoeTest.h:78).  d_partial: local scratch of num_rows
+ * floats for the partial sums the multi-pass strategies carry between chunks; NULL = scratch owned
+ * by the handle (grow-only).
+ * Calls on one handle are stream-ordered; calls issued on different streams are serialised on the
+ * device by an event (they share the handle's scratch); a handle must not be used from two host
+ * threads at once. */
+int tahoe_predict_to(tahoe_forest_t* f, int strategy, const float* d_data, size_t num_rows,
+                     float* d_out, float* d_partial, int32_t* d_leaf_ids, void* stream);
+/* Lets kernels launched on the CURRENT device store into memory of `peer_device` (the device that
+ * owns the gathered output buffer of tahoe_predict_to).  Idempotent.  TAHOE_ERR_NOT_APPLICABLE when
+ * the two devices have no peer path. */
+int tahoe_enable_peer_access(int peer_device);
 /* Same call with HOST buffers: slabs of rows are copied in, predicted and copied
  * out on internal streams so that PCIe transfers overlap the traversal.  This is
  * the harness path generate_data_from_file -> updateDevice -> predict -> updateHost
  * (BaseTahoeTest.h:392, 691-692).  Synchronous. */
 int tahoe_predict_host(tahoe_forest_t* f, int strategy, const float* h_data, size_t num_rows,
                        float* h_preds);
+/* Measurement aid: the slab schedule of tahoe_predict_host for `strategy` with the kernels left out --
+ * the same host-to-device and device-to-host copies on the same streams and nothing else -- so a
+ * caller can time what the copies alone cost (the bound of the end-to-end path).  h_scratch
+ * receives num_rows floats of unspecified content. */
+int tahoe_host_copy_baseline(tahoe_forest_t* f, int strategy, const float* h_data, size_t num_rows,
+                             float* h_scratch);
 
 /* TAHOE_OK if `strategy` can run this forest on `num_rows` rows, else
  * TAHOE_ERR_NOT_APPLICABLE (harness gates, BaseTahoeTest.h:657-679). */
@@ -160,6 +183,22 @@ int tahoe_last_launch_count(const tahoe_forest_t* f);
  * of predicts covered since profiling was switched on. */
 int tahoe_set_profiling(tahoe_forest_t* f, int on);
 int tahoe_profile_read(tahoe_forest_t* f, double* quantize_ms, double* traverse_ms, int* count);
+
+/* ---- roofline denominators --------------------------------------------------------------
+ * Read-bandwidth microbenchmarks on the current device (CUDA events, best of 5): conflict-free
+ * shared-memory LDS.32 stream, random shared-memory word loads, L2-resident streaming read (32 MB
+ * buffer, 16-byte loads) and L2-resident 32-byte sector gathers.  The reference's counterpart is
+ * its copy of the CUDA sample bandwidthTest (bandwidthTest.h:110 runTest, main.cu:8-15). */
+typedef struct {
+  double smem_read_gbs;
+  double smem_random_word_loads_per_s;
+  double l2_read_gbs;
+  double l2_sector_gathers_per_s;
+  int sm_count;
+  int l2_bytes;
+  int persisting_l2_max_bytes;
+} tahoe_peaks_t;
+int tahoe_measure_peaks(tahoe_peaks_t* out);
 
 /* ---- text loaders (host only) -------------------------------------------------------
  * generate_forest_from_file, BaseTahoeTest.h:267-352 / generate_data_from_file,

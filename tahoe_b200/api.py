@@ -63,6 +63,12 @@ class ForestInfo(C.Structure):
                 ("sparse_top_deep_walks", C.c_double)]
 
 
+class Peaks(C.Structure):
+    _fields_ = [("smem_read_gbs", C.c_double), ("smem_random_word_loads_per_s", C.c_double),
+                ("l2_read_gbs", C.c_double), ("l2_sector_gathers_per_s", C.c_double),
+                ("sm_count", C.c_int), ("l2_bytes", C.c_int), ("persisting_l2_max_bytes", C.c_int)]
+
+
 _lib = None
 
 
@@ -82,7 +88,11 @@ def lib() -> C.CDLL:
     L.tahoe_forest_destroy.restype = None
     L.tahoe_forest_info.argtypes = [vp, C.POINTER(ForestInfo)]
     L.tahoe_predict.argtypes = [vp, C.c_int, vp, sz, vp, vp, vp]
+    L.tahoe_predict_to.argtypes = [vp, C.c_int, vp, sz, vp, vp, vp, vp]
+    L.tahoe_enable_peer_access.argtypes = [C.c_int]
+    L.tahoe_measure_peaks.argtypes = [C.POINTER(Peaks)]
     L.tahoe_predict_host.argtypes = [vp, C.c_int, vp, sz, vp]
+    L.tahoe_host_copy_baseline.argtypes = [vp, C.c_int, vp, sz, vp]
     L.tahoe_strategy_applicable.argtypes = [vp, C.c_int, sz]
     L.tahoe_select_strategy.argtypes = [vp, sz, C.POINTER(C.c_double)]
     L.tahoe_last_launch_count.argtypes = [vp]
@@ -191,26 +201,65 @@ class Forest:
         s = lib().tahoe_select_strategy(self._h, rows, t)
         return s, list(t)
 
+    def _check_device_args(self, data, preds, leaf_ids):
+        """The C ABI takes bare pointers: a wrong dtype, stride or length is an out-of-bounds access."""
+        import torch
+        rows = int(data.shape[0])
+        if not (data.is_cuda and data.dtype == torch.float32 and data.is_contiguous() and data.dim() == 2
+                and data.shape[1] == self.num_cols):
+            raise ValueError(f"data must be a contiguous float32 CUDA tensor of shape (rows, {self.num_cols})")
+        if preds is not None and not (preds.is_cuda and preds.dtype == torch.float32 and preds.is_contiguous()
+                                      and preds.numel() >= rows):
+            raise ValueError("preds must be a contiguous float32 CUDA tensor of at least `rows` elements")
+        if leaf_ids is not None and not (leaf_ids.is_cuda and leaf_ids.dtype == torch.int32
+                                         and leaf_ids.is_contiguous()
+                                         and leaf_ids.numel() >= rows * self.num_trees):
+            raise ValueError("leaf_ids must be a contiguous int32 CUDA tensor of rows x num_trees elements")
+        return rows
+
     def predict(self, data, preds=None, *, strategy: int = AUTO, leaf_ids=None, stream=None):
         """data / preds / leaf_ids: torch CUDA tensors (float32 [R,C], float32 [R], int32 [R,T])."""
         import torch
-        rows = int(data.shape[0])
-        assert data.is_cuda and data.dtype == torch.float32 and data.is_contiguous()
-        assert data.shape[1] == self.num_cols
+        rows = self._check_device_args(data, preds, leaf_ids)
         if preds is None:
             preds = torch.empty(rows, dtype=torch.float32, device=data.device)
         _check(lib().tahoe_predict(self._h, strategy, _devptr(data), rows, _devptr(preds),
                                    _devptr(leaf_ids), _stream_ptr(stream)))
         return preds
 
-    def predict_host(self, data: np.ndarray, preds: np.ndarray | None = None, *, strategy: int = AUTO):
-        """Host buffers in, host buffers out (numpy or pinned torch CPU tensors)."""
+    def predict_to(self, data, out, *, partial=None, strategy: int = AUTO, leaf_ids=None, stream=None):
+        """tahoe_predict_to: final scores go to `out` (write-only: may be a tensor that lives on ANOTHER
+        GPU, mapped through CUDA IPC -- the fused gather of the multi-GPU path); `partial` is local
+        scratch for the partial sums between forest chunks (None: owned by the handle)."""
+        rows = self._check_device_args(data, partial, leaf_ids)
+        import torch
+        if not (out.is_cuda and out.dtype == torch.float32 and out.is_contiguous() and out.numel() >= rows):
+            raise ValueError("out must be a contiguous float32 CUDA tensor of at least `rows` elements")
+        _check(lib().tahoe_predict_to(self._h, strategy, _devptr(data), rows, _devptr(out), _devptr(partial),
+                                      _devptr(leaf_ids), _stream_ptr(stream)))
+        return out
+
+    def predict_host(self, data, preds=None, *, strategy: int = AUTO, copy_only: bool = False):
+        """Host buffers in, host buffers out (numpy or pinned torch CPU tensors).  copy_only: the same
+        slab copies without the kernels (tahoe_host_copy_baseline; preds then holds garbage)."""
+        def host_view(x, what, shape_ok):
+            if isinstance(x, np.ndarray):
+                ok = x.dtype == np.float32 and x.flags["C_CONTIGUOUS"]
+                ptr = x.ctypes.data
+            else:
+                import torch
+                ok = (not x.is_cuda) and x.dtype == torch.float32 and x.is_contiguous()
+                ptr = x.data_ptr()
+            if not (ok and shape_ok(x)):
+                raise ValueError(f"{what}: need a C-contiguous float32 host array of the right shape")
+            return ptr
         rows = int(data.shape[0])
+        dp = host_view(data, "data", lambda x: len(x.shape) == 2 and x.shape[1] == self.num_cols)
         if preds is None:
             preds = np.empty(rows, dtype=np.float32)
-        dp = data.ctypes.data if isinstance(data, np.ndarray) else data.data_ptr()
-        pp = preds.ctypes.data if isinstance(preds, np.ndarray) else preds.data_ptr()
-        _check(lib().tahoe_predict_host(self._h, strategy, C.c_void_p(dp), rows, C.c_void_p(pp)))
+        pp = host_view(preds, "preds", lambda x: int(np.prod(x.shape)) >= rows)
+        fn = lib().tahoe_host_copy_baseline if copy_only else lib().tahoe_predict_host
+        _check(fn(self._h, strategy, C.c_void_p(dp), rows, C.c_void_p(pp)))
         return preds
 
     def set_profiling(self, on: bool):
@@ -231,6 +280,18 @@ class Forest:
         buf = np.empty(n.value // np.dtype(dtype).itemsize, dtype=dtype)
         _check(lib().tahoe_forest_export(self._h, which, buf.ctypes.data_as(C.c_void_p), C.byref(n)))
         return buf
+
+
+def measure_peaks() -> dict:
+    """L2 / shared-memory read-bandwidth microbenchmarks on the current device (tahoe_measure_peaks)."""
+    pk = Peaks()
+    _check(lib().tahoe_measure_peaks(C.byref(pk)))
+    return {k: getattr(pk, k) for k, _ in Peaks._fields_}
+
+
+def enable_peer_access(peer_device: int) -> None:
+    """Kernels on the current device may store into `peer_device`'s memory (tahoe_predict_to's d_out)."""
+    _check(lib().tahoe_enable_peer_access(int(peer_device)))
 
 
 def load_model_text(path: str, binary: bool = False):

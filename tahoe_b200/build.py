@@ -15,7 +15,7 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "lib", "libtahoe_b200.so")
 CLI = os.path.join(HERE, "bin", "Tahoe")
 SOURCES = ["abi.cu", "packer.cu", "textio.cu", "gen.cu", "kernels_direct.cu",
-           "kernels_shared_data.cu", "kernels_smem.cu", "kernels_sparse_smem.cu"]
+           "kernels_shared_data.cu", "kernels_smem.cu", "kernels_sparse_smem.cu", "peaks.cu"]
 MAX_DEPTH = 14
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-O2,-fno-fast-math", "--fmad=true", "-prec-div=true",

@@ -22,6 +22,8 @@ static void free_workspace(Workspace& w) {
   if (w.tile_flags) cudaFree(w.tile_flags);
   if (w.slab_data) cudaFree(w.slab_data);
   if (w.slab_preds) cudaFree(w.slab_preds);
+  if (w.partial) cudaFree(w.partial);
+  if (w.done) cudaEventDestroy(w.done);
   if (w.stream) cudaStreamDestroy(w.stream);
   w = Workspace{};
 }
@@ -171,12 +173,24 @@ static int predict_impl(tahoe_forest* f, int strategy, const PredictArgs& a) {
   int rc = applicable(f, strategy, a.rows);
   if (rc == TAHOE_ERR_INVALID) { set_error("unknown strategy id"); return rc; }
   if (rc != TAHOE_OK) { set_error("Strategy is not suitable for this case."); return rc; }
+  // profiling: the single-kernel strategies are bracketed here (no preparation pass: ev[0] == ev[1]);
+  // the shared-memory-forest launchers record around their two kernels themselves
+  cudaEvent_t* ev = nullptr;
+  const bool one_kernel = strategy == TAHOE_STRATEGY_DIRECT || strategy == TAHOE_STRATEGY_SHARED_DATA_PER_THREAD ||
+                          strategy == TAHOE_STRATEGY_SHARED_DATA;
+  if (one_kernel && a.rows && f->profile && a.ws == &f->ws[0] && f->prof_count < kProfRing) {
+    ev = &f->prof_events[(size_t)f->prof_count * 3];
+    ++f->prof_count;
+    TAHOE_CUDA(cudaEventRecord(ev[0], a.stream));
+    TAHOE_CUDA(cudaEventRecord(ev[1], a.stream));
+  }
   switch (strategy) {
     case TAHOE_STRATEGY_DIRECT: rc = launch_direct(f, a, false, &launches); break;
     case TAHOE_STRATEGY_SHARED_DATA_PER_THREAD: rc = launch_direct(f, a, true, &launches); break;
     case TAHOE_STRATEGY_SHARED_DATA: rc = launch_shared_data(f, a, &launches); break;
     default: rc = (f->sparse && !f->sp_use_qt) ? launch_sparse_smem(f, a, &launches) : launch_smem_forest(f, a, &launches); break;
   }
+  if (ev) TAHOE_CUDA(cudaEventRecord(ev[2], a.stream));
   f->last_launches = launches;
   return rc;
 }
@@ -268,16 +282,66 @@ int tahoe_forest_info(const tahoe_forest_t* f, tahoe_forest_info_t* info) {
   return TAHOE_OK;
 }
 
+// tahoe_predict / tahoe_predict_to share the handle's workspace ws[0] (rank tiles, tile flags, partial sums).
+// Two calls on DIFFERENT streams must not overlap on it: the second stream waits for the event the first
+// call recorded (stream-ordered, no host sync).  Calls on one stream are ordered by the stream itself.
+static int predict_on_ws0(tahoe_forest* f, int strategy, PredictArgs a) {
+  Workspace& w = f->ws[0];
+  if (f->device >= 0) {
+    if (!w.done) TAHOE_CUDA(cudaEventCreateWithFlags(&w.done, cudaEventDisableTiming));
+    if (w.used && w.last_stream != a.stream) TAHOE_CUDA(cudaStreamWaitEvent(a.stream, w.done, 0));
+  }
+  const int rc = predict_impl(f, strategy, a);
+  if (f->device >= 0 && rc == TAHOE_OK) {
+    TAHOE_CUDA(cudaEventRecord(w.done, a.stream));
+    w.used = true; w.last_stream = a.stream;
+  }
+  return rc;
+}
+
 int tahoe_predict(tahoe_forest_t* f, int strategy, const float* d_data, size_t num_rows,
                   float* d_preds, int32_t* d_leaf_ids, void* stream) {
   if (!f || (num_rows && (!d_data || !d_preds))) { set_error("null argument"); return TAHOE_ERR_INVALID; }
-  PredictArgs a{d_data, num_rows, d_preds, d_leaf_ids, (cudaStream_t)stream, &f->ws[0]};
-  return predict_impl(f, strategy, a);
+  PredictArgs a{d_data, num_rows, d_preds, d_preds, d_leaf_ids, (cudaStream_t)stream, &f->ws[0]};
+  return predict_on_ws0(f, strategy, a);
 }
 
-int tahoe_predict_host(tahoe_forest_t* f, int strategy, const float* h_data, size_t num_rows,
-                       float* h_preds) {
+int tahoe_predict_to(tahoe_forest_t* f, int strategy, const float* d_data, size_t num_rows,
+                     float* d_out, float* d_partial, int32_t* d_leaf_ids, void* stream) {
+  if (!f || (num_rows && (!d_data || !d_out))) { set_error("null argument"); return TAHOE_ERR_INVALID; }
+  if (!d_partial && num_rows && f->device >= 0) {   // handle-owned scratch, grow-only
+    Workspace& w = f->ws[0];
+    if (w.cap_partial < num_rows) {
+      // (a grow while an earlier call still runs on another stream: wait for it before freeing)
+      if (w.used) TAHOE_CUDA(cudaEventSynchronize(w.done));
+      if (w.partial) cudaFree(w.partial);
+      w.partial = nullptr; w.cap_partial = 0;
+      TAHOE_CUDA(cudaMalloc((void**)&w.partial, num_rows * sizeof(float)));
+      w.cap_partial = num_rows;
+    }
+    d_partial = w.partial;
+  }
+  PredictArgs a{d_data, num_rows, d_partial, d_out, d_leaf_ids, (cudaStream_t)stream, &f->ws[0]};
+  return predict_on_ws0(f, strategy, a);
+}
+
+int tahoe_enable_peer_access(int peer_device) {
+  int cur = 0;
+  TAHOE_CUDA(cudaGetDevice(&cur));
+  if (cur == peer_device) return TAHOE_OK;
+  int can = 0;
+  TAHOE_CUDA(cudaDeviceCanAccessPeer(&can, cur, peer_device));
+  if (!can) { set_error("the current device cannot access the peer device's memory"); return TAHOE_ERR_NOT_APPLICABLE; }
+  const cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return TAHOE_OK; }
+  if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceEnablePeerAccess");
+  return TAHOE_OK;
+}
+
+static int predict_host_impl(tahoe_forest_t* f, int strategy, const float* h_data, size_t num_rows,
+                             float* h_preds, bool copy_only) {
   if (!f || (num_rows && (!h_data || !h_preds))) { set_error("null argument"); return TAHOE_ERR_INVALID; }
+  if (f->device < 0) { set_error("no CUDA device: this handle was packed on a GPU-less host and cannot predict"); return TAHOE_ERR_CUDA; }
   if (num_rows == 0) return TAHOE_OK;
   const int C = f->params.num_cols;
   if (strategy == TAHOE_STRATEGY_AUTO) strategy = select_strategy(f, num_rows, nullptr);
@@ -286,31 +350,48 @@ int tahoe_predict_host(tahoe_forest_t* f, int strategy, const float* h_data, siz
   // of tiles (no ragged last round per chunk pass), growing from 2 waves by 1.5x up to 24: the first
   // copy, which nothing can hide, is short; a slab may only grow as fast as the kernels before it run
   // ahead of the copy engine (the copy of config 2's rows takes 0.8 of their predict); and the later
-  // kernels are long enough to amortise their chunk passes.  TAHOE_HOST_SLAB="first,growth%,cap" (waves).
+  // kernels are long enough to amortise their chunk passes.  TAHOE_HOST_SLAB="first,growth%,cap" (waves),
+  // read when the handle was created.  Other strategies: slabs of about an eighth of the batch, sized in
+  // BYTES (<= 256 MB of rows per slot, whatever the row width).  No slab is larger than the batch.
+  const size_t rows32 = (num_rows + 31) / 32 * 32;
+  const size_t row_bytes = (size_t)C * sizeof(float);
   size_t slab = ((num_rows + 7) / 8 + 31) / 32 * 32;
-  slab = std::min<size_t>(std::max<size_t>(slab, 65536), 1u << 20);
+  slab = std::max<size_t>(slab, std::min<size_t>(65536, (size_t)(32u << 20) / row_bytes / 32 * 32));
+  slab = std::min<size_t>(slab, std::max<size_t>((size_t)(256u << 20) / row_bytes / 32 * 32, 32));
   size_t wave = 0;
-  int slab_first = 2, slab_growth = 150, slab_cap = 24;
+  const int slab_first = f->tune.slab_first, slab_growth = f->tune.slab_growth, slab_cap = f->tune.slab_cap;
   if ((strategy == TAHOE_STRATEGY_SHARED_FOREST || strategy == TAHOE_STRATEGY_SPLIT_SHARED_FOREST) &&
       (f->quant || (f->qt && f->sp_use_qt)) && f->trees_per_chunk > 0) {
     const bool paired = f->sparse && C > kStagedMaxCols && f->warps > 8;
     wave = (size_t)f->sm_count * (size_t)(paired ? f->warps / 2 : f->warps) * 32;
-    if (const char* e = std::getenv("TAHOE_HOST_SLAB")) std::sscanf(e, "%d,%d,%d", &slab_first, &slab_growth, &slab_cap);
-    slab_first = std::max(slab_first, 1); slab_cap = std::max(slab_cap, slab_first); slab_growth = std::max(slab_growth, 100);
     slab = (size_t)slab_cap * wave;
   }
+  slab = std::max<size_t>(32, std::min(slab, rows32));
+  // an error leaves copies of earlier slabs in flight INTO h_preds: drain the slot streams before returning
+  auto fail = [&](int rc) {
+    for (int s = 1; s <= kHostSlots; ++s)
+      if (f->ws[s].stream) cudaStreamSynchronize(f->ws[s].stream);
+    cudaGetLastError();
+    return rc;
+  };
+#define TAHOE_CUDA_SLAB(call)                                                   \
+  do {                                                                          \
+    cudaError_t e__ = (call);                                                   \
+    if (e__ != cudaSuccess) return fail(::tahoe::cuda_fail(e__, #call));        \
+  } while (0)
   int total_launches = 0;
   size_t done = 0;
   double slab_waves = slab_first;
   for (int i = 0; done < num_rows; ++i) {
     Workspace& w = f->ws[1 + i % kHostSlots];
-    if (!w.stream) TAHOE_CUDA(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
+    if (!w.stream) TAHOE_CUDA_SLAB(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
     if (w.cap_slab_rows < slab) {
+      TAHOE_CUDA_SLAB(cudaStreamSynchronize(w.stream));
       if (w.slab_data) cudaFree(w.slab_data);
       if (w.slab_preds) cudaFree(w.slab_preds);
       w.slab_data = nullptr; w.slab_preds = nullptr; w.cap_slab_rows = 0;
-      TAHOE_CUDA(cudaMalloc((void**)&w.slab_data, slab * (size_t)C * sizeof(float)));
-      TAHOE_CUDA(cudaMalloc((void**)&w.slab_preds, slab * sizeof(float)));
+      TAHOE_CUDA_SLAB(cudaMalloc((void**)&w.slab_data, slab * row_bytes));
+      TAHOE_CUDA_SLAB(cudaMalloc((void**)&w.slab_preds, slab * sizeof(float)));
       w.cap_slab_rows = slab;
     }
     size_t this_slab = slab;
@@ -319,20 +400,33 @@ int tahoe_predict_host(tahoe_forest_t* f, int strategy, const float* h_data, siz
       slab_waves = std::min((double)slab_cap, slab_waves * slab_growth / 100.0);
     }
     const size_t n = std::min(this_slab, num_rows - done);
-    TAHOE_CUDA(cudaMemcpyAsync(w.slab_data, h_data + done * (size_t)C, n * (size_t)C * sizeof(float),
-                               cudaMemcpyHostToDevice, w.stream));
-    PredictArgs a{w.slab_data, n, w.slab_preds, nullptr, w.stream, &w};
-    int rc = predict_impl(f, strategy, a);
-    if (rc) return rc;
-    total_launches += f->last_launches;
-    TAHOE_CUDA(cudaMemcpyAsync(h_preds + done, w.slab_preds, n * sizeof(float), cudaMemcpyDeviceToHost,
-                               w.stream));
+    TAHOE_CUDA_SLAB(cudaMemcpyAsync(w.slab_data, h_data + done * (size_t)C, n * row_bytes,
+                                    cudaMemcpyHostToDevice, w.stream));
+    PredictArgs a{w.slab_data, n, w.slab_preds, w.slab_preds, nullptr, w.stream, &w};
+    if (!copy_only) {
+      int rc = predict_impl(f, strategy, a);
+      if (rc) return fail(rc);
+      total_launches += f->last_launches;
+    }
+    TAHOE_CUDA_SLAB(cudaMemcpyAsync(h_preds + done, w.slab_preds, n * sizeof(float), cudaMemcpyDeviceToHost,
+                                    w.stream));
     done += n;
   }
   for (int s = 1; s <= kHostSlots; ++s)
-    if (f->ws[s].stream) TAHOE_CUDA(cudaStreamSynchronize(f->ws[s].stream));
+    if (f->ws[s].stream) TAHOE_CUDA_SLAB(cudaStreamSynchronize(f->ws[s].stream));
+#undef TAHOE_CUDA_SLAB
   f->last_launches = total_launches;
   return TAHOE_OK;
+}
+
+int tahoe_predict_host(tahoe_forest_t* f, int strategy, const float* h_data, size_t num_rows,
+                       float* h_preds) {
+  return predict_host_impl(f, strategy, h_data, num_rows, h_preds, false);
+}
+
+int tahoe_host_copy_baseline(tahoe_forest_t* f, int strategy, const float* h_data, size_t num_rows,
+                             float* h_scratch) {
+  return predict_host_impl(f, strategy, h_data, num_rows, h_scratch, true);
 }
 
 int tahoe_strategy_applicable(const tahoe_forest_t* f, int strategy, size_t num_rows) {

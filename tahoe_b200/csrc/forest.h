@@ -94,7 +94,22 @@ struct Workspace {                     // per-stream scratch, grow-only (no per-
   float* slab_data = nullptr;          // tahoe_predict_host staging
   float* slab_preds = nullptr;
   size_t cap_slab_rows = 0;
+  float* partial = nullptr;            // tahoe_predict_to without caller scratch: partial sums between chunk passes
+  size_t cap_partial = 0;
+  cudaEvent_t done = nullptr;          // ws[0]: end of the last predict that used this scratch ...
+  cudaStream_t last_stream = nullptr;  // ... and the stream it ran on (a call on another stream waits for it)
+  bool used = false;
   cudaStream_t stream = nullptr;       // owned (predict_host only)
+};
+
+// Tuning knobs (measurement runs only): environment variables read ONCE, when the handle is created
+// (query_device) -- nothing on the predict path calls getenv.
+struct Tuning {
+  size_t row_batch_bytes = 0;          // TAHOE_ROW_BATCH_BYTES: k_smem_forest walks the rows in L2-sized batches
+  int sparse_grid = 0;                 // TAHOE_SPARSE_GRID: cap on k_sparse_smem's grid
+  int sparse_group = 3;                // TAHOE_SPARSE_GROUP: sequences per lane of k_sparse_smem
+  int direct_group = 0;                // TAHOE_DIRECT_GROUP: 4 = four walks per thread, 1 = one; 0 = by batch size
+  int slab_first = 2, slab_growth = 150, slab_cap = 24;   // TAHOE_HOST_SLAB="first,growth%,cap" (waves of tiles)
 };
 
 constexpr int kHostSlots = 3;
@@ -176,6 +191,7 @@ struct tahoe_forest {
   int32_t* d_qlut = nullptr;
 
   int device = 0, sm_count = 0, smem_optin = 0, l2_bytes = 0;
+  tahoe::Tuning tune;
   tahoe::Workspace ws[1 + tahoe::kHostSlots];  // [0] = tahoe_predict, [1..] = predict_host slabs
   int last_launches = 0;
 
@@ -209,7 +225,8 @@ double smem_tile_cost(int cols, bool staged, int trees_per_chunk, int depth);   
 struct PredictArgs {
   const float* data;
   size_t rows;
-  float* preds;
+  float* preds;        // partial sums between chunk passes (local memory; may be the same buffer as `out`)
+  float* out;          // final scores, written once and never read back: may be peer-mapped
   int32_t* leaf_ids;
   cudaStream_t stream;
   Workspace* ws;

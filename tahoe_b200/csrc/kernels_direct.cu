@@ -198,7 +198,7 @@ int launch_direct(tahoe_forest* f, const PredictArgs& a, bool rows_in_smem, int*
   p.sparse8 = f->d_sparse8;
   p.fid_bits = f->host.sparse_fid_bits;
   p.tree_offsets = f->d_tree_offsets;
-  p.preds = a.preds;
+  p.preds = a.out;     // one pass: the kernel's only store is the final score
   p.leaf_ids = a.leaf_ids;
   p.tf = Transform{f->params.output, (float)f->params.num_trees, f->params.threshold,
                    f->params.global_bias};
@@ -219,7 +219,7 @@ int launch_direct(tahoe_forest* f, const PredictArgs& a, bool rows_in_smem, int*
   };
   // few rows: not enough warps to hide the L2 round trips -> 4 walks per thread
   int group = a.rows <= (size_t)f->sm_count * 1024 ? 4 : 1;
-  if (const char* e = std::getenv("TAHOE_DIRECT_GROUP")) group = std::atoi(e) == 4 ? 4 : 1;
+  if (f->tune.direct_group) group = f->tune.direct_group == 4 ? 4 : 1;
   if (f->sparse && group == 1 && f->d_sparse8)   // full machine, 8-byte nodes when the fields fit
     return rows_in_smem ? go(k_sparse8<true>) : go(k_sparse8<false>);
   if (group == 4) {

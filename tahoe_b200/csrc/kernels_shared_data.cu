@@ -310,7 +310,7 @@ int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches) {
   SharedDataParams p{};
   p.data = a.data; p.rows = a.rows; p.cols = f->params.num_cols; p.num_trees = f->params.num_trees;
   p.tpad = f->host.tpad; p.depth = f->depth; p.missing = f->params.missing; p.inter = f->d_inter;
-  p.orig_ids = f->d_orig_ids; p.tree_order = f->d_tree_order; p.preds = a.preds;
+  p.orig_ids = f->d_orig_ids; p.tree_order = f->d_tree_order; p.preds = a.out;   // one pass: final scores only
   p.leaf_ids = a.leaf_ids;
   p.tf = Transform{f->params.output, (float)f->params.num_trees, f->params.threshold,
                    f->params.global_bias};

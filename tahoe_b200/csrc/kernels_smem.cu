@@ -193,18 +193,17 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.trees_per_chunk = f->trees_per_chunk; p.num_chunks = f->num_chunks;
   p.col_mask = f->col_mask; p.miss_code = f->miss_code;
   p.col_stride = f->tile_col_stride; p.slot_stride = f->tile_slot_stride; p.tile_region = f->tile_region;
-  p.preds = a.preds; p.leaf_ids = a.leaf_ids;
+  p.preds = a.preds; p.out = a.out; p.leaf_ids = a.leaf_ids;
   p.leaf_origin = f->d_leaf_origin;
   p.deep_blocks = f->d_sp_qblocks; p.block_offsets = f->d_sp_qblock_offsets; p.block_orig = f->d_sp_qblock_orig;
-  if (const char* e = std::getenv("TAHOE_QTOP_NODRAIN")) p.debug_no_drain = std::atoi(e);
   p.tf = Transform{f->params.output, (float)f->params.num_trees, f->params.threshold,
                    f->params.global_bias};
   // Row batches (tuning knob, off by default): walk the rows in batches whose rank tiles stay
   // L2-resident between chunk passes.  Measured on B200 (profiles/r01_row_batch.log): never a win --
   // the tile stream hides behind the traversal, and every batch pays a pipeline fill and drain.
   size_t batch_tiles = tiles;
-  if (const char* e = std::getenv("TAHOE_ROW_BATCH_BYTES")) {
-    const size_t budget = (size_t)std::atoll(e);
+  if (f->tune.row_batch_bytes) {
+    const size_t budget = f->tune.row_batch_bytes;
     const size_t wave = (size_t)f->sm_count * f->warps;
     const size_t fit = budget / ((size_t)p.cols * 128);
     if (budget && f->num_chunks > 1 && fit < tiles) batch_tiles = std::max<size_t>(wave, fit / wave * wave);
@@ -216,6 +215,7 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
     b.qtiles = p.qtiles + t0 * (size_t)p.cols * 32;
     b.tile_flags = p.tile_flags + t0;
     b.preds = p.preds + t0 * 32;
+    b.out = p.out + t0 * 32;
     if (p.leaf_ids) b.leaf_ids = p.leaf_ids + t0 * 32 * (size_t)p.num_trees;
     const unsigned grid = (unsigned)std::min<size_t>((size_t)f->sm_count,
                                                      (b.num_tiles + f->warps - 1) / f->warps);

@@ -169,7 +169,8 @@ k_smem_forest_deep(SmemParams p) {
     auto flush_out = [&]() {
       if (PAIR && half == 0 && out_have) {
         const float s = out_sum + *xch;
-        p.preds[out_row] = last ? apply_transform(s, p.tf) : s;
+        if (last) p.out[out_row] = apply_transform(s, p.tf);
+        else p.preds[out_row] = s;
         out_have = false;
       }
     };
@@ -224,7 +225,10 @@ k_smem_forest_deep(SmemParams p) {
       }
       const float s = acc_prev + dacc_prev;
       if (!PAIR) {
-        if (live_prev) p.preds[row_prev] = last ? apply_transform(s, p.tf) : s;
+        if (live_prev) {
+          if (last) p.out[row_prev] = apply_transform(s, p.tf);
+          else p.preds[row_prev] = s;
+        }
       } else if (half == 1) {
         *xch = s;                                // read by warp 0 after the pair's next barrier
       } else {
@@ -250,7 +254,7 @@ k_smem_forest_deep(SmemParams p) {
       const bool live = row < p.rows;
       cur_sl = sl0 + (uint32_t)buf * p.slot_stride;
       const uint32_t park_tag = (uint32_t)buf << 31;
-      const bool park = live && !p.debug_no_drain;   // (TAHOE_QTOP_NODRAIN: timing experiments, wrong scores)
+      const bool park = live;
 
       for (int t = half * G; t < ntrees; t += kSplit * G) {
         // room for G more parked walks in every lane's ring (rarely taken)

@@ -26,7 +26,9 @@ struct SmemParams {
   //           (column field at bit 7: for forests whose rank + column bits leave no room for the wide field)
   uint32_t col_stride, slot_stride;
   uint32_t tile_region;     // bytes of the tile region (the forest chunk follows it)
-  float* preds;
+  float* preds;             // partial sums between chunk passes (local scratch; may alias `out`)
+  float* out;               // final scores: written once, by the last chunk pass -- may be a PEER-mapped buffer
+                            // (rank g's slice of rank 0's gathered output): never read back
   int32_t* leaf_ids;
   const int32_t* leaf_origin;  // [T][2^d]
   Transform tf;
@@ -35,7 +37,6 @@ struct SmemParams {
   const uint4* deep_blocks;      // [blocks + 1][2] two-level blocks {root, left, right, -} x {rank word | leaf value, leaf<<31 | block delta}
   const int64_t* block_offsets;  // [T+1] first block of every tree
   const int32_t* block_orig;     // [blocks + 1][3] caller's node index of root / left / right
-  int debug_no_drain;          // TAHOE_QTOP_NODRAIN=1: skip the deep walks (timing experiments; scores are wrong)
 };
 
 constexpr uint32_t kContMask = 0xFFC00000u;   // packer.cu: marker = kContMask | node index relative to the chunk's first node
@@ -125,13 +126,26 @@ __global__ void __launch_bounds__(kSmemMaxThreads, 1) k_smem_forest(SmemParams p
   uint32_t tile_phase = 0;   // bit b = parity to wait for on this warp's buffer b
   uint32_t chunk_phase = 0;
 
-  // TMA path: bring tile `tile` into this warp's buffer `b`, one 128-byte bulk copy per column row
+  // TMA path: bring tile `tile` into this warp's buffer `b`.  Slot-major region (col_stride == 128):
+  // the buffer is the tile's own [col][32 lanes] image, so ONE bulk copy of cols*128 bytes brings it in
+  // (one UBLKCP and one proxy fence per tile instead of one per column; the per-column form made the
+  // TMA path lose to register staging on 28-column tiles, profiles/r01_smem_plans.log).  Column-major
+  // region: the slots of a column are interleaved, one 128-byte copy per column row.
+  const bool tile_contiguous = p.col_stride == 128u;
   auto load_tile = [&](size_t tile, int b) {
     const uint32_t bar = bar_tile0 + b * 8;
-    if (lane == 0) mbar_expect_tx(bar, tile_bytes);
-    __syncwarp();
     const uint32_t slot_off = (uint32_t)(warp * kBufs + b) * p.slot_stride;
     const uint32_t* src = p.qtiles + tile * (size_t)p.cols * 32;
+    if (tile_contiguous) {
+      if (lane == 0) {
+        fence_proxy_async();
+        mbar_expect_tx(bar, tile_bytes);
+        bulk_g2s(s_base + slot_off, src, tile_bytes, bar);
+      }
+      return;
+    }
+    if (lane == 0) mbar_expect_tx(bar, tile_bytes);
+    __syncwarp();
     for (int c = lane; c < p.cols; c += 32) {
       fence_proxy_async();
       bulk_g2s(s_base + c * p.col_stride + slot_off, src + c * 32, 128u, bar);
@@ -232,7 +246,10 @@ __global__ void __launch_bounds__(kSmemMaxThreads, 1) k_smem_forest(SmemParams p
                 __ldg(p.leaf_origin + (size_t)(tree0 + t + g) * L + ((a[g] - tree_abs - g * W * 4u) / 4 - L));
         }
       }
-      if (live) p.preds[row] = last ? apply_transform(acc, p.tf) : acc;
+      if (live) {
+        if (last) p.out[row] = apply_transform(acc, p.tf);
+        else p.preds[row] = acc;
+      }
       if (!STAGED) buf ^= 1;
     }
   }

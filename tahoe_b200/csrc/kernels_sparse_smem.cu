@@ -41,7 +41,8 @@ struct SparseSmemParams {
   const int32_t* orig;         // breadth-first index -> caller's node index
   int num_trees, tpc, num_chunks, cut, fid_bits;
   float missing;
-  float* preds;
+  float* preds;                // partial sums between chunk passes
+  float* out;                  // final scores (last chunk pass); may be peer-mapped
   int32_t* leaf_ids;
   Transform tf;
 };
@@ -294,7 +295,10 @@ __global__ void __launch_bounds__(kSparseWarps * 32, 1) k_sparse_smem(SparseSmem
 #pragma unroll
       for (int g = 0; g < G; ++g) acc += accg[g];
       acc += acc_deep;
-      if (live) p.preds[row] = last ? apply_transform(acc, p.tf) : acc;
+      if (live) {
+        if (last) p.out[row] = apply_transform(acc, p.tf);
+        else p.preds[row] = acc;
+      }
     }
   }
 }
@@ -329,10 +333,10 @@ int launch_sparse_smem(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.top = f->d_sp_top; p.full = f->d_sp_full; p.tree_offsets = f->d_tree_offsets; p.orig = f->d_sp_orig;
   p.num_trees = f->params.num_trees; p.tpc = f->sp_tpc; p.num_chunks = f->sp_chunks; p.cut = f->sp_cut;
   p.fid_bits = f->host.sparse_fid_bits; p.missing = f->params.missing;
-  p.preds = a.preds; p.leaf_ids = a.leaf_ids;
+  p.preds = a.preds; p.out = a.out; p.leaf_ids = a.leaf_ids;
   p.tf = Transform{f->params.output, (float)f->params.num_trees, f->params.threshold, f->params.global_bias};
   unsigned grid = (unsigned)std::min<size_t>((size_t)f->sm_count, (tiles + kSparseWarps - 1) / kSparseWarps);
-  if (const char* e = std::getenv("TAHOE_SPARSE_GRID")) grid = std::max(1u, std::min(grid, (unsigned)std::atoi(e)));
+  if (f->tune.sparse_grid > 0) grid = std::max(1u, std::min(grid, (unsigned)f->tune.sparse_grid));
   auto go = [&](auto kern) -> int {
     TAHOE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->sp_smem));
     kern<<<grid, kSparseWarps * 32, f->sp_smem, a.stream>>>(p);
@@ -340,8 +344,7 @@ int launch_sparse_smem(tahoe_forest* f, const PredictArgs& a, int* launches) {
     ++*launches;
     return TAHOE_OK;
   };
-  int group = 3;   // measured on config 4: 28.7 / 24.6 / 23.4 / 24.5 ms for 1 / 2 / 3 / 4 sequences per lane
-  if (const char* e = std::getenv("TAHOE_SPARSE_GROUP")) group = std::atoi(e);
+  const int group = f->tune.sparse_group;   // default 3: measured on config 4: 28.7 / 24.6 / 23.4 / 24.5 ms for 1 / 2 / 3 / 4 sequences per lane
   if (a.leaf_ids) rc = go(k_sparse_smem<true, 2>);
   else if (group == 4) rc = go(k_sparse_smem<false, 4>);
   else rc = group == 3 ? go(k_sparse_smem<false, 3>) : (group == 1 ? go(k_sparse_smem<false, 1>) : go(k_sparse_smem<false, 2>));

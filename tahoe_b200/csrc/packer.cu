@@ -922,7 +922,19 @@ static double plan_chunks_for(tahoe_forest* f, int depth, bool deep) {
   return best;
 }
 
+static void read_tuning(Tuning& t) {
+  if (const char* e = std::getenv("TAHOE_ROW_BATCH_BYTES")) t.row_batch_bytes = (size_t)std::atoll(e);
+  if (const char* e = std::getenv("TAHOE_SPARSE_GRID")) t.sparse_grid = std::atoi(e);
+  if (const char* e = std::getenv("TAHOE_SPARSE_GROUP")) t.sparse_group = std::atoi(e);
+  if (const char* e = std::getenv("TAHOE_DIRECT_GROUP")) t.direct_group = std::atoi(e);
+  if (const char* e = std::getenv("TAHOE_HOST_SLAB")) std::sscanf(e, "%d,%d,%d", &t.slab_first, &t.slab_growth, &t.slab_cap);
+  t.slab_first = std::max(t.slab_first, 1);
+  t.slab_cap = std::max(t.slab_cap, t.slab_first);
+  t.slab_growth = std::max(t.slab_growth, 100);
+}
+
 int query_device(tahoe_forest* f) {
+  read_tuning(f->tune);
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
     // No GPU (authoring container): the forest can be packed and inspected, with the plan a B200

@@ -1,8 +1,13 @@
-// peaks.cu -- measured read bandwidth of shared memory and L2 on this GPU (roofline denominators the
-// driver's MEASURED_PEAKS.json does not hold).  nvcc -O3 -gencode arch=compute_100a,code=sm_100a
-// tools/microbench/peaks.cu -o /tmp/peaks && /tmp/peaks   -> one JSON line.
+// peaks.cu -- tahoe_measure_peaks: measured read bandwidth of shared memory and L2 on the current GPU, the
+// roofline denominators SURVEY 8(d) asks for and the driver's MEASURED_PEAKS.json does not hold (it has
+// HBM and bf16 only).  bench.py calls it in the same run as the kernels it rates; `python -m
+// tahoe_b200.peaks` prints the same numbers as one JSON line.  CUDA events, best of 5.
 #include <cstdio>
 #include <cuda_runtime.h>
+
+#include "forest.h"
+
+namespace {
 
 // conflict-free LDS.32 stream: every lane reads bank = lane, 8 independent loads in flight
 __global__ void __launch_bounds__(1024, 1) k_smem(unsigned* out, int iters) {
@@ -77,32 +82,40 @@ static float time_ms(F f, int reps = 5) {
   return best;
 }
 
-int main() {
+}  // namespace
+
+extern "C" int tahoe_measure_peaks(tahoe_peaks_t* out_peaks) {
+  using namespace tahoe;
+  if (!out_peaks) { set_error("null argument"); return TAHOE_ERR_INVALID; }
+  int dev = 0;
+  TAHOE_CUDA(cudaGetDevice(&dev));
   cudaDeviceProp prop;
-  cudaGetDeviceProperties(&prop, 0);
+  TAHOE_CUDA(cudaGetDeviceProperties(&prop, dev));
   const int sms = prop.multiProcessorCount;
-  unsigned* out;
-  cudaMalloc(&out, 64);
+  unsigned* out = nullptr;
+  uint4* buf = nullptr;
+  TAHOE_CUDA(cudaMalloc(&out, 64));
   const size_t smem = 48 * 1024 * 4;
+  const size_t bytes = 32u << 20;   // 32 MB: L2-resident
+  if (cudaMalloc(&buf, bytes) != cudaSuccess) { cudaFree(out); return cuda_fail(cudaGetLastError(), "cudaMalloc"); }
+  cudaMemset(buf, 1, bytes);
   cudaFuncSetAttribute(k_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   cudaFuncSetAttribute(k_smem_random, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   const int iters = 5000;
   float ms = time_ms([&] { k_smem<<<sms, 1024, smem>>>(out, iters); });
-  const double smem_gbs = (double)sms * 1024 * iters * 32 * 4 / (ms * 1e-3) / 1e9;
+  out_peaks->smem_read_gbs = (double)sms * 1024 * iters * 32 * 4 / (ms * 1e-3) / 1e9;
   ms = time_ms([&] { k_smem_random<<<sms, 1024, smem>>>(out, iters * 4); });
-  const double smem_rand_glds = (double)sms * 1024 * iters * 4 * 4 / (ms * 1e-3) / 1e9;   // G lane-loads/s
-  const size_t bytes = 32u << 20;   // 32 MB: L2-resident
-  uint4* buf;
-  cudaMalloc(&buf, bytes);
-  cudaMemset(buf, 1, bytes);
+  out_peaks->smem_random_word_loads_per_s = (double)sms * 1024 * iters * 4 * 4 / (ms * 1e-3);
   const int reps = 20;
   ms = time_ms([&] { k_l2<<<sms * 8, 512>>>(buf, bytes / 16, out, reps); });
-  const double l2_gbs = (double)bytes * reps / (ms * 1e-3) / 1e9;
+  out_peaks->l2_read_gbs = (double)bytes * reps / (ms * 1e-3) / 1e9;
   const int giters = 2000;
   ms = time_ms([&] { k_l2_gather<<<sms * 8, 256>>>((const uint2*)buf, (bytes / 32) - 1, out, giters); });
-  const double gathers = (double)sms * 8 * 256 * giters / (ms * 1e-3);
-  printf("{\"gpu\": \"%s\", \"sms\": %d, \"smem_read_gbs\": %.1f, \"smem_random_word_gloads_per_s\": %.1f, "
-         "\"l2_read_gbs\": %.1f, \"l2_sector_gathers_per_s\": %.3e, \"l2_sector_gather_gbs\": %.1f}\n",
-         prop.name, sms, smem_gbs, smem_rand_glds, l2_gbs, gathers, gathers * 32 / 1e9);
-  return 0;
+  out_peaks->l2_sector_gathers_per_s = (double)sms * 8 * 256 * giters / (ms * 1e-3);
+  out_peaks->sm_count = sms;
+  out_peaks->l2_bytes = prop.l2CacheSize;
+  out_peaks->persisting_l2_max_bytes = prop.persistingL2CacheMaxSize;
+  cudaFree(buf); cudaFree(out);
+  TAHOE_CUDA(cudaGetLastError());
+  return TAHOE_OK;
 }

@@ -73,15 +73,16 @@ class ShardedForest:
 
 
 class PeerGather:
-    """Gather of the ranks' score slices WITHOUT a collective: `dst` owns one device
-    buffer for the whole batch, every other rank maps it through CUDA IPC once (the handle travels as
-    a pickled object over the process group -- gloo is enough) and then writes its slice with a plain
-    device-to-device copy over NVLink / NVSwitch.  Per predict: one copy of 4 bytes per row per rank
-    on the rank's own stream; the only synchronisation is the barrier the caller already has.
+    """Gather of the ranks' score slices WITHOUT a collective and WITHOUT a copy: `dst`
+    owns one device buffer for the whole batch, every other rank maps it through CUDA IPC once (the
+    handle travels as a pickled object over the process group -- gloo is enough), and
+    `tahoe_predict_to` makes the kernels' last-chunk epilogue store each final score straight into
+    that buffer over NVLink / NVSwitch (4 bytes per row, posted writes, never read back).  The partial
+    sums the multi-pass strategies carry between forest chunks stay in a local scratch.  The only
+    synchronisation is the barrier the caller already has.
 
         pg = PeerGather(total_rows)                  # once
-        forest.predict(x_local, pg.local)            # kernels write this rank's slice buffer
-        pg.push()                                    # slice -> dst's buffer (async, current stream)
+        pg.predict(forest, x_local)                  # final scores land in dst's buffer, at this rank's rows
         torch.cuda.synchronize(); dist.barrier()     # dst may now read pg.full
     """
 
@@ -104,13 +105,12 @@ class PeerGather:
             if self.rank != dst:
                 rebuild, args = box[0]
                 self.full = rebuild(*args)             # dst's memory, mapped into this process
-        # the kernels read their partial sums back between forest chunks: they write a LOCAL slice
-        # (on dst: a view of the gathered buffer itself), pushed once per predict
-        if self.rank == dst:
-            self.local = self.full[self.lo:self.hi]
-        else:
-            self.local = torch.empty(self.hi - self.lo, dtype=torch.float32, device=dev)
+        if self.full.device != dev:                    # our kernels will store into dst's memory
+            from . import api
+            api.enable_peer_access(self.full.device.index)
+        self.out = self.full[self.lo:self.hi]          # this rank's rows of the gathered buffer (peer memory off dst)
+        self.partial = torch.empty(self.hi - self.lo, dtype=torch.float32, device=dev)   # local scratch
 
-    def push(self):
-        if self.rank != self.dst:
-            self.full[self.lo:self.hi].copy_(self.local, non_blocking=True)
+    def predict(self, forest, data, **kw):
+        """One predict of this rank's rows; the final store of every row goes to dst's buffer."""
+        return forest.predict_to(data, self.out, partial=self.partial, **kw)

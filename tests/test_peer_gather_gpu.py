@@ -1,6 +1,7 @@
-"""GPU, two devices: the ranks' score slices are gathered on rank 0 through CUDA IPC peer copies
-(tahoe_b200/shard.py PeerGather) -- no NCCL anywhere: the process group is gloo and carries only the
-forest broadcast and the pickled IPC handle.  Skipped on a one-GPU box."""
+"""GPU, two devices: the ranks' final scores are stored by the kernels' own epilogue straight into
+rank 0's buffer, mapped through CUDA IPC (tahoe_predict_to, tahoe_b200/shard.py PeerGather) -- no copy
+and no NCCL anywhere: the process group is gloo and carries only the forest broadcast and the pickled
+IPC handle.  The gathered buffer must equal the single-GPU result bit for bit.  Skipped on a one-GPU box."""
 import os
 import socket
 
@@ -30,9 +31,12 @@ def _worker(rank, world, port, out_path):
         sf = shard.ShardedForest(nodes, T, D, C, missing=-999.0)
         pg = shard.PeerGather(R)
         x = torch.from_numpy(synth.gen_data(6, pg.hi - pg.lo, C, miss_frac=0.01, row0=pg.lo)).cuda()
-        for s in (api.SPLIT_SHARED_FOREST, api.DIRECT):
-            sf.predict_local(x, pg.local, strategy=s)
-            pg.push()
+        for s in (api.SPLIT_SHARED_FOREST, api.DIRECT, api.SHARED_DATA):
+            if rank == 0:
+                pg.full.fill_(float("nan"))            # every row must be (re)written by some rank's kernel
+                torch.cuda.synchronize()
+            dist.barrier()
+            pg.predict(sf.forest, x, strategy=s)
             torch.cuda.synchronize()
             dist.barrier()
             if rank == 0:
@@ -53,6 +57,12 @@ def test_peer_gather_two_gpus(oracle, tmp_path):
     mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
     nodes = synth.gen_dense_forest(5, T, D, C, leaf_prob=0.05)
     want = oracle.predict_dense(nodes, T, D, synth.gen_data(6, R, C, miss_frac=0.01), -999.0)
-    for s in (api.SPLIT_SHARED_FOREST, api.DIRECT):
+    # the same forest on ONE GPU, all rows: the gathered buffer must hold exactly these bits
+    f = api.Forest.from_dense(nodes, T, D, C, missing=-999.0)
+    x = torch.from_numpy(synth.gen_data(6, R, C, miss_frac=0.01)).cuda()
+    for s in (api.SPLIT_SHARED_FOREST, api.DIRECT, api.SHARED_DATA):
         got = np.load(out + f".{s}.npy")
-        assert np.array_equal(got.view(np.uint32), want.view(np.uint32))     # thread = sample strategies: the CPU's bits
+        single = f.predict(x, strategy=s).cpu().numpy()
+        assert np.array_equal(got.view(np.uint32), single.view(np.uint32)), api.STRATEGY_NAMES[s]
+        if s != api.SHARED_DATA:   # thread = sample strategies: the CPU's bits
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
