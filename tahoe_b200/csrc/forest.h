@@ -22,6 +22,11 @@
 
 namespace tahoe {
 
+// k_smem_forest: levels 0 and 1 of every tree of a launch -- {root, left child, right child} -- travel as a
+// kernel parameter (kernels_smem_traverse.cuh)
+constexpr int kTopTrees = 2688;                 // 2688 * 12 B = 32,256 B (+ SmemParams < the 32,764-byte limit)
+struct TopWords { uint32_t w[3 * kTopTrees]; };
+
 constexpr int kMetaFidMask = (1 << 29) - 1;      // I8: fid in bits 0..28
 constexpr uint32_t kMetaExchange = 1u << 29;     // I8 only (reference EXCHANGE_MASK_INT is bit 31, Struct.h:64)
 constexpr uint32_t kMetaDefLeft = 1u << 30;      // same bit as the reference's DEF_LEFT_MASK, Struct.h:58
@@ -80,6 +85,7 @@ struct HostPack {
   std::vector<float> qtable;          // sorted distinct thresholds, all columns back to back
   std::vector<int32_t> qoffsets;      // [C+1]
   std::vector<int32_t> leaf_origin;   // [T][2^d]
+  std::vector<uint32_t> top3;         // [qwords_trees][3] levels 0 and 1 of every (padded) tree: kernel-parameter table
   // bucket index over each column's threshold range: rank(v) is searched only inside v's bucket
   int qbuckets = 0;                   // B (power of two)
   std::vector<float> qlut_min;        // [C] smallest threshold of the column
@@ -109,6 +115,7 @@ struct Tuning {
   int sparse_grid = 0;                 // TAHOE_SPARSE_GRID: cap on k_sparse_smem's grid
   int sparse_group = 3;                // TAHOE_SPARSE_GROUP: sequences per lane of k_sparse_smem
   int direct_group = 0;                // TAHOE_DIRECT_GROUP: 4 = four walks per thread, 1 = one; 0 = by batch size
+  int top_trees = 0;                   // TAHOE_TOP_TREES: cap on the trees per launch of k_smem_forest (test knob: forces the split)
   int slab_first = 2, slab_growth = 150, slab_cap = 24;   // TAHOE_HOST_SLAB="first,growth%,cap" (waves of tiles)
 };
 
@@ -164,6 +171,7 @@ struct tahoe_forest {
   size_t sd_smem = 0;
 
   tahoe::HostPack host;
+  tahoe::TopWords top_words_all{};   // host.top3 when the whole forest fits one launch's table
 
   // device copies
   uint2* d_heap = nullptr;

@@ -18,6 +18,7 @@
 //                  [rows x blocks] temp and no segmented reduce.
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
 
 #include "kernels_smem_traverse.cuh"   // SmemParams; the kernel itself is instantiated per depth
 
@@ -142,7 +143,7 @@ int ensure_workspace(tahoe_forest* f, Workspace* ws, size_t rows) {
 
 // one translation unit per depth (kernels_smem_depth.cu)
 #define TAHOE_DEPTH_DECL(D) \
-  int launch_smem_depth_##D(tahoe_forest* f, const SmemParams& p, unsigned grid, cudaStream_t stream);
+  int launch_smem_depth_##D(tahoe_forest* f, const SmemParams& p, const TopWords& tw, unsigned grid, cudaStream_t stream);
 TAHOE_DEPTH_DECL(1) TAHOE_DEPTH_DECL(2) TAHOE_DEPTH_DECL(3) TAHOE_DEPTH_DECL(4) TAHOE_DEPTH_DECL(5)
 TAHOE_DEPTH_DECL(6) TAHOE_DEPTH_DECL(7) TAHOE_DEPTH_DECL(8) TAHOE_DEPTH_DECL(9) TAHOE_DEPTH_DECL(10)
 TAHOE_DEPTH_DECL(11) TAHOE_DEPTH_DECL(12) TAHOE_DEPTH_DECL(13) TAHOE_DEPTH_DECL(14)
@@ -208,6 +209,14 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
     const size_t fit = budget / ((size_t)p.cols * 128);
     if (budget && f->num_chunks > 1 && fit < tiles) batch_tiles = std::max<size_t>(wave, fit / wave * wave);
   }
+  // Levels 0 and 1 of the trees ride in the kernel parameters (TopWords).  A forest with more trees than the
+  // table holds is cut into consecutive chunk ranges, one launch each; partial sums flow from launch to
+  // launch through preds[] exactly as they do from chunk to chunk.  (The leaf-id instantiation reads every
+  // level from shared memory and is never split.)
+  const size_t W = (size_t)1 << (f->qdepth + 1);
+  const int top_limit = std::max(f->trees_per_chunk, std::min(kTopTrees, f->tune.top_trees > 0 ? f->tune.top_trees : kTopTrees));
+  const int chunks_per_launch = p.leaf_ids ? f->num_chunks : std::max(1, top_limit / f->trees_per_chunk);
+  if (f->trees_per_chunk > kTopTrees && !p.leaf_ids) { set_error("chunk larger than the top-level table"); return TAHOE_ERR_INVALID; }
   for (size_t t0 = 0; t0 < tiles && rc == TAHOE_OK; t0 += batch_tiles) {
     SmemParams b = p;
     b.num_tiles = std::min(batch_tiles, tiles - t0);
@@ -219,16 +228,31 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
     if (p.leaf_ids) b.leaf_ids = p.leaf_ids + t0 * 32 * (size_t)p.num_trees;
     const unsigned grid = (unsigned)std::min<size_t>((size_t)f->sm_count,
                                                      (b.num_tiles + f->warps - 1) / f->warps);
-    switch (f->qdepth) {
-#define TAHOE_DEPTH_CASE(D) case D: rc = launch_smem_depth_##D(f, b, grid, a.stream); break;
-      TAHOE_DEPTH_CASE(1) TAHOE_DEPTH_CASE(2) TAHOE_DEPTH_CASE(3) TAHOE_DEPTH_CASE(4)
-      TAHOE_DEPTH_CASE(5) TAHOE_DEPTH_CASE(6) TAHOE_DEPTH_CASE(7) TAHOE_DEPTH_CASE(8)
-      TAHOE_DEPTH_CASE(9) TAHOE_DEPTH_CASE(10) TAHOE_DEPTH_CASE(11) TAHOE_DEPTH_CASE(12)
-      TAHOE_DEPTH_CASE(13) TAHOE_DEPTH_CASE(14)
+    for (int c0 = 0; c0 < f->num_chunks && rc == TAHOE_OK; c0 += chunks_per_launch) {
+      SmemParams r = b;
+      r.num_chunks = std::min(chunks_per_launch, f->num_chunks - c0);
+      r.tree_base = c0 * f->trees_per_chunk;
+      r.padded_trees = std::min(r.num_chunks * f->trees_per_chunk, f->qwords_trees - r.tree_base);
+      r.qwords = p.qwords + (size_t)r.tree_base * W;
+      r.first_pass = c0 == 0;
+      r.last_pass = c0 + r.num_chunks >= f->num_chunks;
+      const TopWords* tw = &f->top_words_all;           // whole forest in one launch: prepared at upload
+      TopWords local;
+      if (!p.leaf_ids && chunks_per_launch < f->num_chunks) {
+        std::memcpy(local.w, f->host.top3.data() + (size_t)r.tree_base * 3, (size_t)r.padded_trees * 3 * sizeof(uint32_t));
+        tw = &local;
+      }
+      switch (f->qdepth) {
+#define TAHOE_DEPTH_CASE(D) case D: rc = launch_smem_depth_##D(f, r, *tw, grid, a.stream); break;
+        TAHOE_DEPTH_CASE(1) TAHOE_DEPTH_CASE(2) TAHOE_DEPTH_CASE(3) TAHOE_DEPTH_CASE(4)
+        TAHOE_DEPTH_CASE(5) TAHOE_DEPTH_CASE(6) TAHOE_DEPTH_CASE(7) TAHOE_DEPTH_CASE(8)
+        TAHOE_DEPTH_CASE(9) TAHOE_DEPTH_CASE(10) TAHOE_DEPTH_CASE(11) TAHOE_DEPTH_CASE(12)
+        TAHOE_DEPTH_CASE(13) TAHOE_DEPTH_CASE(14)
 #undef TAHOE_DEPTH_CASE
-      default: set_error("unsupported depth"); return TAHOE_ERR_NOT_APPLICABLE;
+        default: set_error("unsupported depth"); return TAHOE_ERR_NOT_APPLICABLE;
+      }
+      ++*launches;
     }
-    ++*launches;
   }
   if (rc) return rc;
   if (ev) TAHOE_CUDA(cudaEventRecord(ev[2], a.stream));

@@ -47,7 +47,8 @@ __device__ __forceinline__ void ldg_nc_block(uint64_t addr, uint4& a, uint4& b) 
 // <= 64 as a pair; 16: <= 64 columns, plans of <= 8 warps).  K: deep walks in flight per lane.
 template <int DEPTH, int G, bool LEAF_IDS, int PIECES, int K, bool PAIR>
 __global__ void __launch_bounds__(PIECES > kStagedMaxCols / 4 ? 256 : kSmemMaxThreads, 1)
-k_smem_forest_deep(SmemParams p) {
+k_smem_forest_deep(const __grid_constant__ SmemParams p, const __grid_constant__ TopWords tw) {
+  constexpr bool TOPC = !LEAF_IDS;
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr uint32_t W = 1u << (DEPTH + 1);      // words per tree
   constexpr uint32_t L = 1u << DEPTH;            // bottom slots per tree
@@ -139,8 +140,8 @@ k_smem_forest_deep(SmemParams p) {
     mbar_wait(bar_chunk, chunk_phase);
     chunk_phase ^= 1;
 
-    const bool first = (chunk == 0), last = (chunk == p.num_chunks - 1);
-    const int64_t chunk_first = __ldg(p.block_offsets + min(tree0, p.num_trees));
+    const bool first = p.first_pass && chunk == 0, last = p.last_pass && chunk == p.num_chunks - 1;
+    const int64_t chunk_first = __ldg(p.block_offsets + min(p.tree_base + tree0, p.num_trees));
     const uint32_t dummy = (uint32_t)(__ldg(p.block_offsets + p.num_trees) - chunk_first);
     uint64_t cdv = (uint64_t)(p.deep_blocks + 2 * chunk_first);   // kept as one 64-bit register: block address = one IMAD.WIDE
     asm volatile("" : "+l"(cdv));
@@ -262,8 +263,8 @@ k_smem_forest_deep(SmemParams p) {
         deep_step();
         uint32_t a[G];
         const uint32_t tree_abs = s_base + forest_off + (uint32_t)t * W * 4u;
-        if (has_missing) traverse_group<DEPTH, G, true>(tree_abs, s_base, cur_sl, p.col_mask, p.miss_code, a);
-        else traverse_group<DEPTH, G, false>(tree_abs, s_base, cur_sl, p.col_mask, p.miss_code, a);
+        if (has_missing) traverse_group<DEPTH, G, true, TOPC>(tree_abs, s_base, cur_sl, p.col_mask, p.miss_code, a, tw, tree0 + t);
+        else traverse_group<DEPTH, G, false, TOPC>(tree_abs, s_base, cur_sl, p.col_mask, p.miss_code, a, tw, tree0 + t);
         uint32_t v[G];
 #pragma unroll
         for (int g = 0; g < G; ++g) v[g] = lds_u32(a[g]);

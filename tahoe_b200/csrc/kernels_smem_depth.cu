@@ -24,12 +24,12 @@
 
 namespace tahoe {
 
-int TAHOE_CAT(launch_smem_depth_, TAHOE_DEPTH)(tahoe_forest* f, const SmemParams& p, unsigned grid,
-                                              cudaStream_t stream) {
+int TAHOE_CAT(launch_smem_depth_, TAHOE_DEPTH)(tahoe_forest* f, const SmemParams& p, const TopWords& tw,
+                                              unsigned grid, cudaStream_t stream) {
   constexpr int D = TAHOE_DEPTH;
   auto go = [&](auto kern) -> int {
     TAHOE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->smem_bytes));
-    kern<<<grid, (unsigned)f->warps * 32u, f->smem_bytes, stream>>>(p);
+    kern<<<grid, (unsigned)f->warps * 32u, f->smem_bytes, stream>>>(p, tw);
     TAHOE_CUDA(cudaGetLastError());
     return TAHOE_OK;
   };

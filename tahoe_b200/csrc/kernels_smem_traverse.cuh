@@ -18,6 +18,8 @@ struct SmemParams {
   int num_trees;            // real trees (leaf ids are written for these only)
   int padded_trees;         // trees in qwords: whole traversal groups, the extra ones all zero
   int trees_per_chunk, num_chunks;
+  int tree_base;            // index (in the whole padded forest) of this launch's first tree: qwords points at it
+  int first_pass, last_pass;  // this launch holds the forest's first / last chunk (partial sums start / end here)
   uint32_t col_mask, miss_code;
   // tile region: word (col, slot, lane) at col*col_stride + slot*slot_stride + lane*4, and
   // (node & col_mask) == col*col_stride, so a lane's address is one AND-OR.  Two layouts:
@@ -38,6 +40,15 @@ struct SmemParams {
   const int64_t* block_offsets;  // [T+1] first block of every tree
   const int32_t* block_orig;     // [blocks + 1][3] caller's node index of root / left / right
 };
+
+// Levels 0 and 1 of every tree of a launch -- {root, left child, right child}, 12 bytes per tree -- travel as a
+// KERNEL PARAMETER (constant bank 0; parameters may be up to 32,764 bytes since CUDA 12.1).  The root is
+// the same word for all lanes and the level-1 node is a select between two warp-uniform words, so both
+// come through the uniform datapath (LDCU / ULDC) instead of two shared-memory loads: two of a tree's
+// ~28-38 LSU wavefronts and two of its DEPTH + 1 dependent shared-memory round trips disappear.  A forest
+// with more trees than the table holds is run as several launches over consecutive chunk ranges
+// (SmemParams::tree_base / first_pass / last_pass), each with the table of its own trees.
+// (kTopTrees, TopWords: forest.h)
 
 constexpr uint32_t kContMask = 0xFFC00000u;   // packer.cu: marker = kContMask | node index relative to the chunk's first node
 
@@ -64,18 +75,49 @@ constexpr int kSmemMaxThreads = kSmemMaxWarps * 32;
 //   ISETP rank > node ; SEL k = right ? 4-B : -B ; IADD3 a = a + a + k      (B = tree address)
 // i.e. a' - B = 2(a - B) + 4*right, the heap step on byte offsets, with no separate address add.
 // Loads are asm so the address arithmetic stays exactly this; ptxas still interleaves the G chains.
-template <int DEPTH, int G, bool MISSING>
+template <int DEPTH, int G, bool MISSING, bool TOPC>
 __device__ __forceinline__ void traverse_group(uint32_t tree_abs, uint32_t s_base, uint32_t slot_lane,
-                                               uint32_t col_mask, uint32_t miss_code, uint32_t (&a)[G]) {
+                                               uint32_t col_mask, uint32_t miss_code, uint32_t (&a)[G],
+                                               const TopWords& tw, int top_index) {
   constexpr uint32_t W4 = 4u << (DEPTH + 1);  // bytes per tree
   uint32_t k0[G];
 #pragma unroll
-  for (int g = 0; g < G; ++g) {
-    k0[g] = 0u - (tree_abs + g * W4);
-    a[g] = tree_abs + g * W4 + 4;
+  for (int g = 0; g < G; ++g) k0[g] = 0u - (tree_abs + g * W4);
+  auto right = [&](uint32_t F, uint32_t N) {
+    bool c = F > N;
+    if (MISSING) {
+      if (F == miss_code) c = !(N & 1u);      // sentinel: !def_left (BaseTahoeTest.h:452)
+    }
+    return c;
+  };
+  constexpr int kTop = TOPC ? (DEPTH >= 2 ? 2 : 1) : 0;   // levels decided on parameter words
+  if (TOPC) {
+    uint32_t F0[G], N1[G], F1[G];
+    bool c0[G];
+#pragma unroll
+    for (int g = 0; g < G; ++g)   // root: warp-uniform word, the column offset is uniform arithmetic
+      F0[g] = lds_u32(s_base + ((tw.w[3 * (top_index + g)] & col_mask) | slot_lane));
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      c0[g] = right(F0[g], tw.w[3 * (top_index + g)]);
+      N1[g] = c0[g] ? tw.w[3 * (top_index + g) + 2] : tw.w[3 * (top_index + g) + 1];
+    }
+    if (DEPTH >= 2) {
+#pragma unroll
+      for (int g = 0; g < G; ++g) F1[g] = lds_u32(s_base + ((N1[g] & col_mask) | slot_lane));
+#pragma unroll
+      for (int g = 0; g < G; ++g)   // heap index at level 2 = 4 + 2 c0 + c1 (root = 1)
+        a[g] = tree_abs + g * W4 + 16u + (c0[g] ? 8u : 0u) + (right(F1[g], N1[g]) ? 4u : 0u);
+    } else {
+#pragma unroll
+      for (int g = 0; g < G; ++g) a[g] = tree_abs + g * W4 + 8u + (c0[g] ? 4u : 0u);
+    }
+  } else {
+#pragma unroll
+    for (int g = 0; g < G; ++g) a[g] = tree_abs + g * W4 + 4;
   }
 #pragma unroll
-  for (int l = 0; l < DEPTH; ++l) {
+  for (int l = kTop; l < DEPTH; ++l) {
     uint32_t N[G], F[G];
 #pragma unroll
     for (int g = 0; g < G; ++g) N[g] = lds_u32(a[g]);
@@ -85,10 +127,7 @@ __device__ __forceinline__ void traverse_group(uint32_t tree_abs, uint32_t s_bas
     }
 #pragma unroll
     for (int g = 0; g < G; ++g) {
-      bool c = F[g] > N[g];
-      if (MISSING) {
-        if (F[g] == miss_code) c = !(N[g] & 1u);  // sentinel: !def_left (BaseTahoeTest.h:452)
-      }
+      const bool c = right(F[g], N[g]);
       a[g] = a[g] + a[g] + (c ? k0[g] + 4u : k0[g]);
     }
   }
@@ -99,7 +138,9 @@ __device__ __forceinline__ void sts_u128(uint32_t addr, uint4 v) {
 }
 
 template <int DEPTH, int G, bool LEAF_IDS, bool STAGED>
-__global__ void __launch_bounds__(kSmemMaxThreads, 1) k_smem_forest(SmemParams p) {
+__global__ void __launch_bounds__(kSmemMaxThreads, 1)
+k_smem_forest(const __grid_constant__ SmemParams p, const __grid_constant__ TopWords tw) {
+  constexpr bool TOPC = !LEAF_IDS;               // the checking path keeps every level in shared memory
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr uint32_t W = 1u << (DEPTH + 1);      // words per tree
   constexpr uint32_t L = 1u << DEPTH;            // bottom slots per tree
@@ -196,7 +237,7 @@ __global__ void __launch_bounds__(kSmemMaxThreads, 1) k_smem_forest(SmemParams p
     mbar_wait(bar_chunk, chunk_phase);
     chunk_phase ^= 1;
 
-    const bool first = (chunk == 0), last = (chunk == p.num_chunks - 1);
+    const bool first = p.first_pass && chunk == 0, last = p.last_pass && chunk == p.num_chunks - 1;
     int buf = 0;
     // the tile's missing flag and this lane's partial sum are fetched one tile ahead, so that their
     // global-memory latency hides behind the traversal of the tile before
@@ -236,11 +277,12 @@ __global__ void __launch_bounds__(kSmemMaxThreads, 1) k_smem_forest(SmemParams p
       for (int t = 0; t < ntrees; t += G) {
         uint32_t a[G];
         const uint32_t tree_abs = s_base + forest_off + (uint32_t)t * W * 4u;
-        if (has_missing) traverse_group<DEPTH, G, true>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a);
-        else traverse_group<DEPTH, G, false>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a);
+        if (has_missing) traverse_group<DEPTH, G, true, TOPC>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a, tw, tree0 + t);
+        else traverse_group<DEPTH, G, false, TOPC>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a, tw, tree0 + t);
 #pragma unroll
         for (int g = 0; g < G; ++g) {
           acc += __uint_as_float(lds_u32(a[g]));   // a padding tree adds +0.0f: the sum keeps its bits
+          // (the leaf-id instantiation is never split over launches: tree_base == 0)
           if (LEAF_IDS && live && tree0 + t + g < p.num_trees)
             p.leaf_ids[row * (size_t)p.num_trees + tree0 + t + g] =
                 __ldg(p.leaf_origin + (size_t)(tree0 + t + g) * L + ((a[g] - tree_abs - g * W * 4u) / 4 - L));

@@ -927,6 +927,7 @@ static void read_tuning(Tuning& t) {
   if (const char* e = std::getenv("TAHOE_SPARSE_GRID")) t.sparse_grid = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_SPARSE_GROUP")) t.sparse_group = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_DIRECT_GROUP")) t.direct_group = std::atoi(e);
+  if (const char* e = std::getenv("TAHOE_TOP_TREES")) t.top_trees = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_HOST_SLAB")) std::sscanf(e, "%d,%d,%d", &t.slab_first, &t.slab_growth, &t.slab_cap);
   t.slab_first = std::max(t.slab_first, 1);
   t.slab_cap = std::max(t.slab_cap, t.slab_first);
@@ -989,6 +990,12 @@ int upload(tahoe_forest* f) {
     TAHOE_CUDA(cudaMalloc((void**)&f->d_qwords, words * 4));
     TAHOE_CUDA(cudaMemset(f->d_qwords, 0, words * 4));
     TAHOE_CUDA(cudaMemcpy(f->d_qwords, h.qwords.data(), h.qwords.size() * 4, cudaMemcpyHostToDevice));
+    // levels 0 and 1 of every tree for the kernel-parameter table (padding trees: all zero)
+    h.top3.assign((size_t)f->qwords_trees * 3, 0u);
+    const size_t real = h.qwords.size() / W;
+    for (size_t t = 0; t < real; ++t)
+      for (int k = 0; k < 3 && (size_t)(k + 1) < W; ++k) h.top3[t * 3 + k] = h.qwords[t * W + 1 + k];
+    if (f->qwords_trees <= kTopTrees) std::memcpy(f->top_words_all.w, h.top3.data(), h.top3.size() * sizeof(uint32_t));
   }
   if (!h.qtable.empty()) {
     // device copy of the threshold tables: every column starts on a 16-byte boundary and is padded

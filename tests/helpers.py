@@ -55,4 +55,34 @@ def score_close(got, want, l1=None):
     scale = np.maximum(np.abs(want), 1.0)
     if l1 is not None:
         scale = np.maximum(scale, np.asarray(l1, dtype=np.float64))
+        if not score_tight(got, want, l1):     # the attainable bound, ten times tighter (see score_tight)
+            return False
     return bool(np.all(np.abs(got - want) <= 1e-5 * scale))
+
+
+def score_tight(got, want, l1):
+    """What a re-ordered float32 sum actually achieves, asserted next to the stated tolerance so that the
+    looser reading above cannot hide a real defect: sequential f32 summation of T terms carries an rms
+    rounding error of about 0.5 * 2^-24 * sigma * T, i.e. ~3e-8 of the L1 mass whatever T is, so two
+    orderings differ by ~4e-8 * mass rms and ~2.5e-7 * mass at the far tail of 10^7 rows.  Bound:
+    1e-6 * max(l1 mass, 1) -- ten times tighter than 1e-5 * mass."""
+    got = np.asarray(got, dtype=np.float64)
+    want = np.asarray(want, dtype=np.float64)
+    scale = np.maximum(np.asarray(l1, dtype=np.float64), 1.0)
+    return bool(np.all(np.abs(got - want) <= 1e-6 * scale))
+
+
+def abs_leaf_forest(nodes):
+    """The same trees with every LEAF value replaced by its magnitude: a row reaches the same leaves, so
+    its score under this forest is the L1 mass of its summands (used to bound re-ordered sums on all rows,
+    on the device, without 4 bytes x rows x trees of leaf ids).  Works for dense and sparse node arrays."""
+    out = nodes.copy()
+    leaf = out["bits"] < 0
+    out["val"][leaf] = np.abs(out["val"][leaf])
+    return out
+
+
+def l1_mass_sparse(nodes, tree_offsets, leaf_ids):
+    """sum_t |leaf value reached in tree t| per row from the oracle's leaf ids (sparse forests: node index in the tree)."""
+    offs = np.asarray(tree_offsets, dtype=np.int64)[:-1][None, :]
+    return np.abs(nodes["val"][offs + leaf_ids].astype(np.float64)).sum(axis=1)

@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 
 from tahoe_b200 import api, synth
-from tests.helpers import bits_equal, l1_mass, score_close
+from tests.helpers import abs_leaf_forest, bits_equal, l1_mass, l1_mass_sparse, score_close, score_tight
 
 pytestmark = pytest.mark.gpu
 ORDERED = (api.DIRECT, api.SHARED_DATA_PER_THREAD, api.SHARED_FOREST, api.SPLIT_SHARED_FOREST)
@@ -61,9 +61,18 @@ def test_dense_config_full_size(oracle, cfg, miss_frac):
             else:
                 assert bits_equal(g, ref), (cfg, api.STRATEGY_NAMES[s])            # strategy vs strategy, ALL rows
         else:
-            assert score_close(g[idx], want, l1_mass(nodes, T, d, wids)), (cfg, api.STRATEGY_NAMES[s])
+            mass = l1_mass(nodes, T, d, wids)
+            assert score_close(g[idx], want, mass), (cfg, api.STRATEGY_NAMES[s])
+            assert score_tight(g[idx], want, mass), (cfg, api.STRATEGY_NAMES[s])
             if ref is not None:
-                assert np.max(np.abs(g.astype(np.float64) - ref)) <= 1e-5 * T     # every row, L1 mass <= T
+                # every row, against the tree-order sum, bounded by that row's OWN L1 mass: the score of the
+                # same trees with |leaf value| leaves, computed on the device by an in-order strategy
+                fa = api.Forest.from_dense(abs_leaf_forest(nodes), T, d, C, missing=-999.0)
+                in_order = api.SPLIT_SHARED_FOREST if fa.applicable(api.SPLIT_SHARED_FOREST, R) else api.DIRECT
+                mass_all = fa.predict(data, strategy=in_order).cpu().numpy()
+                fa.close()
+                assert np.allclose(mass_all[idx], mass, rtol=1e-5)
+                assert score_close(g, ref, mass_all) and score_tight(g, ref, mass_all), (cfg, api.STRATEGY_NAMES[s])
         ran.append(s)
     assert len(ran) >= 2
     # leaf ids on the subset rows, through the strategy the model picks for the full batch
@@ -103,8 +112,16 @@ def test_sparse_config_full_size(oracle):
     assert f.applicable(api.SPLIT_SHARED_FOREST, R) and info.sparse_top_active == 1
     assert info.sparse_top_chunks > 1 and info.sparse_top_deep_walks > 0
     s = f.predict(data, strategy=api.SPLIT_SHARED_FOREST).cpu().numpy()
-    mass_all = 2000.0          # |leaf| <= 1 in the generator: a bound on every row's L1 mass
-    assert np.all(np.abs(s.astype(np.float64) - a.astype(np.float64)) <= 1e-5 * mass_all)
+    # scores against the ORACLE on the subset, bounded by each row's real L1 mass (~1000 here) ...
+    mass = l1_mass_sparse(sp, offs, wids)
+    assert score_close(s[idx], want, mass) and score_tight(s[idx], want, mass)
+    # ... and against the tree-order sum (DIRECT == oracle bits) on ALL rows, each row bounded by its own mass:
+    # the same trees with |leaf value| leaves, summed in order on the device
+    fa = api.Forest.from_sparse(abs_leaf_forest(sp), offs, c["cols"], weights=w, missing=-999.0)
+    mass_all = fa.predict(data, strategy=api.DIRECT).cpu().numpy()
+    fa.close()
+    assert np.allclose(mass_all[idx], mass, rtol=1e-5)
+    assert score_close(s, a, mass_all) and score_tight(s, a, mass_all)
     ids.zero_()
     f.predict(sub, strategy=api.SPLIT_SHARED_FOREST, leaf_ids=ids)
     torch.cuda.synchronize()
