@@ -205,16 +205,33 @@ def _emit(line: dict):
 
 # ---------------------------------------------------------------------------------------------
 def build_forest(cfg_id: str, nodes=None):
-    """-> (Forest, real node count).  Dense configs from the AoS nodes, config 4 from compact nodes."""
+    """-> (Forest, real node count, levels).  Dense configs from the AoS nodes, config 4 from compact
+    nodes; levels = (tree_offsets, level of every compact node) for the sparse config, else None."""
     from tahoe_b200 import api
     cfg = synth.CONFIGS[cfg_id]
     if cfg["sparse"]:
-        sp, offs, w, _ = synth.gen_sparse_forest(synth.FOREST_SEED[cfg_id], cfg["trees"], cfg["depth"], cfg["cols"])
-        return api.Forest.from_sparse(sp, offs, cfg["cols"], weights=w, missing=-999.0), int(offs[-1])
+        sp, offs, w, lv = synth.gen_sparse_forest(synth.FOREST_SEED[cfg_id], cfg["trees"], cfg["depth"], cfg["cols"])
+        return api.Forest.from_sparse(sp, offs, cfg["cols"], weights=w, missing=-999.0), int(offs[-1]), (offs, lv)
     if nodes is None:
         nodes = synth.gen_dense_forest(synth.FOREST_SEED[cfg_id], cfg["trees"], cfg["depth"], cfg["cols"])
     f = api.Forest.from_dense(nodes, cfg["trees"], cfg["depth"], cfg["cols"], missing=-999.0)
-    return f, cfg["trees"] * synth.tree_num_nodes(cfg["depth"])
+    return f, cfg["trees"] * synth.tree_num_nodes(cfg["depth"]), None
+
+
+def measured_mean_depth(forest, data, levels, sample=4096):
+    """dbar = mean internal nodes visited per (row, tree).  For the unbalanced forest it is
+    MEASURED: the level of the leaf every (row, tree) of a row sample reaches, from the leaf ids the
+    DIRECT kernel reports (held bit-exact to the oracle's by tests/test_gpu_full_size.py)."""
+    import torch
+    from tahoe_b200 import api
+    offs, lv = levels
+    n = min(sample, int(data.shape[0]))
+    T = offs.shape[0] - 1
+    ids = torch.zeros((n, T), dtype=torch.int32, device="cuda")
+    forest.predict(data[:n].contiguous(), strategy=api.DIRECT, leaf_ids=ids)
+    torch.cuda.synchronize()
+    node = np.asarray(offs[:-1], dtype=np.int64)[None, :] + ids.cpu().numpy()
+    return float(np.asarray(lv)[node].mean())
 
 
 KERNEL_OF = {  # dominant kernel per strategy (names as they appear in the ncu launch lists under profiles/)
@@ -223,7 +240,7 @@ KERNEL_OF = {  # dominant kernel per strategy (names as they appear in the ncu l
 }
 
 
-def measure_config(cfg_id, forest, n_nodes, data, peaks, hbm_gbs, steps, strategy=None, flush=None):
+def measure_config(cfg_id, forest, n_nodes, data, peaks, hbm_gbs, steps, strategy=None, flush=None, levels=None):
     """One device-resident measurement of one config: step time over `steps` predicts (CUDA events on
     the launch stream) and the dominant kernel's own time (events recorded around it inside the
     library).  Returns the sub-record with the SURVEY 8(d) fractions."""
@@ -254,7 +271,7 @@ def measure_config(cfg_id, forest, n_nodes, data, peaks, hbm_gbs, steps, strateg
     kernel = KERNEL_OF[name]
     if info.is_sparse and name in ("shared_forest", "split_shared_forest"):
         kernel = "k_smem_forest_deep" if info.sparse_top_active else "k_sparse_smem"
-    mean_depth = info.mean_depth if info.is_sparse else float(cfg["depth"])
+    mean_depth = measured_mean_depth(forest, data, levels) if levels is not None else float(cfg["depth"])
     b_sample, b_node, b_forest = algorithmic_bytes(cfg, rows, mean_depth, n_nodes)
     abytes = b_sample + b_node
     sec = kernel_ms * 1e-3
@@ -485,9 +502,9 @@ def main():
             torch.cuda.empty_cache()
             for cid, steps in (("C1", 20), ("C2", 10), ("C4", 10)):
                 c = synth.CONFIGS[cid]
-                f, nn = build_forest(cid)
+                f, nn, levels = build_forest(cid)
                 d = api.gen_data_device(synth.DATA_SEED[cid], c["rows"], c["cols"])
-                rec, _, _ = measure_config(cid, f, nn, d, peaks, hbm_gbs, steps=steps, flush=flush)
+                rec, _, _ = measure_config(cid, f, nn, d, peaks, hbm_gbs, steps=steps, flush=flush, levels=levels)
                 cfgs[cid] = rec
                 if cid == "C2":
                     sweeps.append(sweep_record("C2", f, d, [1, 1000, 100_000, 5_000_000]))

@@ -83,6 +83,7 @@ constexpr double kSparseDeep = 3.1e-11;       // s per walk that leaves the tops
 constexpr double kSparseStep = 300e-9;        // one step of a lane's two interleaved sequences (latency)
 constexpr double kDeepWalk = 1.3e-11;          // s per parked walk of the QT layout (two-level blocks in L2, pipelined behind the traversal)
 constexpr double kSparseTileFixed = 8e-6;     // refill a warp's tile buffer + final drain
+constexpr double kHostCopyRate = 50e9;        // B/s, pinned host -> device over PCIe Gen5 x16 (measured 57 GB/s, one GPU active)
 }  // namespace model
 
 static double forest_bytes(const tahoe_forest* f) {
@@ -347,23 +348,40 @@ static int predict_host_impl(tahoe_forest_t* f, int strategy, const float* h_dat
   if (strategy == TAHOE_STRATEGY_AUTO) strategy = select_strategy(f, num_rows, nullptr);
   // Slabs: copy of slab i+1 under the kernel of slab i, three slabs in flight.  The shared-memory
   // strategies deal 32-row tiles to sm_count x warps persistent warps, so their slabs are whole WAVES
-  // of tiles (no ragged last round per chunk pass), growing from 2 waves by 1.5x up to 24: the first
-  // copy, which nothing can hide, is short; a slab may only grow as fast as the kernels before it run
-  // ahead of the copy engine (the copy of config 2's rows takes 0.8 of their predict); and the later
-  // kernels are long enough to amortise their chunk passes.  TAHOE_HOST_SLAB="first,growth%,cap" (waves),
-  // read when the handle was created.  Other strategies: slabs of about an eighth of the batch, sized in
-  // BYTES (<= 256 MB of rows per slot, whatever the row width).  No slab is larger than the batch.
+  // of tiles (no ragged last round per chunk pass).  The first slab is short (2 waves: its copy is
+  // the one nothing can hide) and every slab is `growth` times the one before, up to `cap` waves: a slab may
+  // only grow as fast as the kernels before it run ahead of the copy engine, so growth follows the
+  // ratio of copy time to predicted kernel time per row -- 1.5x / 24 waves where the copy takes 0.8 of the
+  // predict (config 2), 3x / 96 waves where it takes 0.37 (config 3: every slab kernel pays 167 chunk
+  // passes of fixed cost, so fewer, larger slabs win) -- tools/probe_e2e.py, profiles/r02_e2e.md.
+  // TAHOE_HOST_SLAB="first,growth%,cap" (waves), read when the handle was created, overrides.
+  // Other strategies: slabs of about an eighth of the batch, sized in BYTES (<= 256 MB of rows per slot,
+  // whatever the row width).  No slab is larger than the batch.
   const size_t rows32 = (num_rows + 31) / 32 * 32;
   const size_t row_bytes = (size_t)C * sizeof(float);
   size_t slab = ((num_rows + 7) / 8 + 31) / 32 * 32;
   slab = std::max<size_t>(slab, std::min<size_t>(65536, (size_t)(32u << 20) / row_bytes / 32 * 32));
   slab = std::min<size_t>(slab, std::max<size_t>((size_t)(256u << 20) / row_bytes / 32 * 32, 32));
   size_t wave = 0;
-  const int slab_first = f->tune.slab_first, slab_growth = f->tune.slab_growth, slab_cap = f->tune.slab_cap;
+  int slab_first = 2, slab_growth = 150, slab_cap = 24;
   if ((strategy == TAHOE_STRATEGY_SHARED_FOREST || strategy == TAHOE_STRATEGY_SPLIT_SHARED_FOREST) &&
       (f->quant || (f->qt && f->sp_use_qt)) && f->trees_per_chunk > 0) {
     const bool paired = f->sparse && C > kStagedMaxCols && f->warps > 8;
     wave = (size_t)f->sm_count * (size_t)(paired ? f->warps / 2 : f->warps) * 32;
+    double t[TAHOE_NUM_STRATEGIES];
+    select_strategy(f, num_rows, t);
+    const double kernel_per_row = t[strategy] / (double)num_rows;
+    const double copy_per_row = (double)row_bytes / model::kHostCopyRate;
+    if (std::isfinite(kernel_per_row) && kernel_per_row > 0.0) {
+      const double g = std::min(3.0, std::max(1.25, 1.15 * kernel_per_row / copy_per_row));
+      slab_growth = (int)(g * 100.0 + 0.5);
+      slab_cap = (int)std::min(128.0, std::max(24.0, 24.0 * (g / 1.5) * (g / 1.5)));
+    }
+    if (f->tune.slab_first > 0) {
+      slab_first = f->tune.slab_first;
+      slab_growth = std::max(f->tune.slab_growth, 100);
+      slab_cap = std::max(f->tune.slab_cap, slab_first);
+    }
     slab = (size_t)slab_cap * wave;
   }
   slab = std::max<size_t>(32, std::min(slab, rows32));

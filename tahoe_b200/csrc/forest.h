@@ -116,7 +116,7 @@ struct Tuning {
   int sparse_group = 3;                // TAHOE_SPARSE_GROUP: sequences per lane of k_sparse_smem
   int direct_group = 0;                // TAHOE_DIRECT_GROUP: 4 = four walks per thread, 1 = one; 0 = by batch size
   int top_trees = 0;                   // TAHOE_TOP_TREES: cap on the trees per launch of k_smem_forest (test knob: forces the split)
-  int slab_first = 2, slab_growth = 150, slab_cap = 24;   // TAHOE_HOST_SLAB="first,growth%,cap" (waves of tiles)
+  int slab_first = 0, slab_growth = 0, slab_cap = 0;   // TAHOE_HOST_SLAB="first,growth%,cap" (waves of tiles); 0 = from the model
 };
 
 constexpr int kHostSlots = 3;

@@ -929,9 +929,6 @@ static void read_tuning(Tuning& t) {
   if (const char* e = std::getenv("TAHOE_DIRECT_GROUP")) t.direct_group = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_TOP_TREES")) t.top_trees = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_HOST_SLAB")) std::sscanf(e, "%d,%d,%d", &t.slab_first, &t.slab_growth, &t.slab_cap);
-  t.slab_first = std::max(t.slab_first, 1);
-  t.slab_cap = std::max(t.slab_cap, t.slab_first);
-  t.slab_growth = std::max(t.slab_growth, 100);
 }
 
 int query_device(tahoe_forest* f) {
