@@ -193,6 +193,7 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.padded_trees = f->qwords_trees;
   p.trees_per_chunk = f->trees_per_chunk; p.num_chunks = f->num_chunks;
   p.col_mask = f->col_mask; p.miss_code = f->miss_code;
+  p.top_levels = f->tune.top_levels >= 0 ? f->tune.top_levels : (f->warps >= 12 ? 2 : 0);
   p.col_stride = f->tile_col_stride; p.slot_stride = f->tile_slot_stride; p.tile_region = f->tile_region;
   p.preds = a.preds; p.out = a.out; p.leaf_ids = a.leaf_ids;
   p.leaf_origin = f->d_leaf_origin;

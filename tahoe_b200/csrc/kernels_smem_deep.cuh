@@ -48,7 +48,6 @@ __device__ __forceinline__ void ldg_nc_block(uint64_t addr, uint4& a, uint4& b) 
 template <int DEPTH, int G, bool LEAF_IDS, int PIECES, int K, bool PAIR>
 __global__ void __launch_bounds__(PIECES > kStagedMaxCols / 4 ? 256 : kSmemMaxThreads, 1)
 k_smem_forest_deep(const __grid_constant__ SmemParams p, const __grid_constant__ TopWords tw) {
-  constexpr bool TOPC = !LEAF_IDS;
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr uint32_t W = 1u << (DEPTH + 1);      // words per tree
   constexpr uint32_t L = 1u << DEPTH;            // bottom slots per tree
@@ -263,8 +262,9 @@ k_smem_forest_deep(const __grid_constant__ SmemParams p, const __grid_constant__
         deep_step();
         uint32_t a[G];
         const uint32_t tree_abs = s_base + forest_off + (uint32_t)t * W * 4u;
-        if (has_missing) traverse_group<DEPTH, G, true, TOPC>(tree_abs, s_base, cur_sl, p.col_mask, p.miss_code, a, tw, tree0 + t);
-        else traverse_group<DEPTH, G, false, TOPC>(tree_abs, s_base, cur_sl, p.col_mask, p.miss_code, a, tw, tree0 + t);
+        constexpr int TOPL = LEAF_IDS ? 0 : 2;       // 16 warps (or pairs): both parameter levels pay (config 4: 9.00 -> 8.84 ms)
+        if (has_missing) traverse_group<DEPTH, G, true, TOPL>(tree_abs, s_base, cur_sl, p.col_mask, p.miss_code, a, tw, tree0 + t);
+        else traverse_group<DEPTH, G, false, TOPL>(tree_abs, s_base, cur_sl, p.col_mask, p.miss_code, a, tw, tree0 + t);
         uint32_t v[G];
 #pragma unroll
         for (int g = 0; g < G; ++g) v[g] = lds_u32(a[g]);

@@ -4,6 +4,7 @@
 #pragma once
 #include "device_utils.cuh"
 #include "forest.h"
+#include <type_traits>
 
 namespace tahoe {
 
@@ -20,6 +21,7 @@ struct SmemParams {
   int trees_per_chunk, num_chunks;
   int tree_base;            // index (in the whole padded forest) of this launch's first tree: qwords points at it
   int first_pass, last_pass;  // this launch holds the forest's first / last chunk (partial sums start / end here)
+  int top_levels;           // levels of every tree decided on the TopWords kernel parameter (0, 1 or 2): the plan's choice
   uint32_t col_mask, miss_code;
   // tile region: word (col, slot, lane) at col*col_stride + slot*slot_stride + lane*4, and
   // (node & col_mask) == col*col_stride, so a lane's address is one AND-OR.  Two layouts:
@@ -75,7 +77,7 @@ constexpr int kSmemMaxThreads = kSmemMaxWarps * 32;
 //   ISETP rank > node ; SEL k = right ? 4-B : -B ; IADD3 a = a + a + k      (B = tree address)
 // i.e. a' - B = 2(a - B) + 4*right, the heap step on byte offsets, with no separate address add.
 // Loads are asm so the address arithmetic stays exactly this; ptxas still interleaves the G chains.
-template <int DEPTH, int G, bool MISSING, bool TOPC>
+template <int DEPTH, int G, bool MISSING, int TOPL>
 __device__ __forceinline__ void traverse_group(uint32_t tree_abs, uint32_t s_base, uint32_t slot_lane,
                                                uint32_t col_mask, uint32_t miss_code, uint32_t (&a)[G],
                                                const TopWords& tw, int top_index) {
@@ -90,19 +92,26 @@ __device__ __forceinline__ void traverse_group(uint32_t tree_abs, uint32_t s_bas
     }
     return c;
   };
-  constexpr int kTop = TOPC ? (DEPTH >= 2 ? 2 : 1) : 0;   // levels decided on parameter words
-  if (TOPC) {
-    uint32_t F0[G], N1[G], F1[G];
+  // TOPL = levels decided on parameter words (constant bank): 0 = none, 1 = the root, 2 = root + level 1
+  constexpr int kTop = TOPL >= 2 && DEPTH >= 2 ? 2 : (TOPL >= 1 ? 1 : 0);
+  if (kTop > 0) {
+    uint32_t R0[G], F0[G];
     bool c0[G];
 #pragma unroll
-    for (int g = 0; g < G; ++g)   // root: warp-uniform word, the column offset is uniform arithmetic
-      F0[g] = lds_u32(s_base + ((tw.w[3 * (top_index + g)] & col_mask) | slot_lane));
+    for (int g = 0; g < G; ++g) R0[g] = tw.w[3 * (top_index + g)];
 #pragma unroll
-    for (int g = 0; g < G; ++g) {
-      c0[g] = right(F0[g], tw.w[3 * (top_index + g)]);
-      N1[g] = c0[g] ? tw.w[3 * (top_index + g) + 2] : tw.w[3 * (top_index + g) + 1];
-    }
-    if (DEPTH >= 2) {
+    for (int g = 0; g < G; ++g)   // root: warp-uniform word, the column offset is uniform arithmetic
+      F0[g] = lds_u32(s_base + ((R0[g] & col_mask) | slot_lane));
+#pragma unroll
+    for (int g = 0; g < G; ++g) c0[g] = right(F0[g], R0[g]);
+    if (kTop == 2) {
+      // level 1: a select between two warp-uniform words (ptxas makes it a pair of predicated constant
+      // loads behind the compare: a win with 12+ warps to cover them -- config 2 8.28 -> 8.10 ms, config 4
+      // 9.00 -> 8.84 -- a loss with 8: config 3 on 2M rows 11.57 -> 12.00 ms; the launcher decides)
+      uint32_t N1[G], F1[G];
+#pragma unroll
+      for (int g = 0; g < G; ++g)
+        N1[g] = c0[g] ? tw.w[3 * (top_index + g) + 2] : tw.w[3 * (top_index + g) + 1];
 #pragma unroll
       for (int g = 0; g < G; ++g) F1[g] = lds_u32(s_base + ((N1[g] & col_mask) | slot_lane));
 #pragma unroll
@@ -140,7 +149,6 @@ __device__ __forceinline__ void sts_u128(uint32_t addr, uint4 v) {
 template <int DEPTH, int G, bool LEAF_IDS, bool STAGED>
 __global__ void __launch_bounds__(kSmemMaxThreads, 1)
 k_smem_forest(const __grid_constant__ SmemParams p, const __grid_constant__ TopWords tw) {
-  constexpr bool TOPC = !LEAF_IDS;               // the checking path keeps every level in shared memory
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr uint32_t W = 1u << (DEPTH + 1);      // words per tree
   constexpr uint32_t L = 1u << DEPTH;            // bottom slots per tree
@@ -277,8 +285,15 @@ k_smem_forest(const __grid_constant__ SmemParams p, const __grid_constant__ TopW
       for (int t = 0; t < ntrees; t += G) {
         uint32_t a[G];
         const uint32_t tree_abs = s_base + forest_off + (uint32_t)t * W * 4u;
-        if (has_missing) traverse_group<DEPTH, G, true, TOPC>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a, tw, tree0 + t);
-        else traverse_group<DEPTH, G, false, TOPC>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a, tw, tree0 + t);
+        // (p.top_levels is launch-uniform; the leaf-id instantiation keeps every level in shared memory)
+        auto walk = [&](auto topl) {
+          constexpr int TOPL = LEAF_IDS ? 0 : decltype(topl)::value;
+          if (has_missing) traverse_group<DEPTH, G, true, TOPL>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a, tw, tree0 + t);
+          else traverse_group<DEPTH, G, false, TOPL>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a, tw, tree0 + t);
+        };
+        if (LEAF_IDS || p.top_levels == 0) walk(std::integral_constant<int, 0>{});
+        else if (p.top_levels == 1) walk(std::integral_constant<int, 1>{});
+        else walk(std::integral_constant<int, 2>{});
 #pragma unroll
         for (int g = 0; g < G; ++g) {
           acc += __uint_as_float(lds_u32(a[g]));   // a padding tree adds +0.0f: the sum keeps its bits

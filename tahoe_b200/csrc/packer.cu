@@ -860,8 +860,10 @@ static double plan_chunks_for(tahoe_forest* f, int depth, bool deep) {
   // visits at the plan's rate + one tile pass per chunk
   double best = 0.0;
   bool found = false;
-  for (int warps = kSmemMaxWarps; warps >= 4; warps >>= 1) {
+  static const int kWarpChoices[] = {16, 12, 8, 4};   // 12: slot-major tile regions only (the wide field needs 2^k slots)
+  for (int warps : kWarpChoices) {
     if (want_warps && warps != want_warps) continue;
+    if (warps == 12 && want_warps != 12) continue;   // built, not yet rated by smem_visit_cost: only on request (TAHOE_SMEM_PLAN)
     // deep: + lane-private rings of parked walks + the pairs' exchange floats
     const size_t bars = 1024 + (deep ? (size_t)warps * kDeepPend * 128 + 512 : 0);
     for (int staged = 0; staged <= 1; ++staged) {
@@ -873,7 +875,9 @@ static double plan_chunks_for(tahoe_forest* f, int depth, bool deep) {
       const int slots = deep ? (paired ? warps : warps * 2) : warps * (staged ? 1 : 2);
       // wide column field (column-major tile region) when rank + column bits leave room for it,
       // else the compact field with a slot-major region whose columns are padded to a power of two
-      const bool wide = f->rank_bits + f->col_bits + kQuantColShift + ilog2_c(slots) <= 32;
+      const bool pow2_slots = (slots & (slots - 1)) == 0;
+      if (deep && !pow2_slots) continue;
+      const bool wide = pow2_slots && f->rank_bits + f->col_bits + kQuantColShift + ilog2_c(slots) <= 32;
       const size_t cols_pad = (size_t)1 << ceil_log2((uint64_t)C);
       const size_t tiles = wide ? (size_t)slots * tile_bytes : (size_t)slots * cols_pad * 128;
       if ((size_t)f->smem_optin < tiles + bars + tree_bytes) continue;
@@ -928,6 +932,7 @@ static void read_tuning(Tuning& t) {
   if (const char* e = std::getenv("TAHOE_SPARSE_GROUP")) t.sparse_group = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_DIRECT_GROUP")) t.direct_group = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_TOP_TREES")) t.top_trees = std::atoi(e);
+  if (const char* e = std::getenv("TAHOE_TOP_LEVELS")) t.top_levels = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_HOST_SLAB")) std::sscanf(e, "%d,%d,%d", &t.slab_first, &t.slab_growth, &t.slab_cap);
 }
 
