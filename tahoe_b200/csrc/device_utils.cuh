@@ -8,9 +8,16 @@ namespace tahoe {
 
 // The reference's branch test (BaseTahoeTest.h:450-452; device Struct.h:976-978):
 // float subtract, fabs, compare with float(1e-6); ties go right; NaN goes left.
-__device__ __forceinline__ bool branch_right(float val, float thr, bool def_left, float missing) {
+// Extension (importers): a NaN sentinel means "NaN IS the missing value" -- the convention of the
+// trainers (XGBoost, LightGBM, scikit-learn).  In the reference a NaN sentinel matches nothing
+// (fabs(v - NaN) <= eps is false) and NaN features fall left; with a finite sentinel this is the
+// reference's test unchanged.
+__device__ __forceinline__ bool is_missing(float val, float missing) {
   const float eps = 1.0e-6f;
-  return (fabsf(val - missing) <= eps) ? !def_left : (val >= thr);
+  return (fabsf(val - missing) <= eps) || (missing != missing && val != val);
+}
+__device__ __forceinline__ bool branch_right(float val, float thr, bool def_left, float missing) {
+  return is_missing(val, missing) ? !def_left : (val >= thr);
 }
 
 struct Transform {   // forest::predict epilogue, Struct.h:196-209 / BaseTahoeTest.h:467-472

@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(kQuantThreads, 1) k_quantize(QuantParams p) {
   const float mn = p.lut_min[c], scale = p.lut_scale[c], fB = (float)B;
 
   auto rank_code = [&](float v, bool& any_missing) -> uint32_t {
-    if (fabsf(v - p.missing) <= 1.0e-6f) {      // BaseTahoeTest.h:451-452
+    if (is_missing(v, p.missing)) {             // BaseTahoeTest.h:451-452 (+ NaN sentinel: device_utils.cuh)
       any_missing = true;
       return p.miss_code;
     }

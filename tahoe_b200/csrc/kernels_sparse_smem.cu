@@ -73,7 +73,7 @@ __global__ void __launch_bounds__(256) k_float_tiles(const float* __restrict__ d
       for (int k = 0; k < 8; ++k)
         if (c0 + k < cols) {
           dst[(size_t)(c0 + k) * 32] = v[k];
-          miss |= fabsf(v[k] - missing) <= 1.0e-6f;
+          miss |= is_missing(v[k], missing);
         }
     }
     const bool any = __any_sync(0xffffffffu, miss);
@@ -247,7 +247,7 @@ __global__ void __launch_bounds__(kSparseWarps * 32, 1) k_sparse_smem(SparseSmem
             const float v = lds_f32(s_base + ((e[g].y & kTopColMask) | slot_lane_rel));   // a leaf reads column 0
             bool c = v >= __uint_as_float(e[g].x);
             if (MISSING) {
-              if (fabsf(v - p.missing) <= 1.0e-6f) c = !(e[g].y & kTopDefLeft);   // BaseTahoeTest.h:451-452
+              if (is_missing(v, p.missing)) c = !(e[g].y & kTopDefLeft);   // BaseTahoeTest.h:451-452
             }
             a2[g] = a[g] + (e[g].y >> 17) + (c ? 8u : 0u);
             const bool past = a2[g] >= lim[g];

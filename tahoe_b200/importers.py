@@ -12,7 +12,20 @@ array `tahoe_forest_create_sparse` takes -- {val, bits, left_idx}, children adja
   a float64 threshold.  For float32 x that is exactly `x < t'` with t' = the smallest float32 above
   the threshold, so the converted forest selects the same leaves as `model.apply(X)`, row by row.
 * XGBoost JSON (`from_xgboost_json`): `x < split_condition -> left`, missing -> `default_left`, all in
-  float32 -- the reference's rule as it stands.  Leaf values are the `split_conditions` of leaf nodes.
+  float32 -- the reference's rule as it stands.  Leaf values are the `split_conditions` of leaf nodes;
+  `dart` boosters scale every tree by its `weight_drop`; categorical splits are rejected.
+* LightGBM text (`from_lightgbm_text`, the `Booster.save_model("m.txt")` format): `x <= threshold -> left`
+  on double thresholds (same float32 conversion as scikit-learn); decision_type bit 1 = default_left,
+  bits 2-3 = missing type (NaN: the default direction; None: LightGBM turns NaN into 0.0, so the node's
+  default direction is where 0.0 goes; Zero: rejected -- "0.0 is missing" has no sentinel form).
+* Treelite JSON (`from_treelite_json`, `Model.dump_as_json()`): numerical test nodes with
+  `comparison_op` < / <= / > / >= (the last two by swapping the children), `default_left`, leaf values.
+
+MISSING VALUES.  The trainers' missing value is NaN; the reference's is a finite sentinel from the data
+header.  `Imported.forest()` therefore packs with the sentinel NaN by default, which this library reads
+as "NaN is the missing value" (csrc/device_utils.cuh is_missing; the reference would match nothing).
+Callers whose data marks absent features with a finite sentinel pass it as `missing=`; NaN inputs then
+take the reference's path (every test fails: left).
 
 Every importer returns an `Imported` record; `Imported.forest()` packs it through the C ABI.
 """
@@ -47,9 +60,12 @@ class Imported:
     def num_trees(self) -> int:
         return int(self.tree_offsets.shape[0] - 1)
 
-    def forest(self, missing: float = float("-inf")):
-        """Pack through the C ABI.  `missing` is the sentinel value the data uses for absent features
-        (data-file header line 3 in the reference, BaseTahoeTest.h:370-371)."""
+    def forest(self, missing: float = float("nan")):
+        """Pack through the C ABI.  `missing` is the value the data uses for absent features: NaN (the
+        default: the trainers' own convention -- NaN inputs take each node's default direction) or a
+        finite sentinel (data-file header line 3 in the reference, BaseTahoeTest.h:370-371)."""
+        if math.isinf(missing):
+            raise ValueError("an infinite sentinel matches nothing (inf - inf is NaN): pass NaN or a finite value")
         from . import api
         return api.Forest.from_sparse(self.nodes, self.tree_offsets, self.num_cols, weights=self.weights,
                                       missing=missing, output=self.output, threshold=self.threshold,
@@ -164,15 +180,32 @@ def from_xgboost_json(model) -> Imported:
         output, bias = OUT_RAW, base_score
     else:
         raise ValueError(f"unsupported objective {objective}")
-    trees = []
-    for t in gbm["trees"]:
-        left = np.asarray(t["left_children"], dtype=np.int64)
-        cond = np.asarray(t["split_conditions"], dtype=np.float32)
-        trees.append(_compact_tree(left, np.asarray(t["right_children"], dtype=np.int64),
-                                   np.asarray(t["split_indices"], dtype=np.int64), cond, cond,
-                                   np.asarray(t["default_left"], dtype=bool),
-                                   np.asarray(t.get("sum_hessian", np.ones(len(left))), dtype=np.float32)))
+    drop = _xgb_weight_drop(gb, len(gbm["trees"]))
+    trees = [_xgb_tree(t, drop[i]) for i, t in enumerate(gbm["trees"])]
     return _assemble(trees, int(lmp["num_feature"]), output=output, global_bias=bias)
+
+
+def _xgb_weight_drop(gb, num_trees):
+    """dart: prediction = sum_i weight_drop[i] * tree_i (gbtree: all ones)."""
+    if gb.get("name", "gbtree") != "dart":
+        return np.ones(num_trees, dtype=np.float64)
+    w = gb.get("weight_drop")
+    if w is None or len(w) != num_trees:
+        raise ValueError("dart booster without a weight_drop entry per tree")
+    return np.asarray(w, dtype=np.float64)
+
+
+def _xgb_tree(t, scale=1.0):
+    left = np.asarray(t["left_children"], dtype=np.int64)
+    split_type = np.asarray(t.get("split_type", np.zeros(len(left))), dtype=np.int64)
+    if np.any(split_type[left >= 0] != 0) or len(t.get("categories", [])) > 0:
+        raise ValueError("categorical splits (split_type != 0) have no threshold form: not supported")
+    cond = np.asarray(t["split_conditions"], dtype=np.float32)
+    leaf = (cond.astype(np.float64) * scale).astype(np.float32) if scale != 1.0 else cond
+    return _compact_tree(left, np.asarray(t["right_children"], dtype=np.int64),
+                         np.asarray(t["split_indices"], dtype=np.int64), cond, leaf,
+                         np.asarray(t["default_left"], dtype=bool),
+                         np.asarray(t.get("sum_hessian", np.ones(len(left))), dtype=np.float32))
 
 
 # ---- per-class outputs (SURVEY.md section 8f, row 3) ---------------------------------------------
@@ -264,17 +297,182 @@ def from_xgboost_json_classes(model) -> ImportedClasses:
         raise ValueError("not a multi-class booster: use from_xgboost_json")
     base_score = float(lmp.get("base_score", "0.5"))
     info = gbm.get("tree_info") or [i % K for i in range(len(gbm["trees"]))]
+    drop = _xgb_weight_drop(gb, len(gbm["trees"]))
     per_class = []
     for k in range(K):
-        trees = []
-        for t, cls in zip(gbm["trees"], info):
-            if int(cls) != k:
-                continue
-            left = np.asarray(t["left_children"], dtype=np.int64)
-            cond = np.asarray(t["split_conditions"], dtype=np.float32)
-            trees.append(_compact_tree(left, np.asarray(t["right_children"], dtype=np.int64),
-                                       np.asarray(t["split_indices"], dtype=np.int64), cond, cond,
-                                       np.asarray(t["default_left"], dtype=bool),
-                                       np.asarray(t.get("sum_hessian", np.ones(len(left))), dtype=np.float32)))
+        trees = [_xgb_tree(t, drop[i]) for i, (t, cls) in enumerate(zip(gbm["trees"], info)) if int(cls) == k]
         per_class.append(_assemble(trees, int(lmp["num_feature"]), output=OUT_RAW, global_bias=base_score))
     return ImportedClasses(per_class, "softmax")
+
+
+# ---- LightGBM model text ---------------------------------------------------------------------------
+def _lgb_parse(text: str):
+    """-> (header dict, list of per-tree dicts of raw strings)."""
+    header, trees, cur = {}, [], None
+    for line in text.splitlines():
+        line = line.strip()
+        if not line:
+            continue
+        if line == "end of trees":
+            break
+        if line.startswith("Tree="):
+            cur = {}
+            trees.append(cur)
+            continue
+        if "=" in line:
+            k, v = line.split("=", 1)
+            (header if cur is None else cur)[k] = v
+        elif cur is None:
+            header[line] = ""          # flags such as `average_output`
+    return header, trees
+
+
+def _lgb_tree(t):
+    """One LightGBM tree -> compact nodes.  Internal nodes 0..n-2, leaves addressed as ~index
+    (child < 0 -> leaf -child-1); rule `x <= threshold -> left`; decision_type: bit 0 categorical,
+    bit 1 default_left, bits 2-3 missing type (0 none, 1 zero, 2 NaN)."""
+    nl = int(t["num_leaves"])
+    leaf_value = np.asarray(t["leaf_value"].split(), dtype=np.float64)   # already carries the shrinkage
+    leaf_cnt = np.asarray(t.get("leaf_count", " ".join(["1"] * nl)).split(), dtype=np.float64)
+    if nl == 1:                                         # a stump: one leaf, no split arrays
+        return _compact_tree(np.array([-1]), np.array([-1]), np.array([0]), np.zeros(1, np.float32),
+                             leaf_value[:1], np.zeros(1, bool), leaf_cnt[:1])
+    ni = nl - 1
+    feat = np.asarray(t["split_feature"].split(), dtype=np.int64)
+    thr = np.asarray(t["threshold"].split(), dtype=np.float64)
+    dec = np.asarray(t["decision_type"].split(), dtype=np.int64)
+    lc = np.asarray(t["left_child"].split(), dtype=np.int64)
+    rc = np.asarray(t["right_child"].split(), dtype=np.int64)
+    int_cnt = np.asarray(t.get("internal_count", " ".join(["1"] * ni)).split(), dtype=np.float64)
+    if np.any(dec & 1):
+        raise ValueError("categorical splits (decision_type bit 0) have no threshold form: not supported")
+    mtype = (dec >> 2) & 3
+    if np.any(mtype == 1):
+        raise ValueError("missing type Zero (0.0 is a missing value) has no sentinel form: retrain with "
+                         "zero_as_missing=false")
+    # NaN: the stored default direction; None: LightGBM turns NaN into 0.0, which goes left iff 0.0 <= threshold
+    def_left = np.where(mtype == 2, (dec & 2) != 0, 0.0 <= thr)
+    unify = lambda c: np.where(c >= 0, c, ni + (-c - 1))       # noqa: E731  leaves after the internal nodes
+    left = np.concatenate([unify(lc), -np.ones(nl, np.int64)])
+    right = np.concatenate([unify(rc), -np.ones(nl, np.int64)])
+    z = np.zeros(nl)
+    return _compact_tree(left, right, np.concatenate([feat, z.astype(np.int64)]),
+                         np.concatenate([_f32_strictly_above(thr), z.astype(np.float32)]),
+                         np.concatenate([np.zeros(ni), leaf_value]),
+                         np.concatenate([def_left, z.astype(bool)]), np.concatenate([int_cnt, leaf_cnt]))
+
+
+def _lgb_load(model):
+    text = model
+    if "\n" not in model:
+        with open(model) as f:
+            text = f.read()
+    header, trees = _lgb_parse(text)
+    if not trees:
+        raise ValueError("no `Tree=` sections: not a LightGBM model text")
+    return header, trees
+
+
+def from_lightgbm_text(model) -> Imported:
+    """LightGBM `Booster.save_model()` text (a path, or the text itself).  Objectives: regression*
+    (raw sum), binary with sigmoid:1 (sigmoid of the sum); `average_output` (random-forest mode) -> AVG."""
+    header, trees = _lgb_load(model)
+    if int(header.get("num_tree_per_iteration", "1")) != 1:
+        raise ValueError("multi-class model: use from_lightgbm_text_classes")
+    obj = header.get("objective", "regression").split()
+    output = OUT_RAW
+    if obj[0] == "binary":
+        sig = [o for o in obj[1:] if o.startswith("sigmoid:")]
+        if sig and float(sig[0].split(":")[1]) != 1.0:
+            raise ValueError("binary objective with sigmoid != 1 is not a plain logistic link")
+        output = OUT_SIGMOID
+    elif not (obj[0].startswith("regression") or obj[0] in ("huber", "fair", "quantile", "mape", "custom")):
+        raise ValueError(f"unsupported objective {obj[0]}")
+    if "average_output" in header:
+        output |= OUT_AVG
+    return _assemble([_lgb_tree(t) for t in trees], int(header["max_feature_idx"]) + 1, output=output)
+
+
+def from_lightgbm_text_classes(model) -> ImportedClasses:
+    """multiclass / multiclassova LightGBM models: tree i belongs to class i % num_tree_per_iteration."""
+    header, trees = _lgb_load(model)
+    K = int(header.get("num_tree_per_iteration", "1"))
+    if K < 2:
+        raise ValueError("not a multi-class model: use from_lightgbm_text")
+    obj = header.get("objective", "multiclass").split()[0]
+    link = "softmax" if obj == "multiclass" else "raw"
+    cols = int(header["max_feature_idx"]) + 1
+    out = OUT_SIGMOID if obj == "multiclassova" else OUT_RAW
+    return ImportedClasses([_assemble([_lgb_tree(t) for t in trees[k::K]], cols, output=out) for k in range(K)], link)
+
+
+# ---- Treelite JSON ---------------------------------------------------------------------------------
+def from_treelite_json(model) -> Imported:
+    """`treelite.Model.dump_as_json()` (a path, the JSON text, or the parsed dict): trees of
+    numerical_test_node {split_feature_id, default_left, comparison_op, threshold, left_child, right_child}
+    and leaf nodes {leaf_value}.  `x op threshold` true -> left child.  Single-output models only."""
+    if not isinstance(model, dict):
+        text = model
+        if not model.lstrip().startswith("{"):
+            with open(model) as f:
+                text = f.read()
+        model = json.loads(text)
+    mp = model.get("model_param", {})
+    post = model.get("postprocessor", mp.get("pred_transform", "identity"))
+    if post in ("identity", "identity_multiclass"):
+        output = OUT_RAW
+    elif post == "sigmoid":
+        if float(model.get("sigmoid_alpha", mp.get("sigmoid_alpha", 1.0))) != 1.0:
+            raise ValueError("sigmoid_alpha != 1 is not a plain logistic link")
+        output = OUT_SIGMOID
+    else:
+        raise ValueError(f"unsupported postprocessor {post}")
+    if model.get("average_tree_output", False):
+        output |= OUT_AVG
+    nclass = model.get("num_class", [1])
+    if (max(nclass) if isinstance(nclass, list) else int(nclass)) > 1 or int(model.get("num_target", 1)) > 1:
+        raise ValueError("multi-class / multi-target Treelite models sum one forest per output; Tahoe's predict has one")
+    base = model.get("base_scores", [mp.get("global_bias", 0.0)])
+    trees = []
+    for t in model["trees"]:
+        nodes = {int(n["node_id"]): n for n in t["nodes"]}
+        ids = sorted(nodes)
+        root = int(t.get("root_id", ids[0]))
+        if ids[0] != root:                             # _compact_tree starts at index 0
+            ids.remove(root)
+            ids.insert(0, root)
+        pos = {nid: i for i, nid in enumerate(ids)}
+        n = len(ids)
+        left, right = -np.ones(n, np.int64), -np.ones(n, np.int64)
+        feat, thr = np.zeros(n, np.int64), np.zeros(n, np.float32)
+        leaf, dl, cover = np.zeros(n, np.float64), np.zeros(n, bool), np.ones(n, np.float64)
+        for nid in ids:
+            nd, i = nodes[nid], pos[nid]
+            cover[i] = float(nd.get("data_count", nd.get("sum_hess", 1.0)))
+            if "leaf_value" in nd:
+                v = nd["leaf_value"]
+                if isinstance(v, list):
+                    if len(v) != 1:
+                        raise ValueError("leaf vectors: one forest per output is needed")
+                    v = v[0]
+                leaf[i] = float(v)
+                continue
+            if nd.get("node_type", "numerical_test_node") != "numerical_test_node":
+                raise ValueError("categorical test nodes have no threshold form: not supported")
+            op = nd["comparison_op"]
+            lch, rch, d = pos[int(nd["left_child"])], pos[int(nd["right_child"])], bool(nd["default_left"])
+            if op in (">", ">="):                      # x > t -> left   ==   x <= t -> (old) right: swap the children
+                lch, rch, d = rch, lch, not d
+                op = "<=" if op == ">" else "<"
+            t64 = float(nd["threshold"])
+            if op == "<":                              # x < t  <=>  x < first float32 >= t
+                t32 = np.float32(t64)
+                thr[i] = t32 if float(t32) >= t64 else np.nextafter(t32, np.float32(np.inf))
+            elif op == "<=":
+                thr[i] = _f32_strictly_above(np.array([t64]))[0]
+            else:
+                raise ValueError(f"unsupported comparison_op {op}")
+            left[i], right[i], feat[i], dl[i] = lch, rch, int(nd["split_feature_id"]), d
+        sp, w, order = _compact_tree(left, right, feat, thr, leaf, dl, cover)
+        trees.append((sp, w, np.asarray(ids, dtype=np.int32)[order]))      # source ids = node_id
+    return _assemble(trees, int(model["num_feature"]), output=output, global_bias=float(base[0]))
