@@ -167,6 +167,7 @@ struct tahoe_forest {
 
   // SHARED_DATA plan (plan_shared_data, at create): teams of team_warps warps share a row
   int sd_teams = 0, sd_team_warps = 1, sd_group = 1;
+  int sd_row_bufs = 2;           // row buffers per team (1: single-buffered, twice the teams)
   int sd_top = 0;                // forest levels copied to shared memory
   bool sd_blocked = false;       // B32 two-level blocks below the top levels
   size_t sd_smem = 0;

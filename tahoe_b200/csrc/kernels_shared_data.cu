@@ -40,6 +40,8 @@ struct SharedDataParams {
   const uint4* blocks;       // [block][tpad][2]
   const int32_t* orig_bottom;  // [2^depth][tpad]
   int block_levels;          // (depth + 1 - top_levels) / 2 >= 1
+  int row_bufs;              // row buffers per team: 2 = the next row streams in under the walk; 1 = twice the teams,
+                             // a team's own load latency exposed, hidden by the other teams of the SM
 };
 
 __device__ __forceinline__ void ldg_block(const uint4* p, uint32_t (&w)[8]) {   // one 32-byte sector, one request
@@ -201,9 +203,10 @@ __global__ void __launch_bounds__(1024, 1) k_shared_data(SharedDataParams p) {
   const int team = warp / p.team_warps, wt = warp % p.team_warps;
   const int team_threads = 32 * p.team_warps;
   const uint32_t row_stride = ((uint32_t)p.cols * 4u + 15u) & ~15u;       // bytes, 16-aligned buffers
-  float* buf0 = reinterpret_cast<float*>(sd_smem + (size_t)team * 2 * row_stride);
-  double* partials = reinterpret_cast<double*>(sd_smem + (size_t)p.teams_per_block * 2 * row_stride) + team * 8;
-  const uint32_t bar0 = smem_u32(sd_smem) + (uint32_t)p.teams_per_block * (2 * row_stride + 64) + team * 16u;
+  const uint32_t nb = (uint32_t)p.row_bufs;
+  float* buf0 = reinterpret_cast<float*>(sd_smem + (size_t)team * nb * row_stride);
+  double* partials = reinterpret_cast<double*>(sd_smem + (size_t)p.teams_per_block * nb * row_stride) + team * 8;
+  const uint32_t bar0 = smem_u32(sd_smem) + (uint32_t)p.teams_per_block * (nb * row_stride + 64) + team * 16u;
   const size_t team_global = (size_t)blockIdx.x * p.teams_per_block + team;
   const size_t stride = (size_t)gridDim.x * p.teams_per_block;
   const uint32_t row_bytes = (uint32_t)p.cols * 4u;
@@ -269,7 +272,7 @@ __global__ void __launch_bounds__(1024, 1) k_shared_data(SharedDataParams p) {
     const size_t next = row + stride;
     if (TMA) {
       // buffer b^1 was last read for the previous row; the team barrier at its end released it
-      if (next < p.rows && wt == 0 && lane == 0) load_row_tma(next, b ^ 1);
+      if (nb == 2 && next < p.rows && wt == 0 && lane == 0) load_row_tma(next, b ^ 1);
       mbar_wait(bar0 + b * 8, (phase >> b) & 1u);
       phase ^= 1u << b;
     } else {
@@ -290,8 +293,10 @@ __global__ void __launch_bounds__(1024, 1) k_shared_data(SharedDataParams p) {
       double sum = 0.0;
       for (int w = 0; w < p.team_warps; ++w) sum += partials[b * 4 + w];   // fixed order: reproducible
       p.preds[row] = apply_transform((float)sum, p.tf);
+      // one buffer: the team barrier above released it; the next row starts to stream in now
+      if (TMA && nb == 1 && next < p.rows) load_row_tma(next, 0);
     }
-    b ^= 1;
+    b ^= (int)(nb - 1);
   }
 }
 
@@ -320,7 +325,8 @@ int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.teams_per_block = f->sd_teams;
   p.top_nodes = f->d_sd_top_nodes; p.blocks = f->d_sd_blocks; p.orig_bottom = f->d_sd_orig_bottom;
   p.block_levels = f->sd_blocked ? (f->depth + 1 - f->sd_top) / 2 : 0;
-  const size_t per_team = 2 * row_stride + 64 + 16;    // two row buffers, partials, mbarriers
+  p.row_bufs = f->sd_row_bufs;
+  const size_t per_team = (size_t)p.row_bufs * row_stride + 64 + 16;    // row buffers, partials, mbarriers
   p.top_off = (uint32_t)(((size_t)p.teams_per_block * per_team + 127) / 128 * 128);
   const size_t smem = f->sd_smem;
   // bulk copies need 16-byte rows at 16-byte addresses; short rows are cheaper through the LSU

@@ -64,9 +64,13 @@ int TAHOE_CAT(launch_smem_depth_, TAHOE_DEPTH)(tahoe_forest* f, const SmemParams
   if (f->sparse) { set_error("sparse tops deeper than 12 levels are not built"); return TAHOE_ERR_INVALID; }
 #endif
   // the leaf-id instantiation is the checking path: one tree at a time keeps the build small
-  if (p.leaf_ids) return f->staged ? go(k_smem_forest<D, 1, true, true>) : go(k_smem_forest<D, 1, true, false>);
-#define TAHOE_G_CASE(G) \
-  case G: return f->staged ? go(k_smem_forest<D, G, false, true>) : go(k_smem_forest<D, G, false, false>);
+  if (p.leaf_ids) return f->staged ? go(k_smem_forest<D, 1, true, true, 0>) : go(k_smem_forest<D, 1, true, false, 0>);
+  // p.top_levels: 2 = levels 0-1 of every tree from the kernel-parameter table, 0 = every level from shared memory
+#define TAHOE_G_CASE(G)                                                                                         \
+  case G:                                                                                                       \
+    if (p.top_levels >= 2)                                                                                      \
+      return f->staged ? go(k_smem_forest<D, G, false, true, 2>) : go(k_smem_forest<D, G, false, false, 2>);    \
+    return f->staged ? go(k_smem_forest<D, G, false, true, 0>) : go(k_smem_forest<D, G, false, false, 0>);
   switch (f->group) {
     TAHOE_G_CASE(1) TAHOE_G_CASE(2) TAHOE_G_CASE(3) TAHOE_G_CASE(4) TAHOE_G_CASE(5) TAHOE_G_CASE(6)
     default: break;

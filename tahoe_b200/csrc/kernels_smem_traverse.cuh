@@ -4,7 +4,6 @@
 #pragma once
 #include "device_utils.cuh"
 #include "forest.h"
-#include <type_traits>
 
 namespace tahoe {
 
@@ -21,7 +20,7 @@ struct SmemParams {
   int trees_per_chunk, num_chunks;
   int tree_base;            // index (in the whole padded forest) of this launch's first tree: qwords points at it
   int first_pass, last_pass;  // this launch holds the forest's first / last chunk (partial sums start / end here)
-  int top_levels;           // levels of every tree decided on the TopWords kernel parameter (0, 1 or 2): the plan's choice
+  int top_levels;           // levels of every tree decided on the TopWords kernel parameter (0 or 2): picks the instantiation
   uint32_t col_mask, miss_code;
   // tile region: word (col, slot, lane) at col*col_stride + slot*slot_stride + lane*4, and
   // (node & col_mask) == col*col_stride, so a lane's address is one AND-OR.  Two layouts:
@@ -146,9 +145,10 @@ __device__ __forceinline__ void sts_u128(uint32_t addr, uint4 v) {
   asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
-template <int DEPTH, int G, bool LEAF_IDS, bool STAGED>
+template <int DEPTH, int G, bool LEAF_IDS, bool STAGED, int TOPL>
 __global__ void __launch_bounds__(kSmemMaxThreads, 1)
 k_smem_forest(const __grid_constant__ SmemParams p, const __grid_constant__ TopWords tw) {
+  static_assert(!LEAF_IDS || TOPL == 0, "the leaf-id instantiation keeps every level in shared memory");
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr uint32_t W = 1u << (DEPTH + 1);      // words per tree
   constexpr uint32_t L = 1u << DEPTH;            // bottom slots per tree
@@ -285,15 +285,11 @@ k_smem_forest(const __grid_constant__ SmemParams p, const __grid_constant__ TopW
       for (int t = 0; t < ntrees; t += G) {
         uint32_t a[G];
         const uint32_t tree_abs = s_base + forest_off + (uint32_t)t * W * 4u;
-        // (p.top_levels is launch-uniform; the leaf-id instantiation keeps every level in shared memory)
-        auto walk = [&](auto topl) {
-          constexpr int TOPL = LEAF_IDS ? 0 : decltype(topl)::value;
-          if (has_missing) traverse_group<DEPTH, G, true, TOPL>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a, tw, tree0 + t);
-          else traverse_group<DEPTH, G, false, TOPL>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a, tw, tree0 + t);
-        };
-        if (LEAF_IDS || p.top_levels == 0) walk(std::integral_constant<int, 0>{});
-        else if (p.top_levels == 1) walk(std::integral_constant<int, 1>{});
-        else walk(std::integral_constant<int, 2>{});
+        // TOPL is a template parameter of the KERNEL: a run-time choice between the forms puts every form's
+        // unrolled walk into one kernel, and the walk then no longer fits the instruction cache (measured:
+        // config 3, 8 warps, 11.57 -> 12.1 ms with three forms inlined even when the old one is the one run)
+        if (has_missing) traverse_group<DEPTH, G, true, TOPL>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a, tw, tree0 + t);
+        else traverse_group<DEPTH, G, false, TOPL>(tree_abs, s_base, slot_lane, p.col_mask, p.miss_code, a, tw, tree0 + t);
 #pragma unroll
         for (int g = 0; g < G; ++g) {
           acc += __uint_as_float(lds_u32(a[g]));   // a padding tree adds +0.0f: the sum keeps its bits

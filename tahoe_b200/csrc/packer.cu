@@ -205,7 +205,9 @@ void plan_shared_data(tahoe_forest* f) {
   if (const char* e = std::getenv("TAHOE_SD_TEAM")) f->sd_team_warps = std::max(1, std::min(f->sd_team_warps, std::atoi(e)));
   const int per_warp = (slot_groups + f->sd_team_warps - 1) / f->sd_team_warps;   // slot groups each warp walks
   f->sd_group = per_warp >= 4 ? 4 : (per_warp >= 2 ? 2 : 1);
-  const size_t per_team = 2 * row_stride + 64 + 16;    // two row buffers, partials, mbarriers
+  f->sd_row_bufs = 2;
+  if (const char* e = std::getenv("TAHOE_SD_BUFS")) f->sd_row_bufs = std::atoi(e) == 1 ? 1 : 2;
+  const size_t per_team = (size_t)f->sd_row_bufs * row_stride + 64 + 16;    // row buffers, partials, mbarriers
   f->sd_teams = 0;
   f->sd_blocked = false;
   if (per_team + 128 > (size_t)f->smem_optin) return;  // SHARED_DATA not applicable: two rows do not fit

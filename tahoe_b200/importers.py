@@ -221,7 +221,7 @@ class ImportedClasses:
     def num_classes(self) -> int:
         return len(self.per_class)
 
-    def forests(self, missing: float = float("-inf")):
+    def forests(self, missing: float = float("nan")):
         return ClassForests([imp.forest(missing) for imp in self.per_class], self.link)
 
 

@@ -170,7 +170,7 @@ def _class_data(rows=900, cols=10, classes=4, seed=21):
     return X, y
 
 
-def _oracle_classes(oracle, imps, X, missing=-np.inf):
+def _oracle_classes(oracle, imps, X, missing=-np.inf):   # (the oracle takes any sentinel; -inf matches nothing)
     cols = [oracle.predict_sparse(i.nodes, i.tree_offsets, X, missing, output=i.output, global_bias=i.global_bias)
             for i in imps.per_class]
     out = np.stack(cols, axis=1).astype(np.float64)
