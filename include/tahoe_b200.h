@@ -153,6 +153,22 @@ int tahoe_predict_to(tahoe_forest_t* f, int strategy, const float* d_data, size_
  * owns the gathered output buffer of tahoe_predict_to).  Idempotent.  TAHOE_ERR_NOT_APPLICABLE when
  * the two devices have no peer path. */
 int tahoe_enable_peer_access(int peer_device);
+/* No counterpart in the reference.
+ * The shared-memory-forest predict (k_quantize + k_smem_forest, i.e. tahoe_predict with
+ * TAHOE_STRATEGY_SPLIT_SHARED_FOREST) for callers that cannot allocate: code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc.  It calls no cudaMalloc / cudaFree / allocating
+ * library routine: the kernels' scratch (the batch's rank tiles and per-tile flag words) is a file-scope
+ * static __device__ array of TAHOE_NO_ALLOC_SCRATCH_BYTES that every GPU loading the library holds until
+ * exit.  Limit: roundup(4 * tiles, 256) + tiles * 128 * num_cols <= TAHOE_NO_ALLOC_SCRATCH_BYTES with
+ * tiles = ceil(num_rows / 32) (232,608 rows of 18 columns, 149,600 of 28, 83,808 of 50); more rows -> TAHOE_ERR_INVALID with the limit in
+ * tahoe_last_error().  Forests without the rank-quantised layout -> TAHOE_ERR_NOT_APPLICABLE.  The handle's
+ * device must be current.  d_preds is both the partial-sum carrier and the output (local memory).  Same
+ * results as tahoe_predict, bit for bit.  ALL calls on one GPU share the array, which keeps the previous
+ * call's contents (what must start at zero is cleared on `stream` first): calls that overlap on the GPU --
+ * two streams, two handles, two host threads -- race. */
+#define TAHOE_NO_ALLOC_SCRATCH_BYTES (16u << 20)
+int tahoe_predict_no_alloc(tahoe_forest_t* f, const float* d_data, size_t num_rows, float* d_preds,
+                           void* stream);
 /* Same call with HOST buffers: slabs of rows are copied in, predicted and copied
  * out on internal streams so that PCIe transfers overlap the traversal.  This is
  * the harness path generate_data_from_file -> updateDevice -> predict -> updateHost

@@ -92,6 +92,7 @@ def lib() -> C.CDLL:
     L.tahoe_enable_peer_access.argtypes = [C.c_int]
     L.tahoe_measure_peaks.argtypes = [C.POINTER(Peaks)]
     L.tahoe_predict_host.argtypes = [vp, C.c_int, vp, sz, vp]
+    L.tahoe_predict_no_alloc.argtypes = [vp, vp, sz, vp, vp]
     L.tahoe_host_copy_baseline.argtypes = [vp, C.c_int, vp, sz, vp]
     L.tahoe_strategy_applicable.argtypes = [vp, C.c_int, sz]
     L.tahoe_select_strategy.argtypes = [vp, sz, C.POINTER(C.c_double)]
@@ -238,6 +239,13 @@ class Forest:
         _check(lib().tahoe_predict_to(self._h, strategy, _devptr(data), rows, _devptr(out), _devptr(partial),
                                       _devptr(leaf_ids), _stream_ptr(stream)))
         return out
+
+    def predict_no_alloc(self, data, preds, *, stream=None):
+        """tahoe_predict_no_alloc: the shared-memory-forest predict on the library's static device scratch
+        (no allocation inside the call; `preds` is the caller's).  Raises TahoeError beyond the row limit."""
+        rows = self._check_device_args(data, preds, None)
+        _check(lib().tahoe_predict_no_alloc(self._h, _devptr(data), rows, _devptr(preds), _stream_ptr(stream)))
+        return preds
 
     def predict_host(self, data, preds=None, *, strategy: int = AUTO, copy_only: bool = False):
         """Host buffers in, host buffers out (numpy or pinned torch CPU tensors).  copy_only: the same

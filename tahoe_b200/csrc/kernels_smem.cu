@@ -19,6 +19,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <string>
 
 #include "kernels_smem_traverse.cuh"   // SmemParams; the kernel itself is instantiated per depth
 
@@ -263,3 +264,79 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
 }
 
 }  // namespace tahoe
+
+// ---------------------------------------------------------------------------------------------
+// tahoe_predict_no_alloc -- SPLIT_SHARED_FOREST / SHARED_FOREST (k_quantize + k_smem_forest) for callers that
+// may not allocate: code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc.  No
+// counterpart in the reference.
+//
+// The scratch the two kernels share -- the batch's rank tiles [tiles][cols][32] and one flag word per tile,
+// which tahoe_predict keeps in a grow-only cudaMalloc'd workspace -- lives here in a file-scope __device__
+// array of kNoAllocScratchBytes (16 MiB: every GPU that loads this library holds it until exit).  In host
+// code the array's NAME is only a stand-in, not a device address: the address is asked for once per device,
+// with that device current, through cudaGetSymbolAddress, and that pointer is what the kernels get.
+// Every call shares the array and finds the previous call's contents in it: the flag words (which must start
+// at zero) are cleared on the stream before k_quantize, the rank tiles are fully overwritten.  Calls that
+// overlap on one GPU (two streams, two handles, two host threads) RACE on it.
+namespace tahoe {
+
+constexpr size_t kNoAllocScratchBytes = (size_t)TAHOE_NO_ALLOC_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char g_no_alloc_scratch[kNoAllocScratchBytes];
+
+constexpr int kNoAllocMaxDevices = 64;
+static void* g_no_alloc_ptr[kNoAllocMaxDevices];     // device address of the array, per device ordinal
+
+// layout: [tiles] flag words, rounded up to 256 bytes, then [tiles][cols][32] rank words
+static size_t no_alloc_flag_bytes(size_t tiles) { return (tiles * sizeof(uint32_t) + 255) / 256 * 256; }
+static size_t no_alloc_max_tiles(int cols) {
+  size_t t = kNoAllocScratchBytes / ((size_t)cols * 128 + sizeof(uint32_t));
+  while (t > 0 && no_alloc_flag_bytes(t) + t * (size_t)cols * 128 > kNoAllocScratchBytes) --t;
+  return t;
+}
+
+}  // namespace tahoe
+
+extern "C" int tahoe_predict_no_alloc(tahoe_forest_t* f, const float* d_data, size_t num_rows, float* d_preds,
+                                      void* stream) {
+  using namespace tahoe;
+  if (!f || (num_rows && (!d_data || !d_preds))) { set_error("null argument"); return TAHOE_ERR_INVALID; }
+  if (f->device < 0) { set_error("no CUDA device: this handle was packed on a GPU-less host and cannot predict"); return TAHOE_ERR_CUDA; }
+  if (!(f->quant || (f->qt && f->sp_use_qt)) || f->trees_per_chunk < 1) {
+    set_error("tahoe_predict_no_alloc runs the shared-memory-forest strategy: the forest needs the rank-quantised layout "
+              "(tahoe_strategy_applicable(f, TAHOE_STRATEGY_SPLIT_SHARED_FOREST, rows))");
+    return TAHOE_ERR_NOT_APPLICABLE;
+  }
+  if (num_rows == 0) return TAHOE_OK;
+  const int cols = f->params.num_cols;
+  const size_t tiles = (num_rows + 31) / 32;
+  const size_t max_tiles = no_alloc_max_tiles(cols);
+  if (tiles > max_tiles) {
+    set_error("tahoe_predict_no_alloc: " + std::to_string(num_rows) + " rows of " + std::to_string(cols) +
+              " columns need more than the " + std::to_string(kNoAllocScratchBytes >> 20) +
+              " MiB static scratch; the limit for this forest is " + std::to_string(max_tiles * 32) +
+              " rows per call (split the batch, or use tahoe_predict)");
+    return TAHOE_ERR_INVALID;
+  }
+  int dev = 0;
+  TAHOE_CUDA(cudaGetDevice(&dev));
+  if (dev != f->device) { set_error("tahoe_predict_no_alloc: the handle's device is not the current device"); return TAHOE_ERR_INVALID; }
+  if (dev >= kNoAllocMaxDevices) { set_error("tahoe_predict_no_alloc: device ordinal out of range"); return TAHOE_ERR_INVALID; }
+  if (!g_no_alloc_ptr[dev]) {   // set-up, once per device, that device current: the array's address ON this device
+    void* ptr = nullptr;
+    TAHOE_CUDA(cudaGetSymbolAddress(&ptr, g_no_alloc_scratch));
+    g_no_alloc_ptr[dev] = ptr;
+  }
+  unsigned char* base = static_cast<unsigned char*>(g_no_alloc_ptr[dev]);
+  // A workspace that is already large enough: ensure_workspace() returns on its first line (tiles <= cap_tiles
+  // was checked above), so nothing on this path calls cudaMalloc / cudaFree.  launch_smem_forest clears the
+  // flag words with cudaMemsetAsync on the stream before k_quantize.  Not ws[0]: no profiling events.
+  Workspace w{};
+  w.tile_flags = reinterpret_cast<uint32_t*>(base);
+  w.qtiles = reinterpret_cast<uint32_t*>(base + no_alloc_flag_bytes(tiles));
+  w.cap_tiles = tiles;
+  PredictArgs a{d_data, num_rows, d_preds, d_preds, nullptr, (cudaStream_t)stream, &w};
+  int launches = 0;
+  const int rc = launch_smem_forest(f, a, &launches);
+  f->last_launches = launches;
+  return rc;
+}
