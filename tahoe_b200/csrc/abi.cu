@@ -70,11 +70,11 @@ constexpr double kForestHalf = 80e6;        // forest bytes at which the L2-gath
 constexpr double kTeamLevel = 0.7e-6;       // SHARED_DATA: one tree level of a row's walk (latency-bound)
 constexpr double kSharedDataRate = 7.0e11;  // visits/s (slot-levels), SHARED_DATA
 constexpr double kRowStream = 3.7e12;       // B/s of sample rows through a TMA-fed SHARED_DATA kernel
-constexpr double kSmemVisit = 3.3e-13;      // s per visit, shared-memory forest, 16 warps x 6 trees (unit plan)
+constexpr double kSmemVisit = 2.9e-13;      // s per visit, shared-memory forest, 16 warps x 5-6 trees staged at depth 10 (unit plan)
 constexpr double kTileStream = 5.0e12;      // B/s of rank tiles re-read once per chunk (half hidden)
-constexpr double kChunkFixed = 1.2e-6;      // stage one chunk + barrier
-constexpr double kTileLevel = 40e-9;        // one level of one traversal group of a tile: this much alone ...
-constexpr double kTileLevelPerWarp = 7.5e-9;  // ... plus this per warp sharing the SM (16 warps: 160 ns, 8: 100 ns)
+constexpr double kChunkFixed = 4.0e-6;      // stage one chunk + barrier + the ragged end of a pass (config 3: 0.9 ms over 167 chunks)
+constexpr double kTileLevel = 30e-9;        // one level of one traversal group of a tile: this much alone ...
+constexpr double kTileLevelPerWarp = 5e-9;    // ... plus this per warp sharing the SM (16 warps: 110 ns, 8: 70 ns)
 constexpr double kQuantRate = 1.7e12;       // B/s in+out of k_quantize, whole table in shared memory
 constexpr double kQuantRateStrided = 1.0e12;   // ... every 2^k-th threshold there, rest probed in L2
 constexpr double kSparseVisit = 2.3e-12;      // s per node visit, sparse tree tops in shared memory (free-running lanes)
@@ -143,14 +143,16 @@ static int select_strategy(const tahoe_forest* f, size_t rows_, double* out) {
         } else {   // SHARED_FOREST / SPLIT_SHARED_FOREST: quantise pass + chunk passes
           // (sparse forests, QT layout: the same kernel on the dense tops + parked deep walks in L2)
           const int depth = f->qdepth;
-          const double plan = smem_visit_cost(f->warps, f->group, f->staged);
+          const double plan = smem_visit_cost(f->warps, f->group, f->staged) * (f->sparse ? 1.0 : smem_depth_factor(depth)) *
+                              ((f->warps >= 16 && !f->sparse) ? 1.0 - 0.25 * std::min(2, depth) / std::max(depth, 1) : 1.0);
+          const bool wide = f->tile_col_stride != 128u;
           const double visits = R * (double)f->qwords_trees * depth;               // padded depth
           const double tiles_per_warp = std::ceil(R / 32.0 / ((double)f->sm_count * f->warps));
           const double groups = (double)f->trees_per_chunk / std::max(f->group, 1);
           const double lat = f->num_chunks * (kChunkFixed + tiles_per_warp * groups * depth *
                                               (kTileLevel + kTileLevelPerWarp * f->warps));
           const double thr = kSmemVisit * (visits * plan + f->num_chunks * R *
-                             smem_tile_cost(f->params.num_cols, f->staged, f->trees_per_chunk, depth)) +
+                             smem_tile_cost(f->params.num_cols, f->staged, f->trees_per_chunk, depth, wide)) +
                              (f->sparse ? R * T * f->qt_overflow * kDeepWalk : 0.0);
           const double quant = kLaunch + R * C * 8.0 / (f->quant_stride > 1 ? kQuantRateStrided : kQuantRate);
           t = kLaunch + quant + std::max(lat, thr);

@@ -229,7 +229,8 @@ int upload(tahoe_forest* f);
 void plan_chunks(tahoe_forest* f);
 void plan_shared_data(tahoe_forest* f);   // teams / top levels / B32 blocks; needs host.inter and query_device
 double smem_visit_cost(int warps, int group, bool staged);   // relative cost of a node visit under a plan
-double smem_tile_cost(int cols, bool staged, int trees_per_chunk, int depth);   // one tile pass, in node visits
+double smem_tile_cost(int cols, bool staged, int trees_per_chunk, int depth, bool wide);   // one tile pass, in node visits
+double smem_depth_factor(int depth);   // bank conflicts of the deep levels, relative to depth 10
 
 // launchers (kernels_*.cu); each returns a status and adds to *launches
 struct PredictArgs {

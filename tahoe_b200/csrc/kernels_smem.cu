@@ -195,8 +195,8 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.trees_per_chunk = f->trees_per_chunk; p.num_chunks = f->num_chunks;
   p.col_mask = f->col_mask; p.miss_code = f->miss_code;
   // parameter-table levels pay when enough warps cover the predicated constant loads (config 2, 16 warps:
-  // 8.23 -> 7.82 ms; config 4: 9.00 -> 8.84) and lose with 8 warps (config 3: 11.57 -> 12.0 on 2M rows)
-  p.top_levels = f->tune.top_levels >= 0 ? (f->tune.top_levels >= 1 ? 2 : 0) : (f->warps >= 12 ? 2 : 0);
+  // 8.23 -> 7.82 ms; config 4: 9.00 -> 8.84) and lose with fewer (config 3, 8 warps: 11.57 -> 12.0 ms on 2M rows; 12 warps: 11.01 -> 11.19)
+  p.top_levels = f->tune.top_levels >= 0 ? (f->tune.top_levels >= 1 ? 2 : 0) : (f->warps >= 16 ? 2 : 0);
   p.col_stride = f->tile_col_stride; p.slot_stride = f->tile_slot_stride; p.tile_region = f->tile_region;
   p.preds = a.preds; p.out = a.out; p.leaf_ids = a.leaf_ids;
   p.leaf_origin = f->d_leaf_origin;

@@ -202,10 +202,16 @@ void plan_shared_data(tahoe_forest* f) {
   const size_t row_stride = (row_bytes + 15) & ~(size_t)15;
   const int slot_groups = tpad / 32;
   f->sd_team_warps = slot_groups >= 4 ? 4 : (slot_groups >= 2 ? 2 : 1);
+  // Wide rows (config 1: 12 KB): the row buffers bound the teams in flight, and the kernel streams rows from
+  // HBM.  Teams of two warps with ONE buffer each put 15 rows in flight per SM instead of 8; a team's own
+  // load latency is exposed but the other teams cover it (B200, 50K x 3072: 0.168 -> 0.142 ms; one-warp
+  // teams 0.152, two-warp teams with two buffers 0.165 -- gpurun_out/r2d_c1.log, profiles/r02_c1_plans.md).
+  const bool wide_rows = row_stride >= 4096 && slot_groups >= 2;
+  if (wide_rows) f->sd_team_warps = 2;
   if (const char* e = std::getenv("TAHOE_SD_TEAM")) f->sd_team_warps = std::max(1, std::min(f->sd_team_warps, std::atoi(e)));
   const int per_warp = (slot_groups + f->sd_team_warps - 1) / f->sd_team_warps;   // slot groups each warp walks
   f->sd_group = per_warp >= 4 ? 4 : (per_warp >= 2 ? 2 : 1);
-  f->sd_row_bufs = 2;
+  f->sd_row_bufs = wide_rows ? 1 : 2;
   if (const char* e = std::getenv("TAHOE_SD_BUFS")) f->sd_row_bufs = std::atoi(e) == 1 ? 1 : 2;
   const size_t per_team = (size_t)f->sd_row_bufs * row_stride + 64 + 16;    // row buffers, partials, mbarriers
   f->sd_teams = 0;
@@ -818,22 +824,35 @@ static void plan_sparse_qtop(tahoe_forest* f) {
 // number of dependent chains in flight per SM (warps x trees per thread); TMA-fed tiles with few
 // warps lose the overlap that hides the bulk copies.
 double smem_visit_cost(int warps, int G, bool staged) {
+  // B200 measurements, round 2 (gpurun_out r2d_plans: config 2 on 5M rows, config 3 on 2M rows, one-copy
+  // TMA tiles, parameter-table levels at >= 16 warps), unit = 16 warps x 5-6 trees staged (2.9e-13 s):
+  //   chains (warps x trees per thread) in flight per SM   24: 1.75   32: 1.45   40: 1.12   >= 48: 1.0
+  //   TMA, 3 trees per group: 1.10 (16 x 3 on config 3); staged G = 4: 1.04 (config 2)
+  //   staged 12 warps: 1.03 (config 2: 7.93 vs 7.72 ms), 8 warps: 1.04
   const int chains = warps * G;
-  const double by_chains = chains >= 40 ? 1.0 : chains >= 32 ? 1.12 : chains >= 24 ? 1.25
-                         : chains >= 16 ? 1.5 : chains >= 12 ? 1.9 : 2.5;
-  if (staged) return by_chains * (warps >= 16 ? 1.0 : (warps >= 8 ? 1.04 : 1.15));
-  // TMA-fed tiles: the group size matters at every warp count, and few warps lose the overlap
-  static const double by_group[kMaxGroup + 1] = {0.0, 1.50, 1.25, 1.124, 1.096, 1.056, 1.0};
-  return by_group[G] * (warps >= 16 ? 1.0 : (warps >= 8 ? 1.3 : 2.4));
+  const double by_chains = chains >= 48 ? 1.0 : chains >= 40 ? 1.12 : chains >= 32 ? 1.45 : chains >= 24 ? 1.75
+                         : chains >= 16 ? 2.2 : chains >= 12 ? 2.6 : 3.0;
+  if (staged) {
+    const double by_group = G >= 5 ? 1.0 : G == 4 ? 1.04 : G == 3 ? 1.1 : G == 2 ? 1.2 : 1.4;
+    return by_chains * by_group * (warps >= 16 ? 1.0 : (warps >= 12 ? 1.03 : (warps >= 8 ? 1.04 : 1.15)));
+  }
+  static const double by_group[kMaxGroup + 1] = {0.0, 1.50, 1.25, 1.10, 1.0, 1.0, 1.0};
+  return by_chains * by_group[G];
 }
 
-// One pass of a row's tile through a chunk, in node-visit units: the staged path moves the tile
-// through the LSU twice (C/4 128-bit loads + stores per lane = 2C wavefronts against ~2.5 per
-// visit) plus its fixed part; bulk copies cost the fixed part only, but are exposed when a chunk
-// holds too little work per tile to hide them.
-double smem_tile_cost(int cols, bool staged, int trees_per_chunk, int depth) {
-  if (staged) return (2.0 * cols + 20.0) / 2.5;
-  return 8.0 + ((double)trees_per_chunk * depth < 100.0 ? 45.0 : 0.0);
+// Deep trees cost more per visit: the bottom levels of a 2^12-leaf tree are random words (bank conflicts:
+// 3.3 shared-memory wavefronts per level on config 3 against 2.8 on config 2) and the pipe runs at 82 %
+// instead of 92 %.  Measured 1.4 at depth 12 relative to depth 10; applied to the visits, not to the tile passes.
+double smem_depth_factor(int depth) { return 1.0 + 0.2 * std::max(0, depth - 10); }
+
+// One pass of a row's tile through a chunk, in node-visit units.  Staged: the tile moves through the LSU
+// twice (C/4 128-bit loads + stores per lane) plus a fixed part -- fitted 14.4 visits at 18 columns, 19.5 at
+// 28.  TMA: the fixed part only when the tile is ONE bulk copy (slot-major region); the column-major
+// (wide) region takes one 128-byte copy per column (fitted 22 visits at 18 columns).
+double smem_tile_cost(int cols, bool staged, int trees_per_chunk, int depth, bool wide) {
+  if (staged) return 0.256 * (2.0 * cols + 20.0);
+  (void)trees_per_chunk; (void)depth;   // (4 trees x 12 levels per tile already hide the copy: 12 warps x 4 trees on config 3)
+  return 8.0 + (wide ? 0.8 * cols : 0.0);
 }
 
 void plan_chunks(tahoe_forest* f) { plan_chunks_for(f, f->depth, false); }
@@ -865,7 +884,6 @@ static double plan_chunks_for(tahoe_forest* f, int depth, bool deep) {
   static const int kWarpChoices[] = {16, 12, 8, 4};   // 12: slot-major tile regions only (the wide field needs 2^k slots)
   for (int warps : kWarpChoices) {
     if (want_warps && warps != want_warps) continue;
-    if (warps == 12 && want_warps != 12) continue;   // built, not yet rated by smem_visit_cost: only on request (TAHOE_SMEM_PLAN)
     // deep: + lane-private rings of parked walks + the pairs' exchange floats
     const size_t bars = 1024 + (deep ? (size_t)warps * kDeepPend * 128 + 512 : 0);
     for (int staged = 0; staged <= 1; ++staged) {
@@ -892,11 +910,13 @@ static double plan_chunks_for(tahoe_forest* f, int depth, bool deep) {
         int tpc = std::min(max_tpc / G * G, tpad);
         const int chunks = (tpad + tpc - 1) / tpc;     // balance: same chunk count, even whole groups
         tpc = ((tpad + chunks - 1) / chunks + G - 1) / G * G;
-        double visits = (double)tpad * std::max(depth, 1) * smem_visit_cost(warps, G, staged != 0);
+        double visits = (double)tpad * std::max(depth, 1) * smem_visit_cost(warps, G, staged != 0) * smem_depth_factor(depth);
+        // levels 0-1 from the kernel-parameter table (launch_smem_forest: plans of >= 16 warps)
+        if (warps >= 16 && !deep) visits *= 1.0 - 0.25 * std::min(2, depth) / std::max(depth, 1);
         // deep: the per-group work, and 8 warps (64 staging registers) cover less of it than 16 (measured 1.17x)
         if (deep) visits = visits * (warps <= 8 ? 1.12 : 1.0) + (double)tpad / G * kDeepGroupVisits;
         // (deep: the tile of a pass is committed from registers under the deep walks of the tile before)
-        const double cost = visits + (double)chunks * (deep ? 10.0 : smem_tile_cost(C, staged != 0, tpc, std::max(depth, 1)));
+        const double cost = visits + (double)chunks * (deep ? 10.0 : smem_tile_cost(C, staged != 0, tpc, std::max(depth, 1), wide));
         if (!found || cost < best) {
           found = true; best = cost;
           f->warps = warps; f->staged = staged != 0; f->slots = slots; f->group = G;
