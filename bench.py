@@ -408,7 +408,17 @@ def main():
         ms_total = float(t.item())
     ms_step = ms_total / args.steps
     value = total_rows / (ms_step * 1e-3)
+    # untimed check of the fused gather: every rank predicts its rows once more into LOCAL memory; the sum of those
+    # (all-reduced) must be what rank 0 finds in the gathered buffer, and rank 0's own rows must match bit for bit
+    local_check = forest.predict(data, strategy=strategy)
+    local_sum = torch.tensor([float(local_check.double().sum().item())], dtype=torch.float64, device="cuda")
+    if distributed:
+        dist.all_reduce(local_sum, op=dist.ReduceOp.SUM)
     gathered_checksum = float(gather.full.double().sum().item()) if rank == 0 else None
+    gathered_ok = None
+    if rank == 0:
+        gathered_ok = bool(torch.equal(gather.full[lo:hi], local_check)) and \
+            abs(gathered_checksum - float(local_sum.item())) <= 1e-9 * max(1.0, abs(gathered_checksum))
 
     # ---- end to end: pinned host rows in, host scores out, every step (this rank's shard)
     e2e = None
@@ -435,7 +445,11 @@ def main():
 
         copy_s = timed_host(True)       # the same slabs, copies only: the bound of this path
         e2e_s = timed_host(False)
-        same = bool(torch.equal(h_preds.cuda(), gather.full[lo:hi] if rank == 0 else h_preds.cuda()))
+        same = bool(torch.equal(h_preds.cuda(), local_check))
+        if distributed:
+            ok_t = torch.tensor([1 if same else 0], dtype=torch.int32, device="cuda")
+            dist.all_reduce(ok_t, op=dist.ReduceOp.MIN)
+            same = bool(ok_t.item())
         h2d = rows * cfg["cols"] * 4
         e2e = {"value": total_rows * e2e_steps / e2e_s, "unit": "samples/s",
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": rows * 4,
@@ -470,7 +484,8 @@ def main():
                              f"vs {peaks['l2_bytes'] / 1e6:.0f} MB L2)",
                 "forest_chunks": info.num_chunks, "trees_per_chunk": info.trees_per_chunk,
                 "plan": {"warps": info.smem_warps, "staged": info.smem_staged, "group": info.smem_group},
-                "node_bytes": 4, "rank_bits": info.rank_bits, "gathered_checksum": gathered_checksum},
+                "node_bytes": 4, "rank_bits": info.rank_bits, "gathered_checksum": gathered_checksum,
+                "gathered_matches_local_predicts": gathered_ok},
             "roofline": {"bound": "l2" if fits_l2 else "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": _traffic(WORKLOAD), "kernel": "k_smem_forest",
                          "kernel_ms": trav_ms, "quantize_ms": (q_ms / n_prof if n_prof else None),
@@ -521,6 +536,12 @@ def main():
         _emit(line)
     if distributed:
         dist.barrier()
+    if rank != 0:
+        gather.close()          # mappings first, then (after the barrier) the owner's buffer
+    if distributed:
+        dist.barrier()
+    gather.close()
+    if distributed:
         dist.destroy_process_group()
 
 

@@ -122,6 +122,19 @@ int tahoe_forest_create_dense(const tahoe_dense_node_t* nodes, const tahoe_fores
 int tahoe_forest_create_sparse(const tahoe_sparse_node_t* nodes, const float* weights,
                                const int64_t* tree_offsets, const tahoe_forest_params_t* params,
                                tahoe_forest_t** out);
+/* Per-class outputs.  The reference sums every tree into ONE scalar, also for multi-class
+ * models (Struct.h:196-209, BaseTahoeTest.h:462-466); here tree t belongs to class tree_class[t] in
+ * [0, num_classes) (XGBoost's `tree_info`), all classes share one packed forest -- one set of rank tables, so
+ * ONE quantise pass per batch serves every class -- and tahoe_predict_classes writes d_out[k][row] = the score of
+ * class k: its trees summed in their given order, then the handle's output transform (AVG divides by the class's
+ * own tree count).  d_out: device, [num_classes][num_rows] float32.  Strategies: DIRECT,
+ * SHARED_DATA_PER_THREAD, SHARED_FOREST / SPLIT_SHARED_FOREST (AUTO: the model's pick; others fall back to DIRECT).
+ * tahoe_predict on such a handle still returns the sum over all classes. */
+int tahoe_forest_create_sparse_classes(const tahoe_sparse_node_t* nodes, const float* weights,
+                                       const int64_t* tree_offsets, const tahoe_forest_params_t* params,
+                                       int num_classes, const int32_t* tree_class, tahoe_forest_t** out);
+int tahoe_predict_classes(tahoe_forest_t* f, int strategy, const float* d_data, size_t num_rows, float* d_out,
+                          void* stream);
 /* The reference leaks its forest (`delete forest`, BaseTahoeTest.h:709, no destructor). */
 void tahoe_forest_destroy(tahoe_forest_t* f);
 int tahoe_forest_info(const tahoe_forest_t* f, tahoe_forest_info_t* info);
@@ -149,6 +162,16 @@ int tahoe_predict(tahoe_forest_t* f, int strategy, const float* d_data, size_t n
  * threads at once. */
 int tahoe_predict_to(tahoe_forest_t* f, int strategy, const float* d_data, size_t num_rows,
                      float* d_out, float* d_partial, int32_t* d_leaf_ids, void* stream);
+/* The gathered output buffer of the multi-GPU path: the owner (rank 0) creates it on its device and
+ * gets a CUDA IPC handle (TAHOE_IPC_HANDLE_BYTES opaque bytes) to pass to the other processes by any means;
+ * every other process opens it WITH ITS OWN DEVICE CURRENT and gets a pointer its kernels can store through
+ * (peer mapping over NVLink / NVSwitch), to be used as d_out of tahoe_predict_to at its row offset.
+ * release: owner = 1 frees the buffer, owner = 0 closes the mapping.  No reference counterpart (single device,
+ * BaseTahoeTest.h:78). */
+#define TAHOE_IPC_HANDLE_BYTES 64
+int tahoe_gather_buffer_create(size_t num_floats, float** d_ptr, unsigned char* ipc_handle);
+int tahoe_gather_buffer_open(const unsigned char* ipc_handle, float** d_ptr);
+int tahoe_gather_buffer_release(float* d_ptr, int owner);
 /* Lets kernels launched on the CURRENT device store into memory of `peer_device` (the device that
  * owns the gathered output buffer of tahoe_predict_to).  Idempotent.  TAHOE_ERR_NOT_APPLICABLE when
  * the two devices have no peer path. */

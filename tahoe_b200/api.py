@@ -84,12 +84,17 @@ def lib() -> C.CDLL:
     vp, sz = C.c_void_p, C.c_size_t
     L.tahoe_forest_create_dense.argtypes = [vp, C.POINTER(ForestParams), C.POINTER(vp)]
     L.tahoe_forest_create_sparse.argtypes = [vp, vp, vp, C.POINTER(ForestParams), C.POINTER(vp)]
+    L.tahoe_forest_create_sparse_classes.argtypes = [vp, vp, vp, C.POINTER(ForestParams), C.c_int, vp, C.POINTER(vp)]
+    L.tahoe_predict_classes.argtypes = [vp, C.c_int, vp, sz, vp, vp]
     L.tahoe_forest_destroy.argtypes = [vp]
     L.tahoe_forest_destroy.restype = None
     L.tahoe_forest_info.argtypes = [vp, C.POINTER(ForestInfo)]
     L.tahoe_predict.argtypes = [vp, C.c_int, vp, sz, vp, vp, vp]
     L.tahoe_predict_to.argtypes = [vp, C.c_int, vp, sz, vp, vp, vp, vp]
     L.tahoe_enable_peer_access.argtypes = [C.c_int]
+    L.tahoe_gather_buffer_create.argtypes = [sz, C.POINTER(vp), C.c_char_p]
+    L.tahoe_gather_buffer_open.argtypes = [C.c_char_p, C.POINTER(vp)]
+    L.tahoe_gather_buffer_release.argtypes = [vp, C.c_int]
     L.tahoe_measure_peaks.argtypes = [C.POINTER(Peaks)]
     L.tahoe_predict_host.argtypes = [vp, C.c_int, vp, sz, vp]
     L.tahoe_predict_no_alloc.argtypes = [vp, vp, sz, vp, vp]
@@ -178,6 +183,38 @@ class Forest:
             offs.ctypes.data_as(C.c_void_p), C.byref(ps), C.byref(h)))
         return cls(h, T, num_cols)
 
+    @classmethod
+    def from_sparse_classes(cls, nodes: np.ndarray, tree_offsets: np.ndarray, num_cols: int, tree_class, num_classes: int,
+                            *, weights=None, missing: float = 0.0, output: int = 0, threshold: float = 0.0,
+                            global_bias: float = 0.0) -> "Forest":
+        """One packed forest for a K-class ensemble (tahoe_forest_create_sparse_classes): tree t scores class tree_class[t]."""
+        nodes = np.ascontiguousarray(nodes, dtype=SPARSE_NODE)
+        offs = np.ascontiguousarray(tree_offsets, dtype=np.int64)
+        tc = np.ascontiguousarray(tree_class, dtype=np.int32)
+        T = offs.shape[0] - 1
+        assert tc.shape[0] == T
+        w = None if weights is None else np.ascontiguousarray(weights, dtype=np.float32)
+        ps = ForestParams(int(offs[-1]), 0, T, num_cols, 0, output, threshold, global_bias, 0, missing)
+        h = C.c_void_p()
+        _check(lib().tahoe_forest_create_sparse_classes(
+            nodes.ctypes.data_as(C.c_void_p), None if w is None else w.ctypes.data_as(C.c_void_p),
+            offs.ctypes.data_as(C.c_void_p), C.byref(ps), num_classes, tc.ctypes.data_as(C.c_void_p), C.byref(h)))
+        f = cls(h, T, num_cols)
+        f.num_classes = num_classes
+        return f
+
+    def predict_classes(self, data, out=None, *, strategy: int = AUTO, stream=None):
+        """-> float32 [num_classes, rows]: one score per class (tahoe_predict_classes; one quantise pass for all classes)."""
+        import torch
+        rows = self._check_device_args(data, None, None)
+        K = self.num_classes
+        if out is None:
+            out = torch.empty((K, rows), dtype=torch.float32, device=data.device)
+        if not (out.is_cuda and out.dtype == torch.float32 and out.is_contiguous() and out.numel() >= K * rows):
+            raise ValueError("out must be a contiguous float32 CUDA tensor of num_classes x rows elements")
+        _check(lib().tahoe_predict_classes(self._h, strategy, _devptr(data), rows, _devptr(out), _stream_ptr(stream)))
+        return out
+
     def close(self):
         if self._h:
             lib().tahoe_forest_destroy(self._h)
@@ -234,7 +271,9 @@ class Forest:
         scratch for the partial sums between forest chunks (None: owned by the handle)."""
         rows = self._check_device_args(data, partial, leaf_ids)
         import torch
-        if not (out.is_cuda and out.dtype == torch.float32 and out.is_contiguous() and out.numel() >= rows):
+        # (an int is a raw device pointer: a peer-mapped buffer of another GPU, which torch cannot own as a tensor here)
+        if not isinstance(out, int) and not (out.is_cuda and out.dtype == torch.float32 and out.is_contiguous()
+                                             and out.numel() >= rows):
             raise ValueError("out must be a contiguous float32 CUDA tensor of at least `rows` elements")
         _check(lib().tahoe_predict_to(self._h, strategy, _devptr(data), rows, _devptr(out), _devptr(partial),
                                       _devptr(leaf_ids), _stream_ptr(stream)))
@@ -295,6 +334,34 @@ def measure_peaks() -> dict:
     pk = Peaks()
     _check(lib().tahoe_measure_peaks(C.byref(pk)))
     return {k: getattr(pk, k) for k, _ in Peaks._fields_}
+
+
+IPC_HANDLE_BYTES = 64
+
+
+def gather_buffer_create(num_floats: int):
+    """-> (device pointer, IPC handle bytes): the owner's gathered-output buffer (tahoe_gather_buffer_create)."""
+    p, h = C.c_void_p(), C.create_string_buffer(IPC_HANDLE_BYTES)
+    _check(lib().tahoe_gather_buffer_create(num_floats, C.byref(p), h))
+    return int(p.value), h.raw
+
+
+def gather_buffer_open(handle: bytes) -> int:
+    """Another process's gathered-output buffer, mapped for kernels of the CURRENT device -> device pointer."""
+    p = C.c_void_p()
+    _check(lib().tahoe_gather_buffer_open(C.create_string_buffer(handle, IPC_HANDLE_BYTES), C.byref(p)))
+    return int(p.value)
+
+
+def gather_buffer_release(ptr: int, owner: bool) -> None:
+    _check(lib().tahoe_gather_buffer_release(C.c_void_p(ptr), int(owner)))
+
+
+class DevicePointer:
+    """A raw device pointer to `size` float32 words as an object torch.as_tensor() understands."""
+
+    def __init__(self, ptr: int, size: int):
+        self.__cuda_array_interface__ = {"shape": (size,), "typestr": "<f4", "data": (ptr, False), "version": 2}
 
 
 def enable_peer_access(peer_device: int) -> None:

@@ -246,6 +246,87 @@ int tahoe_forest_create_sparse(const tahoe_sparse_node_t* nodes, const float* we
   return TAHOE_OK;
 }
 
+static int predict_on_ws0(tahoe_forest* f, int strategy, PredictArgs a);   // below, with tahoe_predict
+
+int tahoe_forest_create_sparse_classes(const tahoe_sparse_node_t* nodes, const float* weights,
+                                       const int64_t* tree_offsets, const tahoe_forest_params_t* params,
+                                       int num_classes, const int32_t* tree_class, tahoe_forest_t** out) {
+  if (!nodes || !params || !out || !tree_offsets || !tree_class) { set_error("null argument"); return TAHOE_ERR_INVALID; }
+  *out = nullptr;
+  const int T = params->num_trees;
+  if (num_classes < 1 || T < 1) { set_error("need at least one class and one tree"); return TAHOE_ERR_INVALID; }
+  std::vector<int32_t> class_first((size_t)num_classes + 1, 0), class_real((size_t)num_classes, 0);
+  for (int t = 0; t < T; ++t) {
+    if (tree_class[t] < 0 || tree_class[t] >= num_classes) { set_error("tree_class out of range"); return TAHOE_ERR_INVALID; }
+    ++class_real[(size_t)tree_class[t]];
+  }
+  // trees grouped by class (stable: training order inside a class), every class padded to a multiple of kClassPad
+  // with single-leaf trees worth +0.0f, so that a class is whole traversal groups under every plan
+  try {
+    std::vector<tahoe_sparse_node_t> pn;
+    std::vector<float> pw;
+    std::vector<int64_t> po(1, 0);
+    for (int k = 0; k < num_classes; ++k) {
+      class_first[(size_t)k] = (int32_t)po.size() - 1;
+      for (int t = 0; t < T; ++t) {
+        if (tree_class[t] != k) continue;
+        const int64_t b = tree_offsets[t], e = tree_offsets[t + 1];
+        if (e <= b) { set_error("empty tree"); return TAHOE_ERR_INVALID; }
+        pn.insert(pn.end(), nodes + b, nodes + e);
+        if (weights) pw.insert(pw.end(), weights + b, weights + e);
+        po.push_back((int64_t)pn.size());
+      }
+      while ((((int64_t)po.size() - 1) - class_first[(size_t)k]) % kClassPad) {
+        pn.push_back(tahoe_sparse_node_t{0.0f, (int32_t)0x80000000, 0});
+        if (weights) pw.push_back(1.0f);
+        po.push_back((int64_t)pn.size());
+      }
+    }
+    class_first[(size_t)num_classes] = (int32_t)po.size() - 1;
+    tahoe_forest_params_t pp = *params;
+    pp.num_trees = (int)po.size() - 1;
+    pp.num_nodes = (int)pn.size();
+    const int rc = tahoe_forest_create_sparse(pn.data(), weights ? pw.data() : nullptr, po.data(), &pp, out);
+    if (rc != TAHOE_OK) return rc;
+    (*out)->class_first = class_first;
+    (*out)->class_real = class_real;
+  } catch (const std::bad_alloc&) {
+    set_error("out of host memory while packing"); return TAHOE_ERR_NOMEM;
+  }
+  return TAHOE_OK;
+}
+
+int tahoe_predict_classes(tahoe_forest_t* f, int strategy, const float* d_data, size_t num_rows, float* d_out,
+                          void* stream) {
+  if (!f || (num_rows && (!d_data || !d_out))) { set_error("null argument"); return TAHOE_ERR_INVALID; }
+  if (f->class_first.empty()) { set_error("not a class forest: create it with tahoe_forest_create_sparse_classes"); return TAHOE_ERR_INVALID; }
+  if (strategy == TAHOE_STRATEGY_AUTO) strategy = select_strategy(f, num_rows, nullptr);
+  const bool smem = strategy == TAHOE_STRATEGY_SHARED_FOREST || strategy == TAHOE_STRATEGY_SPLIT_SHARED_FOREST;
+  // class ranges need the layouts that address trees one by one: the compact nodes (DIRECT / PER_THREAD) and the
+  // quantised tops (shared-memory forest); anything else falls back to DIRECT
+  if ((smem && !(f->qt && f->sp_use_qt)) || strategy == TAHOE_STRATEGY_SHARED_DATA) strategy = TAHOE_STRATEGY_DIRECT;
+  const int K = (int)f->class_real.size();
+  int total = 0;
+  for (int k = 0; k < K; ++k) {
+    PredictArgs a{d_data, num_rows, d_out + (size_t)k * num_rows, d_out + (size_t)k * num_rows, nullptr,
+                  (cudaStream_t)stream, &f->ws[0]};
+    a.tree_lo = f->class_first[(size_t)k];
+    a.tree_hi = f->class_first[(size_t)k + 1];
+    a.avg_trees = std::max(1, f->class_real[(size_t)k]);
+    a.reuse_tiles = smem && k > 0;        // ONE quantise pass for the K classes
+    // every class is a whole forest of its own to the kernels: first and last chunk pass inside its range
+    const int rc = k == 0 ? predict_on_ws0(f, strategy, a) : predict_impl(f, strategy, a);
+    if (rc != TAHOE_OK) return rc;
+    total += f->last_launches;
+  }
+  if (f->device >= 0) {   // the event predict_on_ws0 recorded covered class 0 only
+    Workspace& w = f->ws[0];
+    TAHOE_CUDA(cudaEventRecord(w.done, (cudaStream_t)stream));
+  }
+  f->last_launches = total;
+  return TAHOE_OK;
+}
+
 void tahoe_forest_destroy(tahoe_forest_t* f) {
   if (!f) return;
   cudaFree(f->d_heap); cudaFree(f->d_sparse); cudaFree(f->d_sparse8); cudaFree(f->d_tree_offsets); cudaFree(f->d_inter);
@@ -326,6 +407,37 @@ int tahoe_predict_to(tahoe_forest_t* f, int strategy, const float* d_data, size_
   }
   PredictArgs a{d_data, num_rows, d_partial, d_out, d_leaf_ids, (cudaStream_t)stream, &f->ws[0]};
   return predict_on_ws0(f, strategy, a);
+}
+
+int tahoe_gather_buffer_create(size_t num_floats, float** d_ptr, unsigned char* ipc_handle) {
+  if (!d_ptr || !ipc_handle) { set_error("null argument"); return TAHOE_ERR_INVALID; }
+  static_assert(sizeof(cudaIpcMemHandle_t) == TAHOE_IPC_HANDLE_BYTES, "IPC handle size");
+  *d_ptr = nullptr;
+  // its own cudaMalloc (not a slice of a caching allocator's block): the IPC handle then names exactly this buffer
+  TAHOE_CUDA(cudaMalloc((void**)d_ptr, std::max<size_t>(num_floats, 1) * sizeof(float)));
+  cudaIpcMemHandle_t h;
+  const cudaError_t e = cudaIpcGetMemHandle(&h, *d_ptr);
+  if (e != cudaSuccess) { cudaFree(*d_ptr); *d_ptr = nullptr; return cuda_fail(e, "cudaIpcGetMemHandle"); }
+  std::memcpy(ipc_handle, &h, sizeof(h));
+  return TAHOE_OK;
+}
+
+int tahoe_gather_buffer_open(const unsigned char* ipc_handle, float** d_ptr) {
+  if (!d_ptr || !ipc_handle) { set_error("null argument"); return TAHOE_ERR_INVALID; }
+  *d_ptr = nullptr;
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, ipc_handle, sizeof(h));
+  // opened with the CONSUMER's device current: the lazy flag maps the owner's memory into this device's address
+  // space over NVLink.  (A mapping made in the owner device's context -- what torch's CUDA IPC does -- cannot be
+  // stored to by kernels that run on another GPU: illegal address, found on two B200s.)
+  TAHOE_CUDA(cudaIpcOpenMemHandle((void**)d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return TAHOE_OK;
+}
+
+int tahoe_gather_buffer_release(float* d_ptr, int owner) {
+  if (!d_ptr) return TAHOE_OK;
+  TAHOE_CUDA(owner ? cudaFree(d_ptr) : cudaIpcCloseMemHandle(d_ptr));
+  return TAHOE_OK;
 }
 
 int tahoe_enable_peer_access(int peer_device) {

@@ -120,6 +120,7 @@ struct Tuning {
   int slab_first = 0, slab_growth = 0, slab_cap = 0;   // TAHOE_HOST_SLAB="first,growth%,cap" (waves of tiles); 0 = from the model
 };
 
+constexpr int kClassPad = 12;               // lcm of the traversal group sizes the sparse plans use (2, 4, 6) and of 1, 2, 3, 4, 6
 constexpr int kHostSlots = 3;
 constexpr int kProfRing = 512;         // per-kernel CUDA-event triples kept while profiling is on
 
@@ -171,6 +172,11 @@ struct tahoe_forest {
   int sd_top = 0;                // forest levels copied to shared memory
   bool sd_blocked = false;       // B32 two-level blocks below the top levels
   size_t sd_smem = 0;
+
+  // per-class outputs (tahoe_forest_create_sparse_classes): class k owns packed trees
+  // [class_first[k], class_first[k+1]) -- its real trees followed by single-leaf (+0.0f) padding trees up to a
+  // multiple of kClassPad, so that a class is whole traversal groups under every plan -- class_real[k] of them real
+  std::vector<int32_t> class_first, class_real;
 
   tahoe::HostPack host;
   tahoe::TopWords top_words_all{};   // host.top3 when the whole forest fits one launch's table
@@ -241,6 +247,12 @@ struct PredictArgs {
   int32_t* leaf_ids;
   cudaStream_t stream;
   Workspace* ws;
+  // tahoe_predict_classes: only trees [tree_lo, tree_hi) of the packed forest (0, 0 = all of them), the AVG
+  // transform divides by avg_trees (0 = params.num_trees), and the rank tiles of an earlier launch on the same
+  // stream and workspace are reused (the quantise pass runs once per batch, not once per class)
+  int tree_lo = 0, tree_hi = 0;
+  int avg_trees = 0;
+  bool reuse_tiles = false;
 };
 int launch_direct(tahoe_forest* f, const PredictArgs& a, bool rows_in_smem, int* launches);
 int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches);

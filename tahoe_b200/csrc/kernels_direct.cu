@@ -200,8 +200,13 @@ int launch_direct(tahoe_forest* f, const PredictArgs& a, bool rows_in_smem, int*
   p.tree_offsets = f->d_tree_offsets;
   p.preds = a.out;     // one pass: the kernel's only store is the final score
   p.leaf_ids = a.leaf_ids;
-  p.tf = Transform{f->params.output, (float)f->params.num_trees, f->params.threshold,
+  p.tf = Transform{f->params.output, (float)(a.avg_trees ? a.avg_trees : f->params.num_trees), f->params.threshold,
                    f->params.global_bias};
+  if (a.tree_hi > a.tree_lo) {   // one class of a class forest (sparse layouts: trees are addressed through tree_offsets)
+    if (!f->sparse || a.leaf_ids) { set_error("tree ranges need a sparse forest and no leaf ids"); return TAHOE_ERR_INVALID; }
+    p.tree_offsets += a.tree_lo;
+    p.num_trees = a.tree_hi - a.tree_lo;
+  }
   const size_t blocks = (a.rows + kDirectThreads - 1) / kDirectThreads;
   if (blocks > 0x7FFFFFFFull) { set_error("too many rows for one launch"); return TAHOE_ERR_INVALID; }
   const size_t smem = rows_in_smem ? (size_t)p.cols * kDirectThreads * sizeof(float) : 0;

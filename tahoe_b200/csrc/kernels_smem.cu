@@ -182,11 +182,13 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
     ++f->prof_count;
     TAHOE_CUDA(cudaEventRecord(ev[0], a.stream));
   }
-  TAHOE_CUDA(cudaMemsetAsync(a.ws->tile_flags, 0, tiles * sizeof(uint32_t), a.stream));
-  k_quantize<<<qgrid, kQuantThreads, f->quant_smem, a.stream>>>(q);
+  if (!a.reuse_tiles) {   // (a later class of tahoe_predict_classes walks the tiles its first class quantised)
+    TAHOE_CUDA(cudaMemsetAsync(a.ws->tile_flags, 0, tiles * sizeof(uint32_t), a.stream));
+    k_quantize<<<qgrid, kQuantThreads, f->quant_smem, a.stream>>>(q);
+    ++*launches;
+  }
   if (ev) TAHOE_CUDA(cudaEventRecord(ev[1], a.stream));
   TAHOE_CUDA(cudaGetLastError());
-  ++*launches;
 
   SmemParams p{};
   p.qtiles = a.ws->qtiles; p.tile_flags = a.ws->tile_flags; p.num_tiles = tiles; p.rows = a.rows;
@@ -201,7 +203,7 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.preds = a.preds; p.out = a.out; p.leaf_ids = a.leaf_ids;
   p.leaf_origin = f->d_leaf_origin;
   p.deep_blocks = f->d_sp_qblocks; p.block_offsets = f->d_sp_qblock_offsets; p.block_orig = f->d_sp_qblock_orig;
-  p.tf = Transform{f->params.output, (float)f->params.num_trees, f->params.threshold,
+  p.tf = Transform{f->params.output, (float)(a.avg_trees ? a.avg_trees : f->params.num_trees), f->params.threshold,
                    f->params.global_bias};
   // Row batches (tuning knob, off by default): walk the rows in batches whose rank tiles stay
   // L2-resident between chunk passes.  Measured on B200 (profiles/r01_row_batch.log): never a win --
@@ -219,7 +221,15 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   // level from shared memory and is never split.)
   const size_t W = (size_t)1 << (f->qdepth + 1);
   const int top_limit = std::max(f->trees_per_chunk, std::min(kTopTrees, f->tune.top_trees > 0 ? f->tune.top_trees : kTopTrees));
-  const int chunks_per_launch = p.leaf_ids ? f->num_chunks : std::max(1, top_limit / f->trees_per_chunk);
+  // the trees this call walks: all of them, or one class (whole traversal groups: kClassPad)
+  const bool ranged = a.tree_hi > a.tree_lo;
+  if (ranged && (p.leaf_ids || (a.tree_lo % f->group) || ((a.tree_hi - a.tree_lo) % f->group))) {
+    set_error("tree ranges must be whole traversal groups and carry no leaf ids"); return TAHOE_ERR_INVALID;
+  }
+  const int range_lo = ranged ? a.tree_lo : 0;
+  const int range_trees = ranged ? a.tree_hi - a.tree_lo : f->qwords_trees;
+  const int range_chunks = ranged ? (range_trees + f->trees_per_chunk - 1) / f->trees_per_chunk : f->num_chunks;
+  const int chunks_per_launch = p.leaf_ids ? range_chunks : std::max(1, top_limit / f->trees_per_chunk);
   if (f->trees_per_chunk > kTopTrees && !p.leaf_ids) { set_error("chunk larger than the top-level table"); return TAHOE_ERR_INVALID; }
   for (size_t t0 = 0; t0 < tiles && rc == TAHOE_OK; t0 += batch_tiles) {
     SmemParams b = p;
@@ -232,17 +242,17 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
     if (p.leaf_ids) b.leaf_ids = p.leaf_ids + t0 * 32 * (size_t)p.num_trees;
     const unsigned grid = (unsigned)std::min<size_t>((size_t)f->sm_count,
                                                      (b.num_tiles + f->warps - 1) / f->warps);
-    for (int c0 = 0; c0 < f->num_chunks && rc == TAHOE_OK; c0 += chunks_per_launch) {
+    for (int c0 = 0; c0 < range_chunks && rc == TAHOE_OK; c0 += chunks_per_launch) {
       SmemParams r = b;
-      r.num_chunks = std::min(chunks_per_launch, f->num_chunks - c0);
-      r.tree_base = c0 * f->trees_per_chunk;
-      r.padded_trees = std::min(r.num_chunks * f->trees_per_chunk, f->qwords_trees - r.tree_base);
+      r.num_chunks = std::min(chunks_per_launch, range_chunks - c0);
+      r.tree_base = range_lo + c0 * f->trees_per_chunk;
+      r.padded_trees = std::min(r.num_chunks * f->trees_per_chunk, range_trees - c0 * f->trees_per_chunk);
       r.qwords = p.qwords + (size_t)r.tree_base * W;
       r.first_pass = c0 == 0;
-      r.last_pass = c0 + r.num_chunks >= f->num_chunks;
+      r.last_pass = c0 + r.num_chunks >= range_chunks;
       const TopWords* tw = &f->top_words_all;           // whole forest in one launch: prepared at upload
       TopWords local;
-      if (!p.leaf_ids && chunks_per_launch < f->num_chunks) {
+      if (!p.leaf_ids && (r.tree_base != 0 || r.padded_trees != f->qwords_trees || f->qwords_trees > kTopTrees)) {
         std::memcpy(local.w, f->host.top3.data() + (size_t)r.tree_base * 3, (size_t)r.padded_trees * 3 * sizeof(uint32_t));
         tw = &local;
       }

@@ -222,7 +222,35 @@ class ImportedClasses:
         return len(self.per_class)
 
     def forests(self, missing: float = float("nan")):
+        """K handles, one per class (K quantise passes per batch): kept as the cross-check of `forest()`."""
         return ClassForests([imp.forest(missing) for imp in self.per_class], self.link)
+
+    def forest(self, missing: float = float("nan")):
+        """ONE packed forest for the K classes through the C ABI (tahoe_forest_create_sparse_classes): one set of
+        rank tables, so one quantise pass per batch serves every class.  The classes must share their output
+        transform; a per-class bias (multi-class gradient boosting priors) is added to the K scores afterwards."""
+        from . import api
+        if math.isinf(missing):
+            raise ValueError("an infinite sentinel matches nothing (inf - inf is NaN): pass NaN or a finite value")
+        first = self.per_class[0]
+        if any(i.output != first.output or i.threshold != first.threshold or i.num_cols != first.num_cols
+               for i in self.per_class):
+            raise ValueError("the classes of one packed forest share output transform and width")
+        if (first.output & (OUT_SIGMOID | OUT_THRESHOLD)) and any(i.global_bias != first.global_bias for i in self.per_class):
+            raise ValueError("per-class biases do not commute with a sigmoid / threshold transform")
+        nodes = np.concatenate([i.nodes for i in self.per_class])
+        weights = np.concatenate([i.weights for i in self.per_class])
+        sizes = np.concatenate([np.diff(i.tree_offsets) for i in self.per_class])
+        offs = np.zeros(sizes.shape[0] + 1, dtype=np.int64)
+        offs[1:] = np.cumsum(sizes)
+        tree_class = np.concatenate([np.full(i.num_trees, k, dtype=np.int32) for k, i in enumerate(self.per_class)])
+        common_bias = first.global_bias if all(i.global_bias == first.global_bias for i in self.per_class) else 0.0
+        f = api.Forest.from_sparse_classes(nodes, offs, first.num_cols, tree_class, self.num_classes, weights=weights,
+                                           missing=missing, output=first.output, threshold=first.threshold,
+                                           global_bias=common_bias)
+        extra = None if common_bias == first.global_bias and all(i.global_bias == common_bias for i in self.per_class) \
+            else np.array([i.global_bias for i in self.per_class], dtype=np.float32)
+        return PackedClassForest(f, self.link, extra)
 
 
 class ClassForests:
@@ -239,6 +267,21 @@ class ClassForests:
         for k, f in enumerate(self.forests):
             f.predict(data, out[k], strategy=api.AUTO if strategy is None else strategy)
         out = out.t()
+        return torch.softmax(out, dim=1) if self.link == "softmax" else out
+
+
+class PackedClassForest:
+    """One handle for K classes: predict -> [R, K] (device rows in, device scores out)."""
+
+    def __init__(self, forest, link="raw", class_bias=None):
+        self.forest, self.link, self.class_bias = forest, link, class_bias
+
+    def predict(self, data, *, strategy=None):
+        import torch
+        from . import api
+        out = self.forest.predict_classes(data, strategy=api.AUTO if strategy is None else strategy).t()
+        if self.class_bias is not None:
+            out = out + torch.from_numpy(self.class_bias).to(out.device)[None, :]
         return torch.softmax(out, dim=1) if self.link == "softmax" else out
 
 

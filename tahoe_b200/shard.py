@@ -74,8 +74,9 @@ class ShardedForest:
 
 class PeerGather:
     """Gather of the ranks' score slices WITHOUT a collective and WITHOUT a copy: `dst`
-    owns one device buffer for the whole batch, every other rank maps it through CUDA IPC once (the
-    handle travels as a pickled object over the process group -- gloo is enough), and
+    owns one device buffer for the whole batch (tahoe_gather_buffer_create), every other rank maps it through
+    CUDA IPC once, with its own device current (tahoe_gather_buffer_open; the 64-byte handle travels as a
+    pickled object over the process group -- gloo is enough), and
     `tahoe_predict_to` makes the kernels' last-chunk epilogue store each final score straight into
     that buffer over NVLink / NVSwitch (4 bytes per row, posted writes, never read back).  The partial
     sums the multi-pass strategies carry between forest chunks stay in a local scratch.  The only
@@ -89,28 +90,35 @@ class PeerGather:
     def __init__(self, total_rows: int, dst: int = 0):
         import torch
         import torch.distributed as dist
-        from torch.multiprocessing.reductions import reduce_tensor
+        from . import api
         self.rank = dist.get_rank() if dist.is_initialized() else 0
         self.world = dist.get_world_size() if dist.is_initialized() else 1
         self.dst, self.total = dst, int(total_rows)
         self.lo, self.hi = row_range(self.rank, self.world, self.total)
         dev = torch.device("cuda", torch.cuda.current_device())
-        self.full = None
+        self.owner = self.rank == dst
         box = [None]
-        if self.rank == dst:
-            self.full = torch.empty(self.total, dtype=torch.float32, device=dev)
-            box[0] = reduce_tensor(self.full)          # (rebuild function, IPC handle + geometry)
+        if self.owner:      # a cudaMalloc of its own, so that the IPC handle names exactly this buffer
+            self.ptr, box[0] = api.gather_buffer_create(self.total)
         if self.world > 1:
             dist.broadcast_object_list(box, src=dst)
-            if self.rank != dst:
-                rebuild, args = box[0]
-                self.full = rebuild(*args)             # dst's memory, mapped into this process
-        if self.full.device != dev:                    # our kernels will store into dst's memory
-            from . import api
-            api.enable_peer_access(self.full.device.index)
-        self.out = self.full[self.lo:self.hi]          # this rank's rows of the gathered buffer (peer memory off dst)
+            if not self.owner:
+                # dst's memory, mapped for the kernels of THIS rank's GPU (opened with this device current)
+                self.ptr = api.gather_buffer_open(box[0])
+        # dst reads the gathered scores through a tensor view of its own buffer; the other ranks only ever hand the
+        # raw pointer (+ their row offset) to tahoe_predict_to as d_out
+        self.full = torch.as_tensor(api.DevicePointer(self.ptr, self.total), device=dev) if self.owner else None
+        self.out = self.ptr + 4 * self.lo              # this rank's rows of the gathered buffer
         self.partial = torch.empty(self.hi - self.lo, dtype=torch.float32, device=dev)   # local scratch
 
     def predict(self, forest, data, **kw):
         """One predict of this rank's rows; the final store of every row goes to dst's buffer."""
         return forest.predict_to(data, self.out, partial=self.partial, **kw)
+
+    def close(self):
+        """Collective in spirit: every rank closes its mapping before the owner frees the buffer (callers barrier)."""
+        from . import api
+        if getattr(self, "ptr", None):
+            self.full = None
+            api.gather_buffer_release(self.ptr, self.owner)
+            self.ptr = None

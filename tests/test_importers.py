@@ -477,3 +477,51 @@ def test_nan_is_the_missing_value_on_the_gpu(oracle):
     tl = importers.from_treelite_json(_treelite_fixture())
     got = tl.forest().predict(torch.from_numpy(Xl).cuda()).cpu().numpy()
     assert np.allclose(got, np.array([_treelite_eval(_treelite_fixture(), r) for r in Xl]), rtol=0, atol=1e-6)
+
+
+def test_class_forest_packs_through_the_c_abi():
+    """tahoe_forest_create_sparse_classes: classes padded to whole traversal groups with single-leaf trees."""
+    X, y = _class_data(rows=600)
+    m = sk.RandomForestClassifier(n_estimators=10, max_depth=5, random_state=2).fit(X, y)
+    pf = importers.from_sklearn_classes(m).forest()
+    inf = pf.forest.info()
+    assert pf.forest.num_classes == 4 and inf.num_trees == 4 * 12            # 10 real + 2 padding trees per class
+    assert inf.num_nodes == 4 * (sum(e.tree_.node_count for e in m.estimators_) + 2)
+
+
+@pytest.mark.gpu
+def test_per_class_outputs_in_one_handle_on_the_gpu(oracle):
+    """tahoe_predict_classes (one packed forest, ONE quantise pass) against K separate handles and against the
+    trainer's own predict_proba, through every strategy it supports, incl. NaN inputs."""
+    import torch
+    from tahoe_b200 import api
+    X, y = _class_data(rows=20000, cols=16, classes=3, seed=5)
+    rng = np.random.default_rng(8)
+    X[rng.uniform(size=X.shape) < 0.05] = np.nan
+    m = sk.RandomForestClassifier(n_estimators=50, max_depth=9, random_state=1).fit(X[:3000], y[:3000])
+    imps = importers.from_sklearn_classes(m)
+    packed, separate = imps.forest(), imps.forests()
+    x = torch.from_numpy(X).cuda()
+    want = m.predict_proba(X)
+    sep = separate.predict(x, strategy=api.DIRECT).cpu().numpy()
+    assert np.allclose(sep, want, rtol=0, atol=5e-6)
+    ran = 0
+    for s in (api.DIRECT, api.SHARED_DATA_PER_THREAD, api.SPLIT_SHARED_FOREST, api.AUTO):
+        if s != api.AUTO and not packed.forest.applicable(s, X.shape[0]):
+            continue
+        got = packed.predict(x, strategy=s).cpu().numpy()
+        assert got.shape == (X.shape[0], 3)
+        assert np.allclose(got, want, rtol=0, atol=5e-6), s
+        if s in (api.DIRECT, api.SHARED_DATA_PER_THREAD):                     # same trees in the same order: same bits
+            assert np.array_equal(got.view(np.uint32), sep.view(np.uint32)), s
+        if s == api.SPLIT_SHARED_FOREST:                                      # one k_quantize + one traverse per class
+            assert packed.forest.launches() == 1 + 3
+        ran += 1
+    assert ran >= 3
+    # multi-class gradient boosting: per-class priors, softmax link; a small batch (fewer rows than one wave)
+    Xs, ys = _class_data(rows=700, cols=10, classes=4, seed=21)
+    g = sk.GradientBoostingClassifier(n_estimators=12, max_depth=3, random_state=3).fit(Xs, ys)
+    pg = importers.from_sklearn_classes(g).forest()
+    for s in (api.DIRECT, api.SPLIT_SHARED_FOREST):
+        got = pg.predict(torch.from_numpy(Xs).cuda(), strategy=s).cpu().numpy()
+        assert np.allclose(got, g.predict_proba(Xs), rtol=0, atol=5e-6), s

@@ -42,6 +42,10 @@ def _worker(rank, world, port, out_path):
             if rank == 0:
                 np.save(out_path + f".{s}.npy", pg.full.cpu().numpy())
             dist.barrier()
+        if rank != 0:
+            pg.close()
+        dist.barrier()
+        pg.close()
     finally:
         dist.destroy_process_group()
 
