@@ -115,6 +115,8 @@ struct Tuning {
   int sparse_grid = 0;                 // TAHOE_SPARSE_GRID: cap on k_sparse_smem's grid
   int sparse_group = 3;                // TAHOE_SPARSE_GROUP: sequences per lane of k_sparse_smem
   int direct_group = 0;                // TAHOE_DIRECT_GROUP: 4 = four walks per thread, 1 = one; 0 = by batch size
+  bool no_reorder = false, no_simhash = false;   // TAHOE_NO_REORDER / TAHOE_NO_SIMHASH: ablation of the I8 layout (tools/probe_reorder.py)
+  int cluster = -1;                    // TAHOE_CLUSTER: CTAs per cluster of the k_smem_forest cluster pipeline (0/1 = off, -1 = by plan)
   int top_levels = -1;                 // TAHOE_TOP_LEVELS: 0/1/2 tree levels from the kernel-parameter table; -1 = by plan
   int top_trees = 0;                   // TAHOE_TOP_TREES: cap on the trees per launch of k_smem_forest (test knob: forces the split)
   int slab_first = 0, slab_growth = 0, slab_cap = 0;   // TAHOE_HOST_SLAB="first,growth%,cap" (waves of tiles); 0 = from the model

@@ -220,6 +220,7 @@ __global__ void __launch_bounds__(1024, 1) k_shared_data(SharedDataParams p) {
     for (int i = threadIdx.x; i < n_top; i += blockDim.x) dst[i] = __ldg(src + i);
   }
   __syncthreads();
+  // (a 16th team on hardware barrier 0 fits shared memory for config 1 and was measured: 0.1453 vs 0.1426 ms with 15)
 
   auto load_row_tma = [&](size_t row, int b) {       // team warp 0, lane 0
     fence_proxy_async();

@@ -205,6 +205,16 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.deep_blocks = f->d_sp_qblocks; p.block_offsets = f->d_sp_qblock_offsets; p.block_orig = f->d_sp_qblock_orig;
   p.tf = Transform{f->params.output, (float)(a.avg_trees ? a.avg_trees : f->params.num_trees), f->params.threshold,
                    f->params.global_bias};
+  // Cluster pipeline (kernels_smem_cluster.cuh): TMA tiles in the slot-major region with a padding column row to
+  // carry the hand-over sums, one traversal group per chunk, dense forest, enough chunks to share
+  {
+    const uint32_t cols_pad_bytes = f->tile_slot_stride;
+    const bool able = !f->sparse && !f->staged && f->tile_col_stride == 128u && cols_pad_bytes >= ((uint32_t)p.cols + 2u) * 128u &&
+                      f->trees_per_chunk == f->group && f->group >= 2 && f->qdepth >= 10 && !p.leaf_ids;
+    int S = f->tune.cluster >= 0 ? f->tune.cluster : 0;
+    S = std::min(S, 8);
+    p.cluster = (able && S > 1 && f->num_chunks >= 2 * S) ? S : 0;
+  }
   // Row batches (tuning knob, off by default): walk the rows in batches whose rank tiles stay
   // L2-resident between chunk passes.  Measured on B200 (profiles/r01_row_batch.log): never a win --
   // the tile stream hides behind the traversal, and every batch pays a pipeline fill and drain.

@@ -4,6 +4,7 @@
 // trees per group (1..6), TMA double-buffered or register-staged tiles.
 #include "kernels_smem_traverse.cuh"
 #include "kernels_smem_deep.cuh"
+#include "kernels_smem_cluster.cuh"
 
 // deep walks in flight per lane (k_smem_forest_deep; each holds a 32-byte block in registers), for the
 // 256-thread and the 512-thread instantiations.  Config 4 on B200, 1M rows, top depth 6 / 7:
@@ -62,6 +63,38 @@ int TAHOE_CAT(launch_smem_depth_, TAHOE_DEPTH)(tahoe_forest* f, const SmemParams
   }
 #else
   if (f->sparse) { set_error("sparse tops deeper than 12 levels are not built"); return TAHOE_ERR_INVALID; }
+#endif
+#if TAHOE_DEPTH >= 10
+  // cluster pipeline (deep trees: one traversal group per chunk): S CTAs hold S consecutive chunks, tiles by multicast
+  if (p.cluster > 1 && !p.leaf_ids) {
+    auto go_cluster = [&](auto kern) -> int {
+      TAHOE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->smem_bytes));
+      cudaLaunchConfig_t cfg{};
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = (unsigned)p.cluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      cfg.blockDim = dim3((unsigned)f->warps * 32u); cfg.dynamicSmemBytes = f->smem_bytes; cfg.stream = stream;
+      cfg.attrs = attr; cfg.numAttrs = 1;
+      cfg.gridDim = dim3((unsigned)p.cluster);
+      int max_clusters = 0;
+      TAHOE_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, kern, &cfg));
+      if (max_clusters < 1) { set_error("no cluster of this size fits the device"); return TAHOE_ERR_NOT_APPLICABLE; }
+      const size_t want = (p.num_tiles + f->warps - 1) / f->warps;
+      cfg.gridDim = dim3((unsigned)(std::min<size_t>((size_t)max_clusters, want) * (size_t)p.cluster));
+      TAHOE_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
+      return TAHOE_OK;
+    };
+    switch (f->group) {
+      case 2: return go_cluster(k_smem_forest_cluster<D, 2>);
+      case 3: return go_cluster(k_smem_forest_cluster<D, 3>);
+      case 4: return go_cluster(k_smem_forest_cluster<D, 4>);
+      case 5: return go_cluster(k_smem_forest_cluster<D, 5>);
+      case 6: return go_cluster(k_smem_forest_cluster<D, 6>);
+      default: break;
+    }
+    set_error("unsupported traversal group size for the cluster pipeline");
+    return TAHOE_ERR_INVALID;
+  }
 #endif
   // the leaf-id instantiation is the checking path: one tree at a time keeps the build small
   if (p.leaf_ids) return f->staged ? go(k_smem_forest<D, 1, true, true, 0>) : go(k_smem_forest<D, 1, true, false, 0>);

@@ -21,6 +21,7 @@ struct SmemParams {
   int tree_base;            // index (in the whole padded forest) of this launch's first tree: qwords points at it
   int first_pass, last_pass;  // this launch holds the forest's first / last chunk (partial sums start / end here)
   int top_levels;           // levels of every tree decided on the TopWords kernel parameter (0 or 2): picks the instantiation
+  int cluster;              // > 1: k_smem_forest_cluster with this many CTAs per cluster (kernels_smem_cluster.cuh)
   uint32_t col_mask, miss_code;
   // tile region: word (col, slot, lane) at col*col_stride + slot*slot_stride + lane*4, and
   // (node & col_mask) == col*col_stride, so a lane's address is one AND-OR.  Two layouts:

@@ -154,7 +154,7 @@ int pack_dense(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
       s.orig[k] = (int32_t)k;
     }
     // bottom-up child swap, Struct.h:1775-1825
-    for (int lv = d - 1; lv >= 0; --lv) {
+    for (int lv = f->tune.no_reorder ? -1 : d - 1; lv >= 0; --lv) {
       for (int64_t k = ((int64_t)1 << lv) - 1; k < ((int64_t)1 << (lv + 1)) - 1; ++k) {
         if (s.meta[k] & kMetaLeaf) continue;
         if (s.weight[2 * k + 1] < s.weight[2 * k + 2]) {
@@ -170,8 +170,9 @@ int pack_dense(tahoe_forest* f, const tahoe_dense_node_t* nodes) {
   {
     std::vector<int> order(T);
     std::iota(order.begin(), order.end(), 0);
-    std::stable_sort(order.begin(), order.end(),
-                     [&](int a, int b) { return h.simhash[a] < h.simhash[b]; });
+    if (!f->tune.no_simhash)
+      std::stable_sort(order.begin(), order.end(),
+                       [&](int a, int b) { return h.simhash[a] < h.simhash[b]; });
     for (int i = 0; i < T; ++i) h.tree_order[i] = order[i];
   }
   if (build_inter) {
@@ -955,6 +956,9 @@ static void read_tuning(Tuning& t) {
   if (const char* e = std::getenv("TAHOE_DIRECT_GROUP")) t.direct_group = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_TOP_TREES")) t.top_trees = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_TOP_LEVELS")) t.top_levels = std::atoi(e);
+  if (const char* e = std::getenv("TAHOE_CLUSTER")) t.cluster = std::atoi(e);
+  if (const char* e = std::getenv("TAHOE_NO_REORDER")) t.no_reorder = std::atoi(e) != 0;
+  if (const char* e = std::getenv("TAHOE_NO_SIMHASH")) t.no_simhash = std::atoi(e) != 0;
   if (const char* e = std::getenv("TAHOE_HOST_SLAB")) std::sscanf(e, "%d,%d,%d", &t.slab_first, &t.slab_growth, &t.slab_cap);
 }
 

@@ -231,3 +231,32 @@ def test_multi_chunk_split_and_host_path(oracle):
     assert bits_equal(ph, p.cpu().numpy())
     assert bits_equal(golden_preds(c, 0, 0.0, 0.0),
                       f.predict_host(np.ascontiguousarray(c["data"]), strategy=api.SPLIT_SHARED_FOREST))
+
+
+@pytest.mark.parametrize("cluster,trees,rows", [(2, 40, 200_003), (4, 36, 50_001), (2, 12, 33), (4, 44, 1)])
+def test_cluster_pipeline_is_bit_exact(oracle, monkeypatch, cluster, trees, rows):
+    """k_smem_forest_cluster (kernels_smem_cluster.cuh): S CTAs hold S consecutive chunks, tiles arrive by TMA
+    multicast, partial sums pass CTA -> CTA through distributed shared memory IN TREE ORDER -- the scores must be
+    the CPU's bits.  Forced on a Higgs-shaped forest (depth 12: one group of 4 trees per chunk); chunk counts that
+    do and do not divide by S, missing values, one tile, one row."""
+    import torch
+    d, C = 12, 28
+    monkeypatch.setenv("TAHOE_SMEM_PLAN", "12,0,4")
+    monkeypatch.setenv("TAHOE_CLUSTER", str(cluster))
+    nodes = synth.gen_dense_forest(4100 + trees, trees, d, C, leaf_prob=0.02)
+    f = api.Forest.from_dense(nodes, trees, d, C, missing=-999.0)
+    inf = f.info()
+    assert (inf.smem_warps, inf.smem_staged, inf.smem_group, inf.trees_per_chunk) == (12, 0, 4, 4)
+    assert inf.num_chunks == trees // 4 and inf.num_chunks >= 2 * cluster or rows <= 33
+    x = api.gen_data_device(4200 + trees, rows, C, miss_frac=0.002)
+    got = f.predict(x, strategy=api.SPLIT_SHARED_FOREST).cpu().numpy()
+    ref = f.predict(x, strategy=api.DIRECT).cpu().numpy()
+    assert bits_equal(got, ref)
+    n = min(rows, 2048)
+    host = synth.gen_data(4200 + trees, n, C, miss_frac=0.002)
+    assert bits_equal(got[:n], oracle.predict_dense(nodes, trees, d, host, -999.0))
+    got2 = f.predict(x, strategy=api.SPLIT_SHARED_FOREST).cpu().numpy()      # again: barriers and phases end clean
+    assert bits_equal(got2, ref)
+    monkeypatch.setenv("TAHOE_CLUSTER", "0")
+    f0 = api.Forest.from_dense(nodes, trees, d, C, missing=-999.0)
+    assert bits_equal(f0.predict(x, strategy=api.SPLIT_SHARED_FOREST).cpu().numpy(), ref)

@@ -14,4 +14,4 @@ for _ in range(3): f.predict(d, p, strategy=api.SPLIT_SHARED_FOREST)
 torch.cuda.synchronize(); f.set_profiling(True)
 for _ in range(5): f.predict(d, p, strategy=api.SPLIT_SHARED_FOREST)
 q, t, n = f.profile_read()
-print(f"TL={os.environ.get('TAHOE_TOP_LEVELS','auto')} {cfg} rows={rows} plan={os.environ.get('TAHOE_SMEM_PLAN','auto')} -> warps={inf.smem_warps} staged={inf.smem_staged} G={inf.smem_group} tpc={inf.trees_per_chunk} chunks={inf.num_chunks} col_shift={inf.col_shift} quantize={q/n:.3f} ms traverse={t/n:.3f} ms  checksum={float(p.double().sum()):.6f}")
+print(f"TL={os.environ.get('TAHOE_TOP_LEVELS','auto')} S={os.environ.get('TAHOE_CLUSTER','auto')} {cfg} rows={rows} plan={os.environ.get('TAHOE_SMEM_PLAN','auto')} -> warps={inf.smem_warps} staged={inf.smem_staged} G={inf.smem_group} tpc={inf.trees_per_chunk} chunks={inf.num_chunks} col_shift={inf.col_shift} quantize={q/n:.3f} ms traverse={t/n:.3f} ms  checksum={float(p.double().sum()):.6f}")
