@@ -69,8 +69,19 @@ constexpr double kRowGather = 1.7e12;       // B/s of 32-byte row sectors gather
 constexpr double kForestHalf = 80e6;        // forest bytes at which the L2-gather rates halve
 constexpr double kTeamLevel = 0.7e-6;       // SHARED_DATA: one tree level of a row's walk (latency-bound)
 constexpr double kSharedDataRate = 7.0e11;  // visits/s (slot-levels), SHARED_DATA
-constexpr double kRowStream = 3.7e12;       // B/s of sample rows through a TMA-fed SHARED_DATA kernel
-constexpr double kSmemVisit = 2.9e-13;      // s per visit, shared-memory forest, 16 warps x 5-6 trees staged at depth 10 (unit plan)
+constexpr double kRowStream = 4.6e12;       // B/s of sample rows through a TMA-fed SHARED_DATA kernel (ncu config 1: 620.7 MB of DRAM traffic in 133.3 us)
+// The shared-memory forest's rate is DERIVED FROM NCU COUNTERS of the unit plan (config 2, 16 warps x 5 trees staged,
+// parameter-table levels; profiles/r02_ncu_full_C2_summary.json), not fitted to wall-clock:
+//   l1tex__data_pipe_lsu_wavefronts_mem_shared.sum = 2.1175e9 over rows x trees x depth = 5M x 500 x 10 lane-visits
+//   l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed = 97.9 %; the pipe retires one wavefront per clock
+//   per SM (tahoe_measure_peaks: 37.1 TB/s = 128 B x 148 SMs x 1.965 GHz)
+// => seconds per lane-visit = wavefronts per lane-visit / (pipe rate x utilisation) = 2.97e-13 (wall-clock fit: 2.9e-13).
+// The same two counters on config 3 (1.1582e10 wavefronts over 1.2e11 lane-visits at 81.2 %) give 4.09e-13: the ratio,
+// 1.37, is smem_depth_factor(12) = 1.4 of the planner.
+constexpr double kSmemWavefrontsPerLaneVisit = 2.1175e9 / 2.5e10;
+constexpr double kLsuPipeRate = 148.0 * 1.965e9;   // wavefronts/s
+constexpr double kLsuPipeUtil = 0.979;
+constexpr double kSmemVisit = kSmemWavefrontsPerLaneVisit / (kLsuPipeRate * kLsuPipeUtil);   // s per lane-visit, unit plan
 constexpr double kTileStream = 5.0e12;      // B/s of rank tiles re-read once per chunk (half hidden)
 constexpr double kChunkFixed = 4.0e-6;      // stage one chunk + barrier + the ragged end of a pass (config 3: 0.9 ms over 167 chunks)
 constexpr double kTileLevel = 30e-9;        // one level of one traversal group of a tile: this much alone ...
@@ -87,7 +98,10 @@ constexpr double kHostCopyRate = 50e9;        // B/s, pinned host -> device over
 }  // namespace model
 
 static double forest_bytes(const tahoe_forest* f) {
-  return f->sparse ? (double)f->host.sparse.size() * 16.0 : (double)f->host.heap.size() * 8.0;
+  // what the full-machine DIRECT kernels gather from: the 8-byte compact nodes when the fields fit (k_sparse8;
+  // config 4: 115 MB, inside L2 -- the 16-byte form is 229 MB and made the model predict 80.6 ms where 34.4 was measured)
+  if (f->sparse) return f->host.sparse8.empty() ? (double)f->host.sparse.size() * 16.0 : (double)f->host.sparse8.size() * 8.0;
+  return (double)f->host.heap.size() * 8.0;
 }
 
 static int select_strategy(const tahoe_forest* f, size_t rows_, double* out) {
@@ -109,7 +123,7 @@ static int select_strategy(const tahoe_forest* f, size_t rows_, double* out) {
           const bool staged = s == TAHOE_STRATEGY_SHARED_DATA_PER_THREAD;
           // sparse trees are uneven: a warp's lanes idle until its deepest walk ends (14 of 32 lanes
           // active on config 4), and staging rows does not pay for itself there
-          const double rate = (f->sparse ? kDirectRate / (staged ? 2.2 : 1.6) : (staged ? kPerThreadRate : kDirectRate)) * l2_scale;
+          const double rate = (f->sparse ? kDirectRate / (staged ? 1.65 : 1.25) : (staged ? kPerThreadRate : kDirectRate)) * l2_scale;
           const double lat = T * dwalk * kL2Visit * (staged ? 0.96 : 1.0);
           double thr = R * T * dbar / rate;
           // DIRECT gathers features straight from global memory: once the resident threads' rows
@@ -117,7 +131,9 @@ static int select_strategy(const tahoe_forest* f, size_t rows_, double* out) {
           // (the share of visits that miss grows with how far the rows overflow L1)
           if (!staged && C * 4.0 * 2048.0 > kL1Bytes) {
             const double miss = std::min(1.0, (C * 4.0 * 2048.0 / kL1Bytes - 1.0) / 8.0);
-            thr += miss * R * T * dbar * 32.0 / kRowGather;
+            // (sparse walks are short and end at different levels: fewer of a warp's lanes gather at once -- 0.4 fits
+            // config 4: 34.4 ms measured at 1M rows, 10.0 at 300K)
+            thr += (f->sparse ? 0.4 : 1.0) * miss * R * T * dbar * 32.0 / kRowGather;
           }
           t = kLaunch + std::max(lat, thr);
           break;
