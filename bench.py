@@ -290,7 +290,7 @@ def measure_config(cfg_id, forest, n_nodes, data, peaks, hbm_gbs, steps, strateg
         smem_bytes = float(rows) * cfg["trees"] * (cfg["depth"] * 8 + 4)
         rec["frac_smem"] = smem_bytes / sec / 1e9 / peaks["smem_read_gbs"]
         rec["plan"] = {"warps": info.smem_warps, "staged": info.smem_staged, "group": info.smem_group,
-                       "trees_per_chunk": info.trees_per_chunk, "chunks": info.num_chunks}
+                       "trees_per_chunk": info.trees_per_chunk, "chunks": info.num_chunks, "cluster": info.smem_cluster}
     return rec, s, preds
 
 
@@ -483,7 +483,8 @@ def main():
                 "l2_policy": f"inputs_exceed_l2 ({rows * cfg['cols'] * 4 / 1e6:.0f} MB of rows per GPU per step "
                              f"vs {peaks['l2_bytes'] / 1e6:.0f} MB L2)",
                 "forest_chunks": info.num_chunks, "trees_per_chunk": info.trees_per_chunk,
-                "plan": {"warps": info.smem_warps, "staged": info.smem_staged, "group": info.smem_group},
+                "plan": {"warps": info.smem_warps, "staged": info.smem_staged, "group": info.smem_group,
+                         "cluster": info.smem_cluster},
                 "node_bytes": 4, "rank_bits": info.rank_bits, "gathered_checksum": gathered_checksum,
                 "gathered_matches_local_predicts": gathered_ok},
             "roofline": {"bound": "l2" if fits_l2 else "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -107,6 +107,7 @@ typedef struct {
   int sparse_top_trees_per_chunk;
   int sparse_top_chunks;
   double sparse_top_deep_walks; /* expected fraction of (row, tree) walks still on an internal node below the top (finished in L2) */
+  int smem_cluster;           /* shared-memory-forest plan: CTAs per thread-block cluster (0 = no cluster pipeline) */
 } tahoe_forest_info_t;
 
 /* ---- forest lifetime -------------------------------------------------------------

@@ -60,7 +60,7 @@ class ForestInfo(C.Structure):
                 ("sd_blocked", C.c_int), ("sparse_cut", C.c_int), ("sparse_deep_walks", C.c_double),
                 ("sparse_fid_bits", C.c_int), ("sparse_top_depth", C.c_int), ("sparse_top_active", C.c_int),
                 ("sparse_top_trees_per_chunk", C.c_int), ("sparse_top_chunks", C.c_int),
-                ("sparse_top_deep_walks", C.c_double)]
+                ("sparse_top_deep_walks", C.c_double), ("smem_cluster", C.c_int)]
 
 
 class Peaks(C.Structure):

@@ -371,6 +371,7 @@ int tahoe_forest_info(const tahoe_forest_t* f, tahoe_forest_info_t* info) {
   info->sparse_top_depth = f->qt ? f->qt_depth : 0; info->sparse_top_active = f->sp_use_qt;
   info->sparse_top_trees_per_chunk = f->qt ? f->trees_per_chunk : 0; info->sparse_top_chunks = f->qt ? f->num_chunks : 0;
   info->sparse_top_deep_walks = f->qt_overflow;
+  info->smem_cluster = smem_cluster_size(f);
   info->bytes_heap = (int64_t)(f->host.heap.size() * sizeof(uint2) + f->host.sparse.size() * sizeof(uint4));
   info->bytes_interleaved = (int64_t)(f->host.inter.size() * sizeof(uint2));
   info->bytes_quantized = (int64_t)(f->host.qwords.size() * sizeof(uint32_t));

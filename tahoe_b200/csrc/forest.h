@@ -259,6 +259,7 @@ struct PredictArgs {
 int launch_direct(tahoe_forest* f, const PredictArgs& a, bool rows_in_smem, int* launches);
 int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches);
 int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches);
+int smem_cluster_size(const tahoe_forest* f);   // CTAs per cluster of the shared-memory-forest plan (0 = plain kernel)
 int launch_sparse_smem(tahoe_forest* f, const PredictArgs& a, int* launches);   // kernels_sparse_smem.cu
 int query_device(tahoe_forest* f);
 int ensure_workspace(tahoe_forest* f, Workspace* ws, size_t rows);

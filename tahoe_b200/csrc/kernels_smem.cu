@@ -150,6 +150,19 @@ TAHOE_DEPTH_DECL(6) TAHOE_DEPTH_DECL(7) TAHOE_DEPTH_DECL(8) TAHOE_DEPTH_DECL(9) 
 TAHOE_DEPTH_DECL(11) TAHOE_DEPTH_DECL(12) TAHOE_DEPTH_DECL(13) TAHOE_DEPTH_DECL(14)
 #undef TAHOE_DEPTH_DECL
 
+// Cluster pipeline (kernels_smem_cluster.cuh): CTAs per cluster the handle's plan runs with (0 = plain kernel).  Needs TMA
+// tiles in the slot-major region with two spare column rows (the hand-over ring), one traversal group per chunk, a dense
+// forest of depth >= 10 and enough chunks to share.
+int smem_cluster_size(const tahoe_forest* f) {
+  const bool able = !f->sparse && f->quant && !f->staged && f->tile_col_stride == 128u &&
+                    f->tile_slot_stride >= ((uint32_t)f->params.num_cols + 2u) * 128u &&
+                    f->trees_per_chunk == f->group && f->group >= 2 && f->qdepth >= 10;
+  // default: pairs of CTAs (one TPC).  Same box, interleaved, config 3 at 10M rows: 53.14 / 53.23 / 53.29 ms without,
+  // 52.91 / 52.91 / 52.94 ms with S = 2, and the DRAM traffic of the launch halves (300.7 -> 150.3 GB); S = 4 is slower
+  const int S = std::min(f->tune.cluster >= 0 ? f->tune.cluster : 2, 8);
+  return (able && S > 1 && f->num_chunks >= 2 * S) ? S : 0;
+}
+
 int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   if (!(f->quant || f->qt) || f->trees_per_chunk < 1) {
     set_error("shared-memory forest strategies need a dense forest of depth 1..14, <= 64 columns, "
@@ -205,16 +218,7 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.deep_blocks = f->d_sp_qblocks; p.block_offsets = f->d_sp_qblock_offsets; p.block_orig = f->d_sp_qblock_orig;
   p.tf = Transform{f->params.output, (float)(a.avg_trees ? a.avg_trees : f->params.num_trees), f->params.threshold,
                    f->params.global_bias};
-  // Cluster pipeline (kernels_smem_cluster.cuh): TMA tiles in the slot-major region with a padding column row to
-  // carry the hand-over sums, one traversal group per chunk, dense forest, enough chunks to share
-  {
-    const uint32_t cols_pad_bytes = f->tile_slot_stride;
-    const bool able = !f->sparse && !f->staged && f->tile_col_stride == 128u && cols_pad_bytes >= ((uint32_t)p.cols + 2u) * 128u &&
-                      f->trees_per_chunk == f->group && f->group >= 2 && f->qdepth >= 10 && !p.leaf_ids;
-    int S = f->tune.cluster >= 0 ? f->tune.cluster : 0;
-    S = std::min(S, 8);
-    p.cluster = (able && S > 1 && f->num_chunks >= 2 * S) ? S : 0;
-  }
+  p.cluster = p.leaf_ids ? 0 : smem_cluster_size(f);
   // Row batches (tuning knob, off by default): walk the rows in batches whose rank tiles stay
   // L2-resident between chunk passes.  Measured on B200 (profiles/r01_row_batch.log): never a win --
   // the tile stream hides behind the traversal, and every batch pays a pipeline fill and drain.

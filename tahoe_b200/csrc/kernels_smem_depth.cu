@@ -77,23 +77,24 @@ int TAHOE_CAT(launch_smem_depth_, TAHOE_DEPTH)(tahoe_forest* f, const SmemParams
       cfg.attrs = attr; cfg.numAttrs = 1;
       cfg.gridDim = dim3((unsigned)p.cluster);
       int max_clusters = 0;
-      TAHOE_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, kern, &cfg));
-      if (max_clusters < 1) { set_error("no cluster of this size fits the device"); return TAHOE_ERR_NOT_APPLICABLE; }
+      if (cudaOccupancyMaxActiveClusters(&max_clusters, kern, &cfg) != cudaSuccess) { cudaGetLastError(); return TAHOE_ERR_NOT_APPLICABLE; }
+      if (max_clusters < 1) return TAHOE_ERR_NOT_APPLICABLE;   // (the caller falls back to the plain kernel)
       const size_t want = (p.num_tiles + f->warps - 1) / f->warps;
       cfg.gridDim = dim3((unsigned)(std::min<size_t>((size_t)max_clusters, want) * (size_t)p.cluster));
       TAHOE_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
       return TAHOE_OK;
     };
+    int rc = TAHOE_ERR_NOT_APPLICABLE;
     switch (f->group) {
-      case 2: return go_cluster(k_smem_forest_cluster<D, 2>);
-      case 3: return go_cluster(k_smem_forest_cluster<D, 3>);
-      case 4: return go_cluster(k_smem_forest_cluster<D, 4>);
-      case 5: return go_cluster(k_smem_forest_cluster<D, 5>);
-      case 6: return go_cluster(k_smem_forest_cluster<D, 6>);
+      case 2: rc = go_cluster(k_smem_forest_cluster<D, 2>); break;
+      case 3: rc = go_cluster(k_smem_forest_cluster<D, 3>); break;
+      case 4: rc = go_cluster(k_smem_forest_cluster<D, 4>); break;
+      case 5: rc = go_cluster(k_smem_forest_cluster<D, 5>); break;
+      case 6: rc = go_cluster(k_smem_forest_cluster<D, 6>); break;
       default: break;
     }
-    set_error("unsupported traversal group size for the cluster pipeline");
-    return TAHOE_ERR_INVALID;
+    // a device (or partition) that cannot co-schedule the cluster: the plain kernel below does the same work
+    if (rc != TAHOE_ERR_NOT_APPLICABLE) return rc;
   }
 #endif
   // the leaf-id instantiation is the checking path: one tree at a time keeps the build small

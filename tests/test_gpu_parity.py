@@ -260,3 +260,42 @@ def test_cluster_pipeline_is_bit_exact(oracle, monkeypatch, cluster, trees, rows
     monkeypatch.setenv("TAHOE_CLUSTER", "0")
     f0 = api.Forest.from_dense(nodes, trees, d, C, missing=-999.0)
     assert bits_equal(f0.predict(x, strategy=api.SPLIT_SHARED_FOREST).cpu().numpy(), ref)
+
+
+def test_two_streams_share_the_handle_scratch_safely():
+    """tahoe_predict on two streams without a host sync in between: both use the handle's one workspace (rank tiles,
+    tile flags), so the second call must wait for the first ON THE DEVICE (the event in predict_on_ws0)."""
+    import torch
+    c = load_case("susy_like")
+    f = api.Forest.from_dense(c["nodes"], c["trees"], c["depth"], c["cols"], missing=-999.0)
+    xa = api.gen_data_device(91, 300_000, 18, miss_frac=0.001)
+    xb = api.gen_data_device(92, 200_000, 18)
+    want_a = f.predict(xa, strategy=api.SPLIT_SHARED_FOREST).clone()
+    want_b = f.predict(xb, strategy=api.SPLIT_SHARED_FOREST).clone()
+    torch.cuda.synchronize()
+    sa, sb = torch.cuda.Stream(), torch.cuda.Stream()
+    pa, pb = torch.empty_like(want_a), torch.empty_like(want_b)
+    for _ in range(3):
+        f.predict(xa, pa, strategy=api.SPLIT_SHARED_FOREST, stream=sa)
+        f.predict(xb, pb, strategy=api.SPLIT_SHARED_FOREST, stream=sb)     # no sync: overlaps the first on the device unless ordered
+    torch.cuda.synchronize()
+    assert torch.equal(pa, want_a) and torch.equal(pb, want_b)
+
+
+def test_measure_peaks_and_copy_baseline():
+    import torch
+    pk = api.measure_peaks()
+    assert pk["sm_count"] > 0 and pk["l2_bytes"] > 0
+    assert pk["smem_read_gbs"] > pk["l2_read_gbs"] > 1000.0 and pk["l2_sector_gathers_per_s"] > 1e10
+    c = load_case("susy_like")
+    f = api.Forest.from_dense(c["nodes"], c["trees"], c["depth"], c["cols"], missing=-999.0)
+    host = synth.gen_data(93, 50_001, 18)
+    want = f.predict_host(host, strategy=api.SPLIT_SHARED_FOREST)
+    scratch = np.empty(50_001, dtype=np.float32)
+    f.predict_host(host, scratch, strategy=api.SPLIT_SHARED_FOREST, copy_only=True)     # same slabs, no kernels: must not fail
+    assert f.launches() == 0
+    assert bits_equal(f.predict_host(host, strategy=api.SPLIT_SHARED_FOREST), want)
+    with pytest.raises(ValueError):
+        f.predict_host(host.astype(np.float64), strategy=api.SPLIT_SHARED_FOREST)     # the C ABI takes bare pointers: checked here
+    with pytest.raises(ValueError):
+        f.predict(torch.zeros((10, 17), device="cuda"))
