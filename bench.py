@@ -488,7 +488,10 @@ def main():
                 "node_bytes": 4, "rank_bits": info.rank_bits, "gathered_checksum": gathered_checksum,
                 "gathered_matches_local_predicts": gathered_ok},
             "roofline": {"bound": "l2" if fits_l2 else "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": _traffic(WORKLOAD), "kernel": "k_smem_forest",
+                         "frac": achieved / peak,
+                         # ncu capture at the full 10M rows, scaled to this rank's rows (the tile re-streaming is linear in rows)
+                         "traffic": (None if _traffic(WORKLOAD) is None else int(_traffic(WORKLOAD) * rows / cfg["rows"])),
+                         "kernel": "k_smem_forest_cluster" if info.smem_cluster > 1 else "k_smem_forest",
                          "kernel_ms": trav_ms, "quantize_ms": (q_ms / n_prof if n_prof else None),
                          "algorithmic_bytes_per_launch": abytes,
                          "peak_source": "L2 streaming-read bandwidth measured in this run (tahoe_measure_peaks); SURVEY 8(d): "
