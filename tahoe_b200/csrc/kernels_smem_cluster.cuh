@@ -112,10 +112,6 @@ __global__ void __launch_bounds__(kSmemMaxThreads, 1) k_smem_forest_cluster(cons
     const int chunk = pass * (int)S + (int)rank;                 // this CTA's chunk in this pass (may be past the end)
     const bool have = chunk < p.num_chunks;
     const int tree0 = chunk * p.trees_per_chunk;
-    // the first tile of this pass is asked for BEFORE the cluster barrier (both buffers of this warp are free)
-    size_t tile = unit_global;
-    int b = 0;
-    if (tile < p.num_tiles) { __syncwarp(); load_tile(tile, 0); }
     // ---- stage this CTA's chunk.  The hand-over of pass n+1 (rank 0 reads preds[]) needs the last CTA's stores of
     // pass n: the cluster barrier orders them (release / acquire at cluster scope covers global memory)
     if (pass) cluster_sync_all();
@@ -131,6 +127,9 @@ __global__ void __launch_bounds__(kSmemMaxThreads, 1) k_smem_forest_cluster(cons
         done += piece;
       }
     }
+    size_t tile = unit_global;
+    int b = 0;
+    if (tile < p.num_tiles) load_tile(tile, 0);
     if (have) { mbar_wait(bar_chunk, chunk_phase); chunk_phase ^= 1; }
 
     const bool first = p.first_pass && pass == 0, last = p.last_pass && pass == passes - 1;

@@ -121,8 +121,6 @@ k_smem_forest_deep(const __grid_constant__ SmemParams p, const __grid_constant__
   for (int chunk = 0; chunk < p.num_chunks; ++chunk) {
     const int tree0 = chunk * p.trees_per_chunk;
     const int ntrees = min(p.trees_per_chunk, p.padded_trees - tree0);   // a multiple of G
-    size_t tile = warp_global;
-    if (tile < p.num_tiles) fetch_tile(tile);   // into registers, before the barrier: in flight while the chunk lands
     __syncthreads();                         // everyone is done reading the previous chunk
     if (threadIdx.x == 0) {
       fence_proxy_async();
@@ -136,6 +134,8 @@ k_smem_forest_deep(const __grid_constant__ SmemParams p, const __grid_constant__
         done += piece;
       }
     }
+    size_t tile = warp_global;
+    if (tile < p.num_tiles) fetch_tile(tile);
     mbar_wait(bar_chunk, chunk_phase);
     chunk_phase ^= 1;
 

@@ -224,13 +224,6 @@ k_smem_forest(const __grid_constant__ SmemParams p, const __grid_constant__ TopW
   for (int chunk = 0; chunk < p.num_chunks; ++chunk) {
     const int tree0 = chunk * p.trees_per_chunk;
     const int ntrees = min(p.trees_per_chunk, p.padded_trees - tree0);   // a multiple of G
-    // the first tile of this pass is asked for BEFORE the barrier: it flies while the CTA meets and the chunk lands
-    // (both of this warp's buffers are free: its last tile of the previous pass has been walked)
-    size_t tile = warp_global;
-    if (tile < p.num_tiles) {
-      if (STAGED) fetch_tile(tile);
-      else { __syncwarp(); load_tile(tile, 0); }
-    }
     // ---- stage this chunk of trees (everyone is done reading the previous one)
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -244,6 +237,11 @@ k_smem_forest(const __grid_constant__ SmemParams p, const __grid_constant__ TopW
         bulk_g2s(s_base + forest_off + done, src + done, piece, bar_chunk);
         done += piece;
       }
+    }
+    // the first tile of this pass flies while the chunk lands
+    size_t tile = warp_global;
+    if (tile < p.num_tiles) {
+      if (STAGED) fetch_tile(tile); else load_tile(tile, 0);
     }
     mbar_wait(bar_chunk, chunk_phase);
     chunk_phase ^= 1;
