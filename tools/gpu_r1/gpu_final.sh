@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
 timeout 900 python bench.py > gpurun_out/bench_$TAG.json 2> gpurun_out/bench_$TAG.err; echo "bench rc=$?"; cat gpurun_out/bench_$TAG.json
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref_$TAG.json 2> gpurun_out/bench_ref_$TAG.err; echo "ref rc=$?"; cat gpurun_out/bench_ref_$TAG.json
-bash tools/gpu_ncu.sh $TAG
+bash tools/gpu_r1/gpu_ncu.sh $TAG
 timeout 600 python tools/probe_prof.py C3 10000000 2>&1 | cut -c47-300
 timeout 300 python tools/run_one.py C1 2 0 4 2>&1 | tail -2
 timeout 300 python tools/probe_sparse.py 1000000 2>&1 | tail -1

@@ -11,4 +11,4 @@ for shape in "500 10 18 200000" "1000 12 28 100000" "100 8 3072 50000"; do
   TAHOE_NO_REORDER=1 TAHOE_NO_SIMHASH=1 timeout 200 python tools/probe_reorder.py $shape >> $A 2>&1
 done
 cat $A
-bash tools/gpu_ref_compare_big.sh
+bash tools/gpu_r2/ref_compare_big.sh
