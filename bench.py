@@ -53,6 +53,38 @@ def _traffic(cfg_id: str):
     return None
 
 
+def _ncu(cfg_id: str):
+    """Counters of the config's dominant kernel from the committed `ncu --set full` capture (profiles/r02_ncu_full_*):
+    DRAM GB/s, LSU data pipe, shared-memory wavefronts and bank-conflict wavefronts, threads per warp instruction."""
+    name = {"C3": "r02_ncu_full_C3_cluster_summary.json"}.get(cfg_id, f"r02_ncu_full_{cfg_id}_summary.json")
+    path = os.path.join(ROOT, "profiles", name)
+    if not os.path.exists(path):
+        return None
+    with open(path) as f:
+        d = json.load(f)[0]
+
+    def val(key):
+        v = d.get(key)
+        if not v or v[0] in ("", None):
+            return None
+        scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "ms": 1e-3, "us": 1e-6, "ns": 1e-9, "s": 1.0}.get(v[1], 1.0)
+        return float(v[0]) * scale
+
+    sec = val("gpu__time_duration.sum")
+    dram = (val("dram__bytes_read.sum") or 0.0) + (val("dram__bytes_write.sum") or 0.0)
+    wf, conf = val("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum"), val("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum")
+    return {"source": f"profiles/{name}", "kernel": d.get("kernel"), "kernel_ms_under_ncu": None if not sec else sec * 1e3,
+            "dram_gbs": None if not sec else dram / sec / 1e9,
+            "dram_pct_of_peak": val("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"),
+            "l2_hit_pct": val("lts__t_sector_hit_rate.pct"),
+            "lsu_data_pipe_pct": val("l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed"),
+            "smem_wavefronts": wf, "smem_bank_conflict_wavefronts": conf,
+            "smem_bank_conflict_share": None if not wf else (conf or 0.0) / wf,
+            "threads_per_warp_instruction": val("smsp__thread_inst_executed_per_inst_executed.ratio"),
+            "issue_active_pct": val("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+            "stall_samples_pct": d.get("stall_samples_pct")}
+
+
 def width_rule(cols: int) -> int:
     """reference node-width rule, Struct.h:1831-1852: 1 if max_fid < 32, 2 if < 8192, else 4"""
     return 1 if cols - 1 < 32 else (2 if cols - 1 < 8192 else 4)
@@ -283,7 +315,7 @@ def measure_config(cfg_id, forest, n_nodes, data, peaks, hbm_gbs, steps, strateg
         "forest_fits_l2": bool(b_forest <= peaks["l2_bytes"]),
         "frac_l2": abytes / sec / 1e9 / peaks["l2_read_gbs"],
         "frac_hbm_only": (b_sample + b_forest) / sec / 1e9 / hbm_gbs,
-        "mean_depth": mean_depth, "traffic": _traffic(cfg_id),
+        "mean_depth": mean_depth, "traffic": _traffic(cfg_id), "ncu": _ncu(cfg_id),
     }
     if name in ("shared_forest", "split_shared_forest") and not info.is_sparse:
         # the node and rank words of this kernel come out of SHARED MEMORY: 8 B per visit + 4 B per leaf
