@@ -58,7 +58,7 @@ def test_random_sparse_forests(oracle, seed):
 def test_random_dense_forests(oracle, seed):
     rng = np.random.default_rng(2000 + seed)
     T = int(rng.choice([1, 3, 32, 33, 100, 257]))
-    depth = int(rng.integers(1, 12))
+    depth = int(rng.integers(1, 14))          # 10+: deep plans (one traversal group per chunk: the cluster pipeline)
     cols = int(rng.choice([1, 3, 18, 28, 64, 65, 200]))
     rows = int(rng.choice([1, 32, 77, 5000, 148 * 16 * 32 + 31]))
     nodes = synth.gen_dense_forest(700 + seed, T, depth, cols, leaf_prob=float(rng.choice([0.0, 0.05, 0.3])))
