@@ -88,7 +88,11 @@ def test_random_deep_sparse_forests(oracle, seed, monkeypatch):
     data = synth.gen_data(950 + seed, rows, cols, miss_frac=float(rng.choice([0.0, 0.01, 0.2])), nan_frac=0.002)
     want, wids = oracle.predict_sparse(sp, offs, data, -999.0, want_leaf_ids=True)
     f = api.Forest.from_sparse(sp, offs, cols, weights=w, missing=-999.0)
-    assert f.info().sparse_top_active == 1
+    # (a forced top depth with a giant chunk can push a block index past the marker's 22 bits -- soak seed 45: 200 trees to
+    # level 20, 10.8 M nodes in ONE chunk at D = 2 -- and the packer then keeps the forest on the 8-byte tops: legal, and
+    # the checks below hold for that path too)
+    inf = f.info()
+    assert inf.sparse_top_active == 1 or (inf.sparse_cut >= 1 and f.applicable(api.SPLIT_SHARED_FOREST, rows))
     mass = np.abs(sp["val"][offs[:-1][None, :] + wids]).sum(1)
     for s in (api.SPLIT_SHARED_FOREST, api.DIRECT):
         got, ids = _run(f, data, s)
