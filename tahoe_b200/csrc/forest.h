@@ -117,6 +117,7 @@ struct Tuning {
   int direct_group = 0;                // TAHOE_DIRECT_GROUP: 4 = four walks per thread, 1 = one; 0 = by batch size
   bool no_reorder = false, no_simhash = false;   // TAHOE_NO_REORDER / TAHOE_NO_SIMHASH: ablation of the I8 layout (tools/probe_reorder.py)
   int cluster = -1;                    // TAHOE_CLUSTER: CTAs per cluster of the k_smem_forest cluster pipeline (0/1 = off, -1 = by plan)
+  int quant_tiles = -1;                // TAHOE_QUANT_TILES: 1 = transpose to float tiles first, quantise them in place; 0 = from the rows; -1 = by table
   int top_levels = -1;                 // TAHOE_TOP_LEVELS: 0/1/2 tree levels from the kernel-parameter table; -1 = by plan
   int top_trees = 0;                   // TAHOE_TOP_TREES: cap on the trees per launch of k_smem_forest (test knob: forces the split)
   int slab_first = 0, slab_growth = 0, slab_cap = 0;   // TAHOE_HOST_SLAB="first,growth%,cap" (waves of tiles); 0 = from the model
@@ -261,6 +262,8 @@ int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches);
 int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches);
 int smem_cluster_size(const tahoe_forest* f);   // CTAs per cluster of the shared-memory-forest plan (0 = plain kernel)
 int launch_sparse_smem(tahoe_forest* f, const PredictArgs& a, int* launches);   // kernels_sparse_smem.cu
+int launch_float_tiles(tahoe_forest* f, const float* data, size_t rows, float* tiles_out, uint32_t* tile_flags, size_t tiles,
+                       cudaStream_t stream);   // kernels_sparse_smem.cu: rows -> column-major float tiles + missing flags
 int query_device(tahoe_forest* f);
 int ensure_workspace(tahoe_forest* f, Workspace* ws, size_t rows);
 

@@ -57,6 +57,9 @@ constexpr int kQuantUnroll = 4;   // tiles in flight per warp (independent strid
 // the column-major tile [tile][col][32 lanes]: one coalesced 128-byte store per warp.
 // Columns longer than shared memory keep every 2^k-th threshold there and finish with <= 2^k - 1
 // probes of one or two sectors of the full table.
+// FROM_TILES: the values come from (and the rank words go back to) the column-major float tiles k_float_tiles wrote into
+// the same buffer: a warp's 32 values are one 128-byte line instead of 32 sectors of the row-major matrix.
+template <bool FROM_TILES>
 __global__ void __launch_bounds__(kQuantThreads, 1) k_quantize(QuantParams p) {
   extern __shared__ __align__(16) uint8_t qsm[];
   const int c = blockIdx.x % p.cols;
@@ -114,7 +117,8 @@ __global__ void __launch_bounds__(kQuantThreads, 1) k_quantize(QuantParams p) {
       const size_t tile = base + (size_t)u * kWarps;
       const size_t row = tile * 32 + lane;
       live[u] = tile < t1 && row < p.rows;
-      v[u] = live[u] ? __ldg(p.data + row * (size_t)p.cols + c) : 0.0f;
+      if (FROM_TILES) v[u] = live[u] ? __uint_as_float(__ldcg(p.qtiles + (tile * p.cols + c) * 32 + lane)) : 0.0f;
+      else v[u] = live[u] ? __ldg(p.data + row * (size_t)p.cols + c) : 0.0f;
     }
 #pragma unroll
     for (int u = 0; u < kQuantUnroll; ++u) {
@@ -123,7 +127,7 @@ __global__ void __launch_bounds__(kQuantThreads, 1) k_quantize(QuantParams p) {
       bool miss = false;
       const uint32_t code = live[u] ? rank_code(v[u], miss) : 0u;
       p.qtiles[(tile * p.cols + c) * 32 + lane] = code;
-      if (__any_sync(0xffffffffu, miss) && lane == 0) atomicOr(p.tile_flags + tile, 1u);
+      if (!FROM_TILES && __any_sync(0xffffffffu, miss) && lane == 0) atomicOr(p.tile_flags + tile, 1u);   // (k_float_tiles set the flags)
     }
   }
 }
@@ -187,8 +191,15 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
   q.splits = (int)std::max<size_t>(1, std::min<size_t>((tiles + tiles_per_pass - 1) / tiles_per_pass,
                                                         (size_t)std::max(1, f->sm_count / q.cols)));
   const unsigned qgrid = (unsigned)(q.cols * q.splits);
-  if (f->quant_smem > 48 * 1024)
-    TAHOE_CUDA(cudaFuncSetAttribute(k_quantize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->quant_smem));
+  // Rows -> column-major float tiles first (k_float_tiles), then the ranks in place: pays where the column's threshold
+  // table is strided (every value also gathers a 16-byte block of thresholds from L2, so the 32 row sectors per
+  // warp-load hurt most): config 3 2.57 -> 2.17 ms, config 4 0.73 -> 0.55 ms; with the whole table in shared memory
+  // the extra pass costs more than it saves (config 2: 0.42 -> 0.51 ms).  TAHOE_QUANT_TILES=0/1 overrides.
+  const bool from_tiles = f->tune.quant_tiles >= 0 ? f->tune.quant_tiles > 0 : f->quant_stride > 1;
+  if (f->quant_smem > 48 * 1024) {
+    if (from_tiles) TAHOE_CUDA(cudaFuncSetAttribute(k_quantize<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->quant_smem));
+    else TAHOE_CUDA(cudaFuncSetAttribute(k_quantize<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->quant_smem));
+  }
   cudaEvent_t* ev = nullptr;
   if (f->profile && a.ws == &f->ws[0] && f->prof_count < kProfRing) {
     ev = &f->prof_events[(size_t)f->prof_count * 3];
@@ -196,9 +207,17 @@ int launch_smem_forest(tahoe_forest* f, const PredictArgs& a, int* launches) {
     TAHOE_CUDA(cudaEventRecord(ev[0], a.stream));
   }
   if (!a.reuse_tiles) {   // (a later class of tahoe_predict_classes walks the tiles its first class quantised)
-    TAHOE_CUDA(cudaMemsetAsync(a.ws->tile_flags, 0, tiles * sizeof(uint32_t), a.stream));
-    k_quantize<<<qgrid, kQuantThreads, f->quant_smem, a.stream>>>(q);
-    ++*launches;
+    if (from_tiles) {
+      // transpose first (coalesced both ways, sets the tile flags), then quantise the tiles in place
+      int rc2 = launch_float_tiles(f, a.data, a.rows, reinterpret_cast<float*>(a.ws->qtiles), a.ws->tile_flags, tiles, a.stream);
+      if (rc2) return rc2;
+      k_quantize<true><<<qgrid, kQuantThreads, f->quant_smem, a.stream>>>(q);
+      *launches += 2;
+    } else {
+      TAHOE_CUDA(cudaMemsetAsync(a.ws->tile_flags, 0, tiles * sizeof(uint32_t), a.stream));
+      k_quantize<false><<<qgrid, kQuantThreads, f->quant_smem, a.stream>>>(q);
+      ++*launches;
+    }
   }
   if (ev) TAHOE_CUDA(cudaEventRecord(ev[1], a.stream));
   TAHOE_CUDA(cudaGetLastError());

@@ -303,6 +303,14 @@ __global__ void __launch_bounds__(kSparseWarps * 32, 1) k_sparse_smem(SparseSmem
   }
 }
 
+int launch_float_tiles(tahoe_forest* f, const float* data, size_t rows, float* tiles_out, uint32_t* tile_flags, size_t tiles,
+                       cudaStream_t stream) {
+  const unsigned grid = (unsigned)std::min<size_t>((tiles + 7) / 8, (size_t)f->sm_count * 8);
+  k_float_tiles<<<grid, 256, 0, stream>>>(data, rows, f->params.num_cols, f->params.missing, tiles_out, tile_flags, tiles);
+  TAHOE_CUDA(cudaGetLastError());
+  return TAHOE_OK;
+}
+
 int launch_sparse_smem(tahoe_forest* f, const PredictArgs& a, int* launches) {
   if (!f->sparse || f->sp_tpc < 1 || !f->d_sp_top) {
     set_error("shared-memory strategies on a sparse forest need 8-byte breadth-first nodes and room for "

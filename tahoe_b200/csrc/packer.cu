@@ -956,6 +956,7 @@ static void read_tuning(Tuning& t) {
   if (const char* e = std::getenv("TAHOE_DIRECT_GROUP")) t.direct_group = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_TOP_TREES")) t.top_trees = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_TOP_LEVELS")) t.top_levels = std::atoi(e);
+  if (const char* e = std::getenv("TAHOE_QUANT_TILES")) t.quant_tiles = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_CLUSTER")) t.cluster = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_NO_REORDER")) t.no_reorder = std::atoi(e) != 0;
   if (const char* e = std::getenv("TAHOE_NO_SIMHASH")) t.no_simhash = std::atoi(e) != 0;

@@ -218,7 +218,7 @@ def test_multi_chunk_split_and_host_path(oracle):
     assert np.array_equal(d.cpu().numpy().view(np.uint32), host.view(np.uint32))
     p = f.predict(d, strategy=api.SPLIT_SHARED_FOREST)
     torch.cuda.synchronize()
-    assert f.launches() == 2 or os.environ.get("TAHOE_TOP_TREES")   # (forced split of the top-level table: more launches)
+    assert f.launches() == 2 or os.environ.get("TAHOE_TOP_TREES") or os.environ.get("TAHOE_QUANT_TILES")   # (forced variants: more launches)
     sub = np.r_[0:4096, rows - 4096:rows]
     want = oracle.predict_dense(c["nodes"], 500, 10, host[sub], -999.0)
     assert bits_equal(p.cpu().numpy()[sub], want)
@@ -299,3 +299,29 @@ def test_measure_peaks_and_copy_baseline():
         f.predict_host(host.astype(np.float64), strategy=api.SPLIT_SHARED_FOREST)     # the C ABI takes bare pointers: checked here
     with pytest.raises(ValueError):
         f.predict(torch.zeros((10, 17), device="cuda"))
+
+
+@pytest.mark.parametrize("tiles", ["0", "1"])
+def test_quantise_from_rows_and_from_float_tiles_agree(oracle, monkeypatch, tiles):
+    """k_quantize reads the row-major matrix directly, or (strided threshold tables: configs 3 and 4) the column-major
+    float tiles k_float_tiles wrote into the same buffer, ranks going back in place.  Both forms, forced on a dense and
+    on a sparse forest with missing values, NaN and ragged tile ends: the CPU's bits / leaf ids."""
+    import torch
+    monkeypatch.setenv("TAHOE_QUANT_TILES", tiles)
+    c = load_case("susy_like")
+    f = api.Forest.from_dense(c["nodes"], c["trees"], c["depth"], c["cols"], missing=-999.0)
+    for rows in (1, 33, 70_001):
+        host = synth.gen_data(55, rows, 18, miss_frac=0.01, nan_frac=0.01)
+        x = torch.from_numpy(host).cuda()
+        got = f.predict(x, strategy=api.SPLIT_SHARED_FOREST).cpu().numpy()
+        assert f.launches() == (3 if tiles == "1" else 2)
+        assert bits_equal(got, oracle.predict_dense(c["nodes"], c["trees"], c["depth"], host, -999.0)), rows
+    sp, offs, w, _ = synth.gen_sparse_forest(56, 48, 14, 50)
+    fs = api.Forest.from_sparse(sp, offs, 50, weights=w, missing=-999.0)
+    host = synth.gen_data(57, 9_999, 50, miss_frac=0.01, nan_frac=0.01)
+    want, wids = oracle.predict_sparse(sp, offs, host, -999.0, want_leaf_ids=True)
+    ids = torch.zeros((host.shape[0], 48), dtype=torch.int32, device="cuda")
+    got = fs.predict(torch.from_numpy(host).cuda(), strategy=api.SPLIT_SHARED_FOREST, leaf_ids=ids).cpu().numpy()
+    assert np.array_equal(ids.cpu().numpy(), wids)
+    mass = np.abs(sp["val"][offs[:-1][None, :] + wids]).sum(1)
+    assert score_close(got, want, mass)
