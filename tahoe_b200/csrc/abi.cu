@@ -82,7 +82,6 @@ constexpr double kSmemWavefrontsPerLaneVisit = 2.1175e9 / 2.5e10;
 constexpr double kLsuPipeRate = 148.0 * 1.965e9;   // wavefronts/s
 constexpr double kLsuPipeUtil = 0.979;
 constexpr double kSmemVisit = kSmemWavefrontsPerLaneVisit / (kLsuPipeRate * kLsuPipeUtil);   // s per lane-visit, unit plan
-constexpr double kTileStream = 5.0e12;      // B/s of rank tiles re-read once per chunk (half hidden)
 constexpr double kChunkFixed = 4.0e-6;      // stage one chunk + barrier + the ragged end of a pass (config 3: 0.9 ms over 167 chunks)
 constexpr double kTileLevel = 30e-9;        // one level of one traversal group of a tile: this much alone ...
 constexpr double kTileLevelPerWarp = 5e-9;    // ... plus this per warp sharing the SM (16 warps: 110 ns, 8: 70 ns)
