@@ -56,7 +56,7 @@ def _traffic(cfg_id: str):
 def _ncu(cfg_id: str):
     """Counters of the config's dominant kernel from the committed `ncu --set full` capture (profiles/r02_ncu_full_*):
     DRAM GB/s, LSU data pipe, shared-memory wavefronts and bank-conflict wavefronts, threads per warp instruction."""
-    name = {"C3": "r02_ncu_full_C3_cluster_summary.json"}.get(cfg_id, f"r02_ncu_full_{cfg_id}_summary.json")
+    name = f"r02_ncu_full_{cfg_id}_summary.json"
     path = os.path.join(ROOT, "profiles", name)
     if not os.path.exists(path):
         return None
@@ -323,7 +323,34 @@ def measure_config(cfg_id, forest, n_nodes, data, peaks, hbm_gbs, steps, strateg
         rec["frac_smem"] = smem_bytes / sec / 1e9 / peaks["smem_read_gbs"]
         rec["plan"] = {"warps": info.smem_warps, "staged": info.smem_staged, "group": info.smem_group,
                        "trees_per_chunk": info.trees_per_chunk, "chunks": info.num_chunks, "cluster": info.smem_cluster}
+    rec["e2e"] = host_leg(forest, data, preds, s, rows / (step_ms * 1e-3))
     return rec, s, preds
+
+
+def host_leg(forest, data, preds, strategy, device_rate, reps=3):
+    """The same predict through host buffers (tahoe_predict_host: pinned rows in, scores out, copies inside the timed
+    region) and the same slab copies with the kernels left out: what the end-to-end number is bounded by."""
+    import torch
+    rows = int(data.shape[0])
+    h_data = torch.empty(tuple(data.shape), dtype=torch.float32, pin_memory=True)
+    h_data.copy_(data)
+    h_preds = torch.empty(rows, dtype=torch.float32, pin_memory=True)
+    out = {}
+    for key, copy_only in (("copies_only_samples_per_s", True), ("value", False)):
+        forest.predict_host(h_data, h_preds, strategy=strategy, copy_only=copy_only)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            forest.predict_host(h_data, h_preds, strategy=strategy, copy_only=copy_only)
+        torch.cuda.synchronize()
+        out[key] = rows * reps / (time.perf_counter() - t0)
+    out["unit"] = "samples/s"
+    out["h2d_bytes_per_step"] = int(data.numel()) * 4
+    out["d2h_bytes_per_step"] = rows * 4
+    out["matches_device_path"] = bool(torch.equal(h_preds.cuda(), preds))     # bit for bit (the sparse path re-orders its sum per launch shape)
+    out["max_abs_diff_vs_device_path"] = float((h_preds.cuda().double() - preds.double()).abs().max().item())
+    out["frac_of_bound"] = out["value"] / min(device_rate, out["copies_only_samples_per_s"])
+    return out
 
 
 def time_strategy(forest, d, p, s, reps=3):

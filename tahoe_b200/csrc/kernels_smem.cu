@@ -161,9 +161,12 @@ int smem_cluster_size(const tahoe_forest* f) {
   const bool able = !f->sparse && f->quant && !f->staged && f->tile_col_stride == 128u &&
                     f->tile_slot_stride >= ((uint32_t)f->params.num_cols + 2u) * 128u &&
                     f->trees_per_chunk == f->group && f->group >= 2 && f->qdepth >= 10;
-  // default: pairs of CTAs (one TPC).  Same box, interleaved, config 3 at 10M rows: 53.14 / 53.23 / 53.29 ms without,
-  // 52.91 / 52.91 / 52.94 ms with S = 2, and the DRAM traffic of the launch halves (300.7 -> 150.3 GB); S = 4 is slower
-  const int S = std::min(f->tune.cluster >= 0 ? f->tune.cluster : 2, 8);
+  // OPT-IN (TAHOE_CLUSTER=2).  Alone on the GPU, pairs of CTAs run config 3 at equal speed (52.9 vs 53.2 ms) with half the DRAM
+  // traffic and are bit-exact in every test -- but through tahoe_predict_host, where the next slab's small kernels
+  // (k_float_tiles) run CONCURRENTLY with the pipeline, repeated 10M-row calls came back with a few whole tiles wrong at
+  // the slab boundaries (profiles/r02_cluster_pipeline.md, last section; the plain kernel is clean in the same runs).
+  // Until that is understood the plain kernel is the default.
+  const int S = std::min(f->tune.cluster >= 0 ? f->tune.cluster : 0, 8);
   return (able && S > 1 && f->num_chunks >= 2 * S) ? S : 0;
 }
 
