@@ -11,7 +11,7 @@ dev = f.predict(d, strategy=api.SPLIT_SHARED_FOREST).cpu().numpy()
 ref = f.predict(d, strategy=api.DIRECT).cpu().numpy()
 h = torch.empty((rows, c["cols"]), dtype=torch.float32, pin_memory=True); h.copy_(d)
 hp = torch.empty(rows, dtype=torch.float32, pin_memory=True)
-for it in range(3):
+for it in range(int(sys.argv[3]) if len(sys.argv) > 3 else 3):
     f.predict_host(h, hp, strategy=api.SPLIT_SHARED_FOREST)
     got = hp.numpy().copy()
     bad = np.nonzero(got.view(np.uint32) != dev.view(np.uint32))[0]
