@@ -283,7 +283,8 @@ enum {
   TAHOE_EXPORT_QUANT_LUT_MIN = 10,  /* float [C] */
   TAHOE_EXPORT_QUANT_LUT_SCALE = 11, /* float [C] */
   TAHOE_EXPORT_SD_TOP_NODES = 12,  /* uint2 [2^sd_top_levels - 1][Tpad] leaves pushed down (empty unless sd_blocked) */
-  TAHOE_EXPORT_SD_BLOCKS = 13,     /* uint32 [block][Tpad][8] = {root, left, right, 0} x {val bits, meta} */
+  TAHOE_EXPORT_SD_BLOCKS = 13,     /* uint32 [block][Tpad][8] = {root, left, right, 0} x {val bits, word}; word (also in SD_TOP_NODES) = byte offset of the feature in the row | bit 31: a missing value takes child slot 1 |
+                                      bit 30: children exchanged (v >= thr takes slot 0) | bit 29: pushed-down copy of a leaf */
   TAHOE_EXPORT_SD_ORIG_BOTTOM = 14, /* int32 [2^depth][Tpad] bottom position -> original heap id of the leaf */
   TAHOE_EXPORT_SPARSE_BFS = 15,      /* uint2 [nodes] sparse trees renumbered breadth-first: {val, leaf<<31|def_left<<30|delta<<fid_bits|fid} */
   TAHOE_EXPORT_SPARSE_BFS_ORIG = 16, /* int32 [nodes] breadth-first index -> caller's node index inside its tree */

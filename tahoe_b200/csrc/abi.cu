@@ -348,7 +348,7 @@ void tahoe_forest_destroy(tahoe_forest_t* f) {
   cudaFree(f->d_tree_order); cudaFree(f->d_orig_ids);
   cudaFree(f->d_sp_full); cudaFree(f->d_sp_orig); cudaFree(f->d_sp_top); cudaFree(f->d_sp_qblocks);
   cudaFree(f->d_sp_qblock_orig); cudaFree(f->d_sp_qblock_offsets);
-  cudaFree(f->d_sd_top_nodes); cudaFree(f->d_sd_blocks); cudaFree(f->d_sd_orig_bottom); cudaFree(f->d_qwords); cudaFree(f->d_qtable);
+  cudaFree(f->d_sd_top_image); cudaFree(f->d_sd_blocks); cudaFree(f->d_sd_orig_bottom); cudaFree(f->d_qwords); cudaFree(f->d_qtable);
   cudaFree(f->d_qoffsets); cudaFree(f->d_leaf_origin);
   cudaFree(f->d_qlut_min); cudaFree(f->d_qlut_scale); cudaFree(f->d_qlut);
   for (auto& w : f->ws) free_workspace(w);

@@ -31,6 +31,11 @@ constexpr int kMetaFidMask = (1 << 29) - 1;      // I8: fid in bits 0..28
 constexpr uint32_t kMetaExchange = 1u << 29;     // I8 only (reference EXCHANGE_MASK_INT is bit 31, Struct.h:64)
 constexpr uint32_t kMetaDefLeft = 1u << 30;      // same bit as the reference's DEF_LEFT_MASK, Struct.h:58
 constexpr uint32_t kMetaLeaf = 1u << 31;         // same bit as IS_LEAF_MASK, Struct.h:59
+// B32 (SHARED_DATA blocks, plan_shared_data): the node's second word as the walk wants it
+constexpr uint32_t kSdMissRight = 1u << 31;      // a missing feature goes to the right CHILD SLOT (default direction and exchange folded)
+constexpr uint32_t kSdFlip = 1u << 30;           // children exchanged: v >= thr goes to the LEFT child slot
+constexpr uint32_t kSdLeaf = 1u << 29;           // pushed-down copy of a leaf (both children are the same leaf; feature offset 0)
+constexpr uint32_t kSdOffMask = (1u << 29) - 1;  // byte offset of the feature inside the row
 
 // Shared-memory-forest kernel: the plan (warps per CTA, tile buffering, trees per traversal group)
 // is chosen per forest at pack time (plan_chunks) and is all run-time state of the handle; the
@@ -78,6 +83,7 @@ struct HostPack {
   // (shared-memory copy), the levels below in two-level blocks {root, left, right, -} of 32 bytes --
   // one L2 sector serves two levels of a walk
   std::vector<uint2> sd_top_nodes;    // [2^sd_top - 1][tpad]
+  std::vector<uint2> sd_top_image;    // [2^sd_top - 1][sd_top_stride], padded to 16 bytes: what the kernel copies to shared memory
   std::vector<uint4> sd_blocks;       // [block][tpad][2]; block order: level sd_top roots, level sd_top+2 roots, ...
   std::vector<int32_t> sd_orig_bottom;  // [2^d][tpad] bottom position -> original heap id of the leaf reached
   // Q4
@@ -174,6 +180,7 @@ struct tahoe_forest {
   int sd_row_bufs = 2;           // row buffers per team (1: single-buffered, twice the teams)
   int sd_top = 0;                // forest levels copied to shared memory
   bool sd_blocked = false;       // B32 two-level blocks below the top levels
+  int sd_top_stride = 0;         // slots per node in the shared-memory copy of the top levels (tpad, or the tree count)
   size_t sd_smem = 0;
 
   // per-class outputs (tahoe_forest_create_sparse_classes): class k owns packed trees
@@ -198,7 +205,7 @@ struct tahoe_forest {
   uint2* d_inter = nullptr;
   int32_t* d_tree_order = nullptr;
   int32_t* d_orig_ids = nullptr;
-  uint2* d_sd_top_nodes = nullptr;
+  uint2* d_sd_top_image = nullptr;
   uint4* d_sd_blocks = nullptr;
   int32_t* d_sd_orig_bottom = nullptr;
   uint32_t* d_qwords = nullptr;

@@ -33,13 +33,16 @@ struct SharedDataParams {
   int teams_per_block;       // a team = team_warps warps sharing one row (two row buffers)
   int team_warps;            // 1, 2 or 4
   int top_levels;            // levels 0..top_levels-1 of the interleaved forest are copied to shared memory
-  uint32_t top_off;          // byte offset of that copy ([2^top_levels - 1][tpad] uint2)
+  uint32_t top_off;          // byte offset of that copy ([2^top_levels - 1][top_stride] uint2)
+  int top_stride;            //   slots per node in it: tpad, or num_trees (blocked walk: padding slots left out)
+  uint32_t top_bytes;        //   its size (blocked walk: the packer's image, a multiple of 16 bytes, copied as it is)
   // B32 (BLOCKED kernels): the copy comes from top_nodes (leaves pushed down); levels top_levels..depth
   // are walked two at a time through 32-byte blocks {root, left, right, -}
-  const uint2* top_nodes;    // [2^top_levels - 1][tpad]
+  const uint2* top_nodes;    // [2^top_levels - 1][top_stride]: the image of the shared-memory copy
   const uint4* blocks;       // [block][tpad][2]
   const int32_t* orig_bottom;  // [2^depth][tpad]
-  int block_levels;          // (depth + 1 - top_levels) / 2 >= 1
+  int block_levels;          // L2 trips below the top: (depth + 1 - top_levels) / 2 >= 1
+  int l2_ahead;              // single-buffer teams: prefetch the next row into L2 during the walk
   int row_bufs;              // row buffers per team: 2 = the next row streams in under the walk; 1 = twice the teams,
                              // a team's own load latency exposed, hidden by the other teams of the SM
 };
@@ -126,64 +129,124 @@ __device__ __forceinline__ double sd_walk_row(const SharedDataParams& p, const u
 // B32 walk of one row: top_levels (>= 1) levels from shared memory, then block_levels L2 trips of
 // two levels each.  Leaves are pushed down in this layout, so every walk makes exactly `depth`
 // decisions and ends on the bottom level -- no leaf test in the loop, no early exit.
-template <int kSdGroup>
-__device__ __forceinline__ double sd_walk_row_blocked(const SharedDataParams& p, const uint2* s_top, const float* my,
+// The kernel is bound by the INSTRUCTIONS of these walks (clock64 around the walk: its time grows in
+// proportion to the teams per SM whatever the split between shared-memory levels and L2 trips;
+// profiles/r02_c1_walk_cycles.md), so the node's second word is stored the way a decision uses it
+// (kSd* in forest.h) and all addresses are 32-bit byte offsets.
+//   top / my: the top levels [node][tpad] uint2 and the team's row, both in shared memory.
+// The child SLOT a walk takes at one node, as 1 / 2 (the heap step is n = 2n + that): the reference's test (BaseTahoeTest.h:450-452: a missing value
+// follows the default direction, else v >= thr goes right) with the exchange of Struct.h:980 folded into the two
+// flag bits of the node word.  Written as PTX so that each flag costs one predicate-setting instruction.
+// NANM: the sentinel is NaN, so "missing" means "is NaN" (device_utils.cuh, is_missing).
+template <bool NANM>
+__device__ __forceinline__ uint32_t sd_child(float v, uint32_t thr, uint32_t word, float missing) {
+  uint32_t c;
+  if (NANM) {
+    asm("{\n"
+        ".reg .pred pm, pf, pg, pa;\n"
+        ".reg .b32 t;\n"
+        "setp.nan.f32 pm, %1, %1;\n"
+        "and.b32 t, %3, 0x40000000;\n"
+        "setp.ne.u32 pf, t, 0;\n"
+        "setp.ge.f32 pg, %1, %2;\n"
+        "xor.pred pg, pg, pf;\n"
+        "setp.lt.s32 pa, %3, 0;\n"
+        "and.pred pa, pa, pm;\n"
+        "and.pred pg, pg, !pm;\n"
+        "or.pred pg, pg, pa;\n"
+        "selp.u32 %0, 2, 1, pg;\n"
+        "}\n"
+        : "=r"(c) : "f"(v), "f"(__uint_as_float(thr)), "r"(word), "f"(missing));
+  } else {
+    asm("{\n"
+        ".reg .pred pm, pf, pg, pa;\n"
+        ".reg .b32 t;\n"
+        ".reg .f32 d;\n"
+        "sub.f32 d, %1, %4;\n"
+        "abs.f32 d, d;\n"
+        "setp.le.f32 pm, d, 0f358637BD;\n"
+        "and.b32 t, %3, 0x40000000;\n"
+        "setp.ne.u32 pf, t, 0;\n"
+        "setp.ge.f32 pg, %1, %2;\n"
+        "xor.pred pg, pg, pf;\n"
+        "setp.lt.s32 pa, %3, 0;\n"
+        "and.pred pa, pa, pm;\n"
+        "and.pred pg, pg, !pm;\n"
+        "or.pred pg, pg, pa;\n"
+        "selp.u32 %0, 2, 1, pg;\n"
+        "}\n"
+        : "=r"(c) : "f"(v), "f"(__uint_as_float(thr)), "r"(word), "f"(missing));
+  }
+  return c;
+}
+
+template <int kSdGroup, bool NANM>
+__device__ __forceinline__ double sd_walk_row_blocked(const SharedDataParams& p, const uint8_t* top, const uint8_t* my,
                                                       size_t row, int lane, int wt) {
   double acc = 0.0;
   const int gstride = 32 * p.team_warps;
-  auto decide = [&](uint32_t val, uint32_t meta) -> uint32_t {
-    const bool leaf = (meta & kMetaLeaf) != 0;     // a pushed-down copy: both children are the same leaf
-    const float v = my[leaf ? 0u : (meta & kMetaFidMask)];
-    const bool c = branch_right(v, __uint_as_float(val), meta & kMetaDefLeft, p.missing);
-    return (c != ((meta & kMetaExchange) != 0)) ? 1u : 0u;       // Struct.h:980
+  const uint32_t tpad8 = (uint32_t)p.top_stride * 8u, tpad32 = (uint32_t)p.tpad * 32u;   // (top levels | blocks)
+  const float missing = p.missing;
+  auto decide = [&](uint32_t val, uint32_t word) -> uint32_t {
+    return sd_child<NANM>(*reinterpret_cast<const float*>(my + (word & kSdOffMask)), val, word, missing);
   };
-  for (int s0 = lane + 32 * wt; s0 < p.tpad; s0 += gstride * kSdGroup) {
-    uint32_t q[kSdGroup];      // position inside the current level
-    int slot[kSdGroup];
+  auto lds_node = [&](uint32_t off) -> uint2 { return *reinterpret_cast<const uint2*>(top + off); };
+  const int nslots = p.num_trees;                    // slots 0 .. num_trees-1 hold the trees; the rest is padding
+  const uint32_t level_first = (1u << p.top_levels) - 1u;
+  for (int s0 = lane + 32 * wt; s0 < nslots; s0 += gstride * kSdGroup) {
+    uint32_t n[kSdGroup];      // heap index inside the top, then position inside the current level
+    uint32_t slot[kSdGroup];
     uint2 e[kSdGroup];
 #pragma unroll
     for (int g = 0; g < kSdGroup; ++g) {
-      slot[g] = min(s0 + gstride * g, p.tpad - 1);   // past the end: repeat the last slot, drop its sum
-      q[g] = 0;
-      e[g] = s_top[slot[g]];
+      // past the last tree: repeat its walk (the same addresses as the lane that owns it) and drop the sum
+      slot[g] = (uint32_t)min(s0 + gstride * g, nslots - 1);
+      n[g] = 0;
+      e[g] = lds_node(slot[g] * 8u);
     }
-    for (int l = 0; l < p.top_levels; ++l) {         // decisions on levels 0 .. top_levels-1
-      const uint32_t next_first = (2u << l) - 1u;
+    for (int l = 1; l < p.top_levels; ++l) {          // decisions on levels 0 .. top_levels-2, next node fetched
 #pragma unroll
       for (int g = 0; g < kSdGroup; ++g) {
-        q[g] = 2 * q[g] + decide(e[g].x, e[g].y);
-        if (l + 1 < p.top_levels) e[g] = s_top[(size_t)(next_first + q[g]) * p.tpad + slot[g]];
+        n[g] = 2 * n[g] + decide(e[g].x, e[g].y);
+        e[g] = lds_node(slot[g] * 8u + n[g] * tpad8);
       }
     }
-    size_t base = 0;
-    float leaf_val[kSdGroup];
-    for (int j = 0; j < p.block_levels; ++j) {
+#pragma unroll
+    for (int g = 0; g < kSdGroup; ++g)                // the top's last level: position inside level top_levels
+      n[g] = 2 * n[g] + decide(e[g].x, e[g].y) - level_first;
+    const uint8_t* blocks = reinterpret_cast<const uint8_t*>(p.blocks);
+    uint32_t base = 0;
+    for (int j = 1; j < p.block_levels; ++j) {        // every trip but the last: two decisions
       uint32_t w[kSdGroup][8];
 #pragma unroll
       for (int g = 0; g < kSdGroup; ++g)
-        ldg_block(p.blocks + ((base + q[g]) * p.tpad + slot[g]) * 2, w[g]);
-      const bool last = j + 1 == p.block_levels;
+        ldg_block(reinterpret_cast<const uint4*>(blocks + (size_t)((base + n[g]) * tpad32 + slot[g] * 32u)), w[g]);
+      uint32_t c0[kSdGroup];
 #pragma unroll
-      for (int g = 0; g < kSdGroup; ++g) {
-        const uint32_t c0 = decide(w[g][0], w[g][1]);
-        const uint32_t cv = c0 ? w[g][4] : w[g][2], cm = c0 ? w[g][5] : w[g][3];
-        if (last) {                                  // the child is the bottom-level leaf
-          q[g] = 2 * q[g] + c0;
-          leaf_val[g] = __uint_as_float(cv);
-        } else {
-          q[g] = 4 * q[g] + 2 * c0 + decide(cv, cm);
-        }
-      }
-      base += (size_t)1 << (p.top_levels + 2 * j);
+      for (int g = 0; g < kSdGroup; ++g) c0[g] = decide(w[g][0], w[g][1]);
+#pragma unroll
+      for (int g = 0; g < kSdGroup; ++g)     // (decide is 1 or 2: child slot + 1)
+        n[g] = 4 * n[g] + 2 * c0[g] + decide(c0[g] == 2 ? w[g][4] : w[g][2], c0[g] == 2 ? w[g][5] : w[g][3]) - 3;
+      base += 1u << (p.top_levels + 2 * (j - 1));
+    }
+    float leaf_val[kSdGroup];
+    // the last trip: one decision; the children are the bottom-level leaves
+    uint32_t w[kSdGroup][8];
+#pragma unroll
+    for (int g = 0; g < kSdGroup; ++g)
+      ldg_block(reinterpret_cast<const uint4*>(blocks + (size_t)((base + n[g]) * tpad32 + slot[g] * 32u)), w[g]);
+#pragma unroll
+    for (int g = 0; g < kSdGroup; ++g) {
+      const uint32_t c0 = decide(w[g][0], w[g][1]);
+      leaf_val[g] = __uint_as_float(c0 == 2 ? w[g][4] : w[g][2]);
+      n[g] = 2 * n[g] + c0 - 1;
     }
 #pragma unroll
     for (int g = 0; g < kSdGroup; ++g) {
-      if (s0 + gstride * g >= p.tpad) continue;
-      acc += (double)leaf_val[g];                    // padding slots are leaves holding 0.0f
-      if (p.leaf_ids) {
-        const int t = p.tree_order[slot[g]];
-        if (t >= 0) p.leaf_ids[row * (size_t)p.num_trees + t] = p.orig_bottom[(size_t)q[g] * p.tpad + slot[g]];
-      }
+      if (s0 + gstride * g >= nslots) continue;
+      acc += (double)leaf_val[g];
+      if (p.leaf_ids)
+        p.leaf_ids[row * (size_t)p.num_trees + p.tree_order[slot[g]]] = p.orig_bottom[(size_t)n[g] * p.tpad + slot[g]];
     }
   }
 #pragma unroll
@@ -211,17 +274,6 @@ __global__ void __launch_bounds__(1024, 1) k_shared_data(SharedDataParams p) {
   const size_t stride = (size_t)gridDim.x * p.teams_per_block;
   const uint32_t row_bytes = (uint32_t)p.cols * 4u;
 
-  if (TMA && wt == 0 && lane == 0) { mbar_init(bar0, 1); mbar_init(bar0 + 8, 1); fence_mbar_init(); }
-  const uint2* s_top = reinterpret_cast<const uint2*>(sd_smem + p.top_off);
-  {
-    uint2* dst = reinterpret_cast<uint2*>(sd_smem + p.top_off);
-    const int n_top = p.top_levels > 0 ? ((1 << p.top_levels) - 1) * p.tpad : 0;
-    const uint2* src = BLOCKED ? p.top_nodes : p.inter;
-    for (int i = threadIdx.x; i < n_top; i += blockDim.x) dst[i] = __ldg(src + i);
-  }
-  __syncthreads();
-  // (a 16th team on hardware barrier 0 fits shared memory for config 1 and was measured: 0.1453 vs 0.1426 ms with 15)
-
   auto load_row_tma = [&](size_t row, int b) {       // team warp 0, lane 0
     fence_proxy_async();
     mbar_expect_tx(bar0 + b * 8, row_bytes);
@@ -233,6 +285,33 @@ __global__ void __launch_bounds__(1024, 1) k_shared_data(SharedDataParams p) {
       done += piece;
     }
   };
+  // the team's first row starts to stream in before the CTA copies the forest's top levels
+  if (TMA && wt == 0 && lane == 0) {
+    mbar_init(bar0, 1); mbar_init(bar0 + 8, 1); fence_mbar_init();
+    if (team_global < p.rows) load_row_tma(team_global, 0);
+  }
+  const uint2* s_top = reinterpret_cast<const uint2*>(sd_smem + p.top_off);
+  const uint32_t top_bar = smem_u32(sd_smem) + p.top_off + p.top_bytes;     // (in the 128 spare bytes behind the copy)
+  if (BLOCKED) {
+    // the packer's image of the top levels ([node][top_stride], a multiple of 16 bytes) by bulk copies, under the
+    // teams' first rows
+    if (threadIdx.x == 0) {
+      mbar_init(top_bar, 1);
+      fence_mbar_init();
+      mbar_expect_tx(top_bar, p.top_bytes);
+      for (uint32_t done = 0; done < p.top_bytes; done += 65536u)
+        bulk_g2s(smem_u32(sd_smem) + p.top_off + done, reinterpret_cast<const uint8_t*>(p.top_nodes) + done,
+                 min(p.top_bytes - done, 65536u), top_bar);
+    }
+  } else {
+    uint2* dst = reinterpret_cast<uint2*>(sd_smem + p.top_off);
+    const int n_top = p.top_levels > 0 ? ((1 << p.top_levels) - 1) * p.tpad : 0;
+    for (int i = threadIdx.x; i < n_top; i += blockDim.x) dst[i] = __ldg(p.inter + i);
+  }
+  __syncthreads();
+  if (BLOCKED) mbar_wait(top_bar, 0);
+  // (a 16th team on hardware barrier 0 fits shared memory for config 1 and was measured: 0.1453 vs 0.1426 ms with 15)
+
   // LSU path: short rows wait in registers (one tile ahead) and are stored when their turn comes;
   // rows too long for that are copied synchronously
   constexpr int kStage = 4;
@@ -261,12 +340,18 @@ __global__ void __launch_bounds__(1024, 1) k_shared_data(SharedDataParams p) {
     for (int i = t; i < p.cols; i += team_threads) m[i] = __ldg(g + i);
   };
 
+  // one buffer per team: the row after this one is asked into L2 while this one is walked (no shared memory
+  // needed for it), so the team's own bulk copy finds it there instead of waiting for HBM
+  auto prefetch_row_l2 = [&](size_t row) {            // one lane
+    const uint8_t* src = reinterpret_cast<const uint8_t*>(p.data + row * (size_t)p.cols);
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(row_bytes & ~15u) : "memory");
+  };
+  const bool l2_ahead = TMA && nb == 1 && p.l2_ahead;
   uint32_t phase = 0;
-  int b = 0;
+  int b = 0, pp = 0;
+  const bool nan_missing = p.missing != p.missing;
   size_t row = team_global;
-  if (TMA) {
-    if (row < p.rows && wt == 0 && lane == 0) load_row_tma(row, 0);
-  } else if (row < p.rows && staged) {
+  if (!TMA && row < p.rows && staged) {
     fetch_row(row);
   }
   for (; row < p.rows; row += stride) {
@@ -274,6 +359,7 @@ __global__ void __launch_bounds__(1024, 1) k_shared_data(SharedDataParams p) {
     if (TMA) {
       // buffer b^1 was last read for the previous row; the team barrier at its end released it
       if (nb == 2 && next < p.rows && wt == 0 && lane == 0) load_row_tma(next, b ^ 1);
+      if (l2_ahead && next < p.rows && wt == p.team_warps - 1 && lane == 0) prefetch_row_l2(next);
       mbar_wait(bar0 + b * 8, (phase >> b) & 1u);
       phase ^= 1u << b;
     } else {
@@ -286,18 +372,22 @@ __global__ void __launch_bounds__(1024, 1) k_shared_data(SharedDataParams p) {
       team_barrier(1 + team, team_threads);           // the team's stores of this row are visible
     }
     const float* my = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(buf0) + (size_t)b * row_stride);
-    const double acc = BLOCKED ? sd_walk_row_blocked<G>(p, s_top, my, row, lane, wt)
-                               : sd_walk_row<G>(p, s_top, my, row, lane, wt);
-    if (lane == 0) partials[b * 4 + wt] = acc;
+    double acc;
+    if (!BLOCKED) acc = sd_walk_row<G>(p, s_top, my, row, lane, wt);
+    else if (nan_missing) acc = sd_walk_row_blocked<G, true>(p, sd_smem + p.top_off, reinterpret_cast<const uint8_t*>(my), row, lane, wt);
+    else acc = sd_walk_row_blocked<G, false>(p, sd_smem + p.top_off, reinterpret_cast<const uint8_t*>(my), row, lane, wt);
+    if (lane == 0) partials[pp * 4 + wt] = acc;    // (two sets: a fast warp's next row cannot overwrite what warp 0 still reads)
     team_barrier(1 + team, team_threads);
+    // one buffer: the team barrier above released it; the next row starts to stream in now (issued by the team's
+    // LAST warp while its first one writes the score)
+    if (TMA && nb == 1 && next < p.rows && wt == p.team_warps - 1 && lane == 0) load_row_tma(next, 0);
     if (wt == 0 && lane == 0) {
       double sum = 0.0;
-      for (int w = 0; w < p.team_warps; ++w) sum += partials[b * 4 + w];   // fixed order: reproducible
+      for (int w = 0; w < p.team_warps; ++w) sum += partials[pp * 4 + w];   // fixed order: reproducible
       p.preds[row] = apply_transform((float)sum, p.tf);
-      // one buffer: the team barrier above released it; the next row starts to stream in now
-      if (TMA && nb == 1 && next < p.rows) load_row_tma(next, 0);
     }
     b ^= (int)(nb - 1);
+    pp ^= 1;
   }
 }
 
@@ -323,10 +413,12 @@ int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches) {
   // the plan (teams, top levels, B32 blocks) was made when the forest was packed: plan_shared_data
   p.team_warps = f->sd_team_warps;
   p.top_levels = f->sd_top;
+  p.top_stride = f->sd_top_stride;
   p.teams_per_block = f->sd_teams;
-  p.top_nodes = f->d_sd_top_nodes; p.blocks = f->d_sd_blocks; p.orig_bottom = f->d_sd_orig_bottom;
+  p.top_nodes = f->d_sd_top_image; p.top_bytes = (uint32_t)(f->host.sd_top_image.size() * sizeof(uint2)); p.blocks = f->d_sd_blocks; p.orig_bottom = f->d_sd_orig_bottom;
   p.block_levels = f->sd_blocked ? (f->depth + 1 - f->sd_top) / 2 : 0;
   p.row_bufs = f->sd_row_bufs;
+  p.l2_ahead = std::getenv("TAHOE_SD_NO_L2_AHEAD") ? 0 : 1;
   const size_t per_team = (size_t)p.row_bufs * row_stride + 64 + 16;    // row buffers, partials, mbarriers
   p.top_off = (uint32_t)(((size_t)p.teams_per_block * per_team + 127) / 128 * 128);
   const size_t smem = f->sd_smem;

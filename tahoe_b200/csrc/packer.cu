@@ -219,9 +219,16 @@ void plan_shared_data(tahoe_forest* f) {
   f->sd_blocked = false;
   if (per_team + 128 > (size_t)f->smem_optin) return;  // SHARED_DATA not applicable: two rows do not fit
   const int max_teams = std::min(15, 32 / f->sd_team_warps);          // named barriers 1..15; 1024 threads
-  auto top_bytes = [&](int top) { return top ? (((size_t)1 << top) - 1) * tpad * sizeof(uint2) : (size_t)0; };
-  auto teams_for = [&](int top) {
-    return (int)std::min<size_t>((size_t)max_teams, ((size_t)f->smem_optin - 128 - top_bytes(top)) / per_team);
+  // the shared-memory copy of the top levels is [node][stride] uint2: the blocked walk skips the padding slots
+  // (stride = trees: config 1 keeps 7 levels of its 100 trees in 102 KB instead of 130), the plain walk keeps
+  // stride = tpad (bank = slot: conflict-free)
+  const bool tight = !std::getenv("TAHOE_SD_LOOSE_TOP");
+  auto top_stride = [&](bool blocked) { return (size_t)(blocked && tight ? f->params.num_trees : tpad); };
+  auto top_bytes = [&](int top, bool blocked) {
+    return top ? ((((size_t)1 << top) - 1) * top_stride(blocked) * sizeof(uint2) + 15) / 16 * 16 : (size_t)0;
+  };
+  auto teams_for = [&](int top, bool blocked) {
+    return (int)std::min<size_t>((size_t)max_teams, ((size_t)f->smem_optin - 256 - top_bytes(top, blocked)) / per_team);   // (128 of slack + the round-up of the team region)
   };
   // blocked form: top levels K with (d + 1 - K) even and K <= d - 1, blocks small enough to keep
   const char* eb = std::getenv("TAHOE_SD_BLOCKED");
@@ -229,31 +236,44 @@ void plan_shared_data(tahoe_forest* f) {
   int best_top = 0;
   bool best_blocked = false;
   double best_rate = 0.0;
+  // Below the top a blocked walk makes (d - top) decisions, two per L2 trip, the last trip's children being the
+  // bottom-level leaves: (d + 1 - top) must be even.  (A 64-byte tail block -- two decisions and the leaf in one
+  // trip, for the even splits -- was built in round 2 and is slower at every split of config 1:
+  // profiles/r02_c1_walk_cycles.md.)
+  auto trips_for = [&](int top) { return (d + 1 - top) / 2; };
+  auto blocked_bytes = [&](int top) {
+    size_t roots = 0;
+    for (int L = top; L < d; L += 2) roots += (size_t)1 << L;
+    return roots * 32 * tpad;
+  };
+  auto blocked_ok = [&](int top) {
+    return want_blocked && top >= 1 && top <= d - 1 && !((d + 1 - top) & 1) && row_bytes <= kSdOffMask &&
+           blocked_bytes(top) <= ((size_t)512 << 20);
+  };
   for (int blocked = 0; blocked <= (want_blocked ? 1 : 0); ++blocked) {
     for (int top = blocked ? 1 : 0; top <= (blocked ? d - 1 : d + 1); ++top) {
-      if (blocked && ((d + 1 - top) & 1)) continue;
-      if (top_bytes(top) + per_team + 128 > (size_t)f->smem_optin) break;
-      if (blocked) {
-        size_t roots = 0;
-        for (int L = top; L < d; L += 2) roots += (size_t)1 << L;
-        if (roots * tpad * 32 > ((size_t)512 << 20)) continue;
-      }
-      const int below = d + 1 - top;
-      const double rate = teams_for(top) / (100.0 * top + 800.0 * (blocked ? below / 2 : below) + 200.0);
+      if (top_bytes(top, blocked != 0) + per_team + 128 > (size_t)f->smem_optin) break;
+      if (blocked && !blocked_ok(top)) continue;
+      // What the plans of config 1 measure (profiles/r02_c1_walk_cycles.md): the SM's rows per cycle hardly depend on
+      // the teams once ~10 of them keep it busy (a walk takes longer in proportion), an L2 trip costs a little more
+      // than two shared-memory levels, and fewer trips win: 7 levels + 1 trip with 10 teams beats 5 + 2 with 15.
+      const double rate = std::min(teams_for(top, blocked != 0), 10) /
+                          (60.0 * top + 160.0 * (blocked ? trips_for(top) : d + 1 - top) + 100.0);
       if (rate > best_rate) { best_rate = rate; best_top = top; best_blocked = blocked != 0; }
     }
   }
   if (const char* e = std::getenv("TAHOE_SD_TOP_LEVELS")) {
     int top = std::max(0, std::min(std::atoi(e), d + 1));
-    if (top_bytes(top) + per_team + 128 <= (size_t)f->smem_optin) {
+    if (top_bytes(top, blocked_ok(top)) + per_team + 128 <= (size_t)f->smem_optin) {
       best_top = top;
-      best_blocked = want_blocked && top >= 1 && top <= d - 1 && !((d + 1 - top) & 1);
+      best_blocked = blocked_ok(top);
     }
   }
   f->sd_top = best_top;
   f->sd_blocked = best_blocked;
-  f->sd_teams = teams_for(best_top);
-  f->sd_smem = ((size_t)f->sd_teams * per_team + 127) / 128 * 128 + top_bytes(best_top) + 128;
+  f->sd_teams = teams_for(best_top, best_blocked);
+  f->sd_top_stride = (int)top_stride(best_blocked);
+  f->sd_smem = ((size_t)f->sd_teams * per_team + 127) / 128 * 128 + top_bytes(best_top, best_blocked) + 128;
   if (!best_blocked) return;
 
   const int K = best_top;
@@ -273,6 +293,14 @@ void plan_shared_data(tahoe_forest* f) {
       pd[k] = node;
       po[k] = o;
     }
+    // the walk's own node form (kSd* in forest.h): byte offset of the feature, the exchange bit folded into the
+    // outcome of a missing value and into a flip of the comparison -- a decision is six instructions shorter
+    for (int64_t k = 0; k < npt; ++k) {
+      const uint32_t y = pd[k].y;
+      if (y & kMetaLeaf) { pd[k].y = kSdLeaf; continue; }          // pushed down: both children are this leaf
+      const bool exch = (y & kMetaExchange) != 0, def_left = (y & kMetaDefLeft) != 0;
+      pd[k].y = ((!def_left) != exch ? kSdMissRight : 0u) | (exch ? kSdFlip : 0u) | ((y & kMetaFidMask) * 4u);
+    }
     for (int64_t k = 0; k < ((int64_t)1 << K) - 1; ++k) h.sd_top_nodes[(size_t)k * tpad + slot] = pd[k];
     size_t base = 0;
     for (int L = K; L < d; L += 2) {
@@ -288,6 +316,10 @@ void plan_shared_data(tahoe_forest* f) {
     const int64_t bottom = ((int64_t)1 << d) - 1;
     for (int64_t q = 0; q < ((int64_t)1 << d); ++q) h.sd_orig_bottom[(size_t)q * tpad + slot] = po[bottom + q];
   }
+  const size_t top_nodes = ((size_t)1 << K) - 1, stride = (size_t)f->sd_top_stride;
+  h.sd_top_image.assign((top_nodes * stride + 1) / 2 * 2, make_uint2(0, kSdLeaf));
+  for (size_t k = 0; k < top_nodes; ++k)
+    for (size_t slot = 0; slot < stride; ++slot) h.sd_top_image[k * stride + slot] = h.sd_top_nodes[k * tpad + slot];
 }
 
 // ---- Q4: rank-quantised heap ------------------------------------------------------
@@ -1010,7 +1042,7 @@ int upload(tahoe_forest* f) {
   if ((rc = to_device(&f->d_inter, h.inter))) return rc;
   if ((rc = to_device(&f->d_tree_order, h.tree_order))) return rc;
   if ((rc = to_device(&f->d_orig_ids, h.orig_ids))) return rc;
-  if ((rc = to_device(&f->d_sd_top_nodes, h.sd_top_nodes))) return rc;
+  if ((rc = to_device(&f->d_sd_top_image, h.sd_top_image))) return rc;
   if ((rc = to_device(&f->d_sd_blocks, h.sd_blocks))) return rc;
   if ((rc = to_device(&f->d_sd_orig_bottom, h.sd_orig_bottom))) return rc;
   if (!h.qwords.empty()) {   // padded with all-zero trees to whole traversal groups

@@ -3,6 +3,7 @@ They let the CPU suite localise packer bugs without a GPU.  Not a product path."
 import numpy as np
 
 LEAF, DEFLEFT, EXCH, FIDMASK = 1 << 31, 1 << 30, 1 << 29, (1 << 29) - 1
+SD_MISSRIGHT, SD_FLIP, SD_LEAF, SD_OFFMASK = 1 << 31, 1 << 30, 1 << 29, (1 << 29) - 1     # B32 blocks (SHARED_DATA)
 
 
 def _right(v, thr, def_left, missing):
@@ -79,10 +80,14 @@ def blocked_traverse(top_nodes, blocks, orig_bottom, tree_order, tpad, depth, K,
     ids = np.zeros((R, T), np.int32)
 
     def decide(val, meta):
-        leaf = (meta & LEAF) != 0
-        fid = np.where(leaf, 0, (meta & FIDMASK).astype(np.int64))
-        c = _right(data[rows, fid], val.view(np.float32), (meta & DEFLEFT) != 0, missing)
-        return np.where((meta & EXCH) != 0, ~c, c).astype(np.int64)
+        # the walk's own node word (kSd* in forest.h): byte offset of the feature; bit 31 = a missing value takes
+        # child slot 1; bit 30 = the children are exchanged (v >= thr takes slot 0); bit 29 = pushed-down leaf
+        assert np.all((meta & SD_OFFMASK) % 4 == 0) and np.all(((meta & SD_LEAF) == 0) | ((meta & SD_OFFMASK) == 0))
+        v = data[rows, (meta & SD_OFFMASK).astype(np.int64) // 4]
+        with np.errstate(invalid="ignore"):
+            miss = np.isnan(v) if np.isnan(missing) else np.abs((v - np.float32(missing)).astype(np.float32)) <= np.float32(1e-6)
+            ge = v >= val.view(np.float32)
+        return np.where(miss, (meta & SD_MISSRIGHT) != 0, ge != ((meta & SD_FLIP) != 0)).astype(np.int64)
 
     for slot in range(tpad):
         t = tree_order[slot]
@@ -98,7 +103,7 @@ def blocked_traverse(top_nodes, blocks, orig_bottom, tree_order, tpad, depth, K,
             cm = np.where(c0 == 1, w[:, 5], w[:, 3])
             if j == J - 1:
                 q = 2 * q + c0
-                assert np.all(cm & LEAF)
+                assert np.all(cm & SD_LEAF)
                 leaf_val = cv
             else:
                 q = 4 * q + 2 * c0 + decide(cv, cm)
