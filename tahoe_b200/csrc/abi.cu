@@ -69,7 +69,8 @@ constexpr double kRowGather = 1.7e12;       // B/s of 32-byte row sectors gather
 constexpr double kForestHalf = 80e6;        // forest bytes at which the L2-gather rates halve
 constexpr double kTeamLevel = 0.7e-6;       // SHARED_DATA: one tree level of a row's walk (latency-bound)
 constexpr double kSharedDataRate = 7.0e11;  // visits/s (slot-levels), SHARED_DATA
-constexpr double kRowStream = 4.6e12;       // B/s of sample rows through a TMA-fed SHARED_DATA kernel (ncu config 1: 620.7 MB of DRAM traffic in 133.3 us)
+constexpr double kTilePass = 4.6e12;        // B/s through the tile pass of the 8-byte sparse tops (read + write)
+constexpr double kRowStream = 6.0e12;       // B/s of sample rows through a TMA-fed SHARED_DATA kernel (config 1: 614 MB in 0.109 ms at 50K rows, 2.46 GB in 0.364 ms at 200K)
 // The shared-memory forest's rate is DERIVED FROM NCU COUNTERS of the unit plan (config 2, 16 warps x 5 trees staged,
 // parameter-table levels; profiles/r02_ncu_full_C2_summary.json), not fitted to wall-clock:
 //   l1tex__data_pipe_lsu_wavefronts_mem_shared.sum = 2.1175e9 over rows x trees x depth = 5M x 500 x 10 lane-visits
@@ -134,7 +135,9 @@ static int select_strategy(const tahoe_forest* f, size_t rows_, double* out) {
             // config 4: 34.4 ms measured at 1M rows, 10.0 at 300K)
             thr += (f->sparse ? 0.4 : 1.0) * miss * R * T * dbar * 32.0 / kRowGather;
           }
-          t = kLaunch + std::max(lat, thr);
+          // one thread per row: below a full wave of threads the chain and the machine's rate are both felt, so the
+          // two terms ADD (held-out forest 50 x d14 x 28 at 100K rows: 0.186 ms measured, max() said 0.079, the sum 0.141)
+          t = kLaunch + lat + thr;
           break;
         }
         case TAHOE_STRATEGY_SHARED_DATA: {
@@ -153,7 +156,7 @@ static int select_strategy(const tahoe_forest* f, size_t rows_, double* out) {
           // one warp's chain: two sequences of tpc/2 trees per tile, then the tile refill
           const double lat = f->sp_chunks * (kChunkFixed + tiles_per_warp *
                              (0.5 * f->sp_tpc * (dbar + 1.0) * kSparseStep + kSparseTileFixed));
-          t = 2.0 * kLaunch + R * C * 8.0 / kRowStream + std::max(lat, thr);
+          t = 2.0 * kLaunch + R * C * 8.0 / kTilePass + std::max(lat, thr);
           break;
         } else {   // SHARED_FOREST / SPLIT_SHARED_FOREST: quantise pass + chunk passes
           // (sparse forests, QT layout: the same kernel on the dense tops + parked deep walks in L2)
