@@ -2,7 +2,7 @@
 
     python tools/sass_excerpt.py > profiles/r02_sass_excerpts.md
 
-Per kernel: mnemonic counts that prove the design (UBLKCP = cp.async.bulk / TMA bulk copies, SYNCS = mbarrier,
+Per kernel: mnemonic counts that prove the design (UBLKCP = cp.async.bulk / TMA bulk copies, UBLKPF = bulk prefetch into L2, SYNCS = mbarrier,
 LDS = shared-memory visits, LDC = kernel-parameter (constant-bank) tree levels, LDG.E.256 = two-level block
 gathers) and the first lines of the unrolled traversal loop."""
 import collections, os, re, subprocess, sys
@@ -29,9 +29,9 @@ for title, obj, sym in KERNELS:
     for _, t in ins:
         t = re.sub(r"^@!?U?P\d+\s+", "", t)
         op = t.split()[0]
-        key = op if op.startswith(("UBLKCP", "SYNCS", "LDG", "STG", "LDC", "BAR", "UTMA")) else op.split(".")[0]
+        key = op if op.startswith(("UBLKCP", "UBLKPF", "SYNCS", "LDG", "STG", "LDC", "BAR", "UTMA")) else op.split(".")[0]
         cnt[key] += 1
-    keys = [k for k in cnt if k.startswith(("UBLKCP", "SYNCS", "LDS", "STS", "LDG", "STG", "LDC", "BAR", "UTMA", "ISETP", "LOP3", "SEL", "IADD3"))]
+    keys = [k for k in cnt if k.startswith(("UBLKCP", "UBLKPF", "SYNCS", "LDS", "STS", "LDG", "STG", "LDC", "BAR", "UTMA", "ISETP", "LOP3", "SEL", "IADD3"))]
     print("| mnemonic | count |\n|---|---|")
     for k in sorted(keys, key=lambda k: -cnt[k]):
         print(f"| `{k}` | {cnt[k]} |")
