@@ -93,7 +93,7 @@ typedef struct {
   int smem_optin_bytes;
   int col_shift;              /* bit position of the column field in a quantised node word (7 = compact, else wide) */
   int smem_warps;             /* shared-memory-forest plan: warps per CTA, */
-  int smem_staged;            /*   1 = one tile buffer per warp + register staging, 0 = two by TMA, */
+  int smem_staged;            /*   tile buffers per warp: 0 = two by TMA, 1 = one + register staging, 2 = one by TMA, refilled from L2 after the walk, */
   int smem_group;             /*   trees traversed together by one thread */
   int sd_teams;               /* SHARED_DATA plan: row teams per CTA (0 = two rows do not fit shared memory), */
   int sd_team_warps;          /*   warps sharing one row, */

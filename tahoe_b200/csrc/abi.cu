@@ -170,7 +170,7 @@ static int select_strategy(const tahoe_forest* f, size_t rows_, double* out) {
           const double lat = f->num_chunks * (kChunkFixed + tiles_per_warp * groups * depth *
                                               (kTileLevel + kTileLevelPerWarp * f->warps));
           const double thr = kSmemVisit * (visits * plan + f->num_chunks * R *
-                             smem_tile_cost(f->params.num_cols, f->staged, f->trees_per_chunk, depth, wide)) +
+                             smem_tile_cost(f->params.num_cols, f->single ? 2 : (f->staged ? 1 : 0), f->warps, f->group, wide)) +
                              (f->sparse ? R * T * f->qt_overflow * kDeepWalk : 0.0);
           const double quant = kLaunch + R * C * 8.0 / (f->quant_stride > 1 ? kQuantRateStrided : kQuantRate);
           t = kLaunch + quant + std::max(lat, thr);
@@ -379,7 +379,7 @@ int tahoe_forest_info(const tahoe_forest_t* f, tahoe_forest_info_t* info) {
   info->bytes_quantized = (int64_t)(f->host.qwords.size() * sizeof(uint32_t));
   info->exchanged_nodes = f->exchanged; info->mean_depth = f->mean_depth; info->device = f->device;
   info->sm_count = f->sm_count; info->smem_optin_bytes = f->smem_optin; info->col_shift = f->col_shift;
-  info->smem_warps = f->warps; info->smem_staged = f->staged; info->smem_group = f->group;
+  info->smem_warps = f->warps; info->smem_staged = f->single ? 2 : (f->staged ? 1 : 0); info->smem_group = f->group;
   info->sd_teams = f->sd_teams; info->sd_team_warps = f->sd_team_warps;
   info->sd_top_levels = f->sd_top; info->sd_blocked = f->sd_blocked;
   return TAHOE_OK;

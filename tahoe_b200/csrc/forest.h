@@ -152,6 +152,7 @@ struct tahoe_forest {
   int group = 1;                 // trees per traversal group (1..kMaxGroup); qwords_trees is a multiple
   int warps = tahoe::kSmemMaxWarps;  // warps per CTA of k_smem_forest
   bool staged = false;           // one tile buffer per warp, next tile staged in registers (else 2, by TMA)
+  bool single = false;           // one tile buffer per warp filled by TMA after the walk, next tile prefetched into L2 (SINGLE)
   int slots = 0;                 // tile buffers per CTA = warps * (staged ? 1 : 2), a power of two
   // tile region of k_smem_forest: word (col, slot, lane) at col*col_stride + slot*slot_stride + lane*4
   // (wide: column-major, the column field of a node sits at bit 7 + log2 slots; compact: slot-major
@@ -245,7 +246,7 @@ int upload(tahoe_forest* f);
 void plan_chunks(tahoe_forest* f);
 void plan_shared_data(tahoe_forest* f);   // teams / top levels / B32 blocks; needs host.inter and query_device
 double smem_visit_cost(int warps, int group, bool staged);   // relative cost of a node visit under a plan
-double smem_tile_cost(int cols, bool staged, int trees_per_chunk, int depth, bool wide);   // one tile pass, in node visits
+double smem_tile_cost(int cols, int mode, int warps, int group, bool wide);   // one tile pass, in node visits (mode: 0 two TMA buffers, 1 staged, 2 SINGLE)
 double smem_depth_factor(int depth);   // bank conflicts of the deep levels, relative to depth 10
 
 // launchers (kernels_*.cu); each returns a status and adds to *launches

@@ -158,7 +158,7 @@ TAHOE_DEPTH_DECL(11) TAHOE_DEPTH_DECL(12) TAHOE_DEPTH_DECL(13) TAHOE_DEPTH_DECL(
 // tiles in the slot-major region with two spare column rows (the hand-over ring), one traversal group per chunk, a dense
 // forest of depth >= 10 and enough chunks to share.
 int smem_cluster_size(const tahoe_forest* f) {
-  const bool able = !f->sparse && f->quant && !f->staged && f->tile_col_stride == 128u &&
+  const bool able = !f->sparse && f->quant && !f->staged && !f->single && f->tile_col_stride == 128u &&
                     f->tile_slot_stride >= ((uint32_t)f->params.num_cols + 2u) * 128u &&
                     f->trees_per_chunk == f->group && f->group >= 2 && f->qdepth >= 10;
   // OPT-IN (TAHOE_CLUSTER=2).  Alone on the GPU, pairs of CTAs run config 3 at equal speed (52.9 vs 53.2 ms) with half the DRAM

@@ -98,10 +98,15 @@ int TAHOE_CAT(launch_smem_depth_, TAHOE_DEPTH)(tahoe_forest* f, const SmemParams
   }
 #endif
   // the leaf-id instantiation is the checking path: one tree at a time keeps the build small
-  if (p.leaf_ids) return f->staged ? go(k_smem_forest<D, 1, true, true, 0>) : go(k_smem_forest<D, 1, true, false, 0>);
+  if (p.leaf_ids)
+    return f->staged ? go(k_smem_forest<D, 1, true, true, 0>)
+                     : (f->single ? go(k_smem_forest<D, 1, true, false, 0, true>) : go(k_smem_forest<D, 1, true, false, 0>));
   // p.top_levels: 2 = levels 0-1 of every tree from the kernel-parameter table, 0 = every level from shared memory
 #define TAHOE_G_CASE(G)                                                                                         \
   case G:                                                                                                       \
+    if (f->single)                                                                                              \
+      return p.top_levels >= 2 ? go(k_smem_forest<D, G, false, false, 2, true>)                                 \
+                               : go(k_smem_forest<D, G, false, false, 0, true>);                                \
     if (p.top_levels >= 2)                                                                                      \
       return f->staged ? go(k_smem_forest<D, G, false, true, 2>) : go(k_smem_forest<D, G, false, false, 2>);    \
     return f->staged ? go(k_smem_forest<D, G, false, true, 0>) : go(k_smem_forest<D, G, false, false, 0>);

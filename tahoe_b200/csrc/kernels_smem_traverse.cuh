@@ -146,14 +146,19 @@ __device__ __forceinline__ void sts_u128(uint32_t addr, uint4 v) {
   asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
-template <int DEPTH, int G, bool LEAF_IDS, bool STAGED, int TOPL>
+// SINGLE: one tile buffer per warp filled by TMA (no register staging, no second buffer): the warp asks for its
+// next tile into L2 (cp.async.bulk.prefetch.L2) when it starts to walk and issues the bulk copy after the walk, so
+// the copy reads L2 and the SM's other warps cover that short wait.  The staged plans pay 2 x cols / 4 128-bit LSU
+// instructions per lane and tile for the same saving of shared memory.
+template <int DEPTH, int G, bool LEAF_IDS, bool STAGED, int TOPL, bool SINGLE = false>
 __global__ void __launch_bounds__(kSmemMaxThreads, 1)
 k_smem_forest(const __grid_constant__ SmemParams p, const __grid_constant__ TopWords tw) {
   static_assert(!LEAF_IDS || TOPL == 0, "the leaf-id instantiation keeps every level in shared memory");
+  static_assert(!(STAGED && SINGLE), "one way of filling the only buffer");
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr uint32_t W = 1u << (DEPTH + 1);      // words per tree
   constexpr uint32_t L = 1u << DEPTH;            // bottom slots per tree
-  constexpr int kBufs = STAGED ? 1 : 2;
+  constexpr int kBufs = (STAGED || SINGLE) ? 1 : 2;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nwarps = blockDim.x >> 5;
   const int slots = nwarps * kBufs;
@@ -266,6 +271,10 @@ k_smem_forest(const __grid_constant__ SmemParams p, const __grid_constant__ TopW
         commit_tile();                       // registers -> this warp's only buffer
         __syncwarp();
         if (next < p.num_tiles) fetch_tile(next);   // lands while this tile is traversed
+      } else if (SINGLE) {
+        if (next < p.num_tiles && lane == 0)          // HBM -> L2 under this tile's walk
+          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.qtiles + next * (size_t)p.cols * 32),
+                       "r"(tile_bytes) : "memory");
       } else if (next < p.num_tiles) {
         load_tile(next, buf ^ 1);
       }
@@ -304,7 +313,12 @@ k_smem_forest(const __grid_constant__ SmemParams p, const __grid_constant__ TopW
         if (last) p.out[row] = apply_transform(acc, p.tf);
         else p.preds[row] = acc;
       }
-      if (!STAGED) buf ^= 1;
+      if (SINGLE) {
+        __syncwarp();                        // every lane is done with the buffer
+        if (next < p.num_tiles) load_tile(next, 0);
+      } else if (!STAGED) {
+        buf ^= 1;
+      }
     }
   }
 }

@@ -878,13 +878,17 @@ double smem_visit_cost(int warps, int G, bool staged) {
 // instead of 92 %.  Measured 1.4 at depth 12 relative to depth 10; applied to the visits, not to the tile passes.
 double smem_depth_factor(int depth) { return 1.0 + 0.2 * std::max(0, depth - 10); }
 
-// One pass of a row's tile through a chunk, in node-visit units.  Staged: the tile moves through the LSU
-// twice (C/4 128-bit loads + stores per lane) plus a fixed part -- fitted 14.4 visits at 18 columns, 19.5 at
-// 28.  TMA: the fixed part only when the tile is ONE bulk copy (slot-major region); the column-major
-// (wide) region takes one 128-byte copy per column (fitted 22 visits at 18 columns).
-double smem_tile_cost(int cols, bool staged, int trees_per_chunk, int depth, bool wide) {
-  if (staged) return 0.256 * (2.0 * cols + 20.0);
-  (void)trees_per_chunk; (void)depth;   // (4 trees x 12 levels per tile already hide the copy: 12 warps x 4 trees on config 3)
+// One pass of a row's tile through a chunk, in node-visit units.  `mode` = how the warp's tile buffer is filled:
+// 1 staged: the tile moves through the LSU twice (C/4 128-bit loads + stores per lane) plus a fixed part --
+//   fitted 14.4 visits at 18 columns, 19.5 at 28.
+// 0 two buffers by TMA: the fixed part only when the tile is ONE bulk copy (slot-major region); the column-major
+//   (wide) region takes one 128-byte copy per column (fitted 22 visits at 18 columns).
+// 2 SINGLE, one buffer by TMA refilled from L2 after the walk: the copy's latency is exposed to the warp and covered
+//   by the SM's other walks -- fitted on config 3 (profiles/r02_single_tiles.log): 0.5 visits with 80 walks per SM,
+//   7 with 60-64, 14.6 with 48.
+double smem_tile_cost(int cols, int mode, int warps, int group, bool wide) {
+  if (mode == 1) return 0.256 * (2.0 * cols + 20.0);
+  if (mode == 2) return std::max(3.0, 1700.0 / std::max(warps * group, 1) - 20.0);
   return 8.0 + (wide ? 0.8 * cols : 0.0);
 }
 
@@ -919,10 +923,12 @@ static double plan_chunks_for(tahoe_forest* f, int depth, bool deep) {
     if (want_warps && warps != want_warps) continue;
     // deep: + lane-private rings of parked walks + the pairs' exchange floats
     const size_t bars = 1024 + (deep ? (size_t)warps * kDeepPend * 128 + 512 : 0);
-    for (int staged = 0; staged <= 1; ++staged) {
+    // tiles: 0 = two buffers per warp by TMA, 1 = one buffer + the next tile in registers, 2 = one buffer by TMA,
+    // refilled after the walk from L2 (SINGLE: slot-major region so that a tile is one bulk copy)
+    for (int staged = 0; staged <= (deep ? 1 : 2); ++staged) {
       if (want_staged >= 0 && staged != want_staged) continue;
       if (deep && !staged) continue;                   // k_smem_forest_deep: the next tile always waits in registers
-      if (staged && C > (deep ? kStagedMaxColsDeep : kStagedMaxCols)) continue;
+      if (staged == 1 && C > (deep ? kStagedMaxColsDeep : kStagedMaxCols)) continue;
       // deep: current + previous tile per warp; rows wider than 32 columns at 16 warps: per PAIR of warps
       const bool paired = deep && C > kStagedMaxCols && warps > 8;
       const int slots = deep ? (paired ? warps : warps * 2) : warps * (staged ? 1 : 2);
@@ -930,7 +936,7 @@ static double plan_chunks_for(tahoe_forest* f, int depth, bool deep) {
       // else the compact field with a slot-major region whose columns are padded to a power of two
       const bool pow2_slots = (slots & (slots - 1)) == 0;
       if (deep && !pow2_slots) continue;
-      const bool wide = pow2_slots && f->rank_bits + f->col_bits + kQuantColShift + ilog2_c(slots) <= 32;
+      const bool wide = staged != 2 && pow2_slots && f->rank_bits + f->col_bits + kQuantColShift + ilog2_c(slots) <= 32;
       const size_t cols_pad = (size_t)1 << ceil_log2((uint64_t)C);
       const size_t tiles = wide ? (size_t)slots * tile_bytes : (size_t)slots * cols_pad * 128;
       if ((size_t)f->smem_optin < tiles + bars + tree_bytes) continue;
@@ -943,16 +949,16 @@ static double plan_chunks_for(tahoe_forest* f, int depth, bool deep) {
         int tpc = std::min(max_tpc / G * G, tpad);
         const int chunks = (tpad + tpc - 1) / tpc;     // balance: same chunk count, even whole groups
         tpc = ((tpad + chunks - 1) / chunks + G - 1) / G * G;
-        double visits = (double)tpad * std::max(depth, 1) * smem_visit_cost(warps, G, staged != 0) * smem_depth_factor(depth);
+        double visits = (double)tpad * std::max(depth, 1) * smem_visit_cost(warps, G, staged == 1) * smem_depth_factor(depth);
         // levels 0-1 from the kernel-parameter table (launch_smem_forest: plans of >= 16 warps)
         if (warps >= 16 && !deep) visits *= 1.0 - 0.25 * std::min(2, depth) / std::max(depth, 1);
         // deep: the per-group work, and 8 warps (64 staging registers) cover less of it than 16 (measured 1.17x)
         if (deep) visits = visits * (warps <= 8 ? 1.12 : 1.0) + (double)tpad / G * kDeepGroupVisits;
         // (deep: the tile of a pass is committed from registers under the deep walks of the tile before)
-        const double cost = visits + (double)chunks * (deep ? 10.0 : smem_tile_cost(C, staged != 0, tpc, std::max(depth, 1), wide));
+        const double cost = visits + (double)chunks * (deep ? 10.0 : smem_tile_cost(C, staged, warps, G, wide));
         if (!found || cost < best) {
           found = true; best = cost;
-          f->warps = warps; f->staged = staged != 0; f->slots = slots; f->group = G;
+          f->warps = warps; f->staged = staged == 1; f->single = staged == 2; f->slots = slots; f->group = G;
           f->qwords_trees = tpad; f->trees_per_chunk = tpc;
           f->num_chunks = (tpad + tpc - 1) / tpc;
           f->smem_bytes = tiles + bars + (size_t)tpc * tree_bytes;
