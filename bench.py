@@ -238,12 +238,14 @@ def _emit(line: dict):
 # ---------------------------------------------------------------------------------------------
 def build_forest(cfg_id: str, nodes=None):
     """-> (Forest, real node count, levels).  Dense configs from the AoS nodes, config 4 from compact
-    nodes; levels = (tree_offsets, level of every compact node) for the sparse config, else None."""
+    nodes; levels = (tree_offsets, level of every compact node, largest |leaf value|) for the sparse config, else None."""
     from tahoe_b200 import api
     cfg = synth.CONFIGS[cfg_id]
     if cfg["sparse"]:
         sp, offs, w, lv = synth.gen_sparse_forest(synth.FOREST_SEED[cfg_id], cfg["trees"], cfg["depth"], cfg["cols"])
-        return api.Forest.from_sparse(sp, offs, cfg["cols"], weights=w, missing=-999.0), int(offs[-1]), (offs, lv)
+        leaf_abs_max = float(np.abs(sp["val"][sp["bits"] < 0]).max()) if "bits" in sp.dtype.names else 1.0
+        return (api.Forest.from_sparse(sp, offs, cfg["cols"], weights=w, missing=-999.0), int(offs[-1]),
+                (offs, lv, leaf_abs_max))
     if nodes is None:
         nodes = synth.gen_dense_forest(synth.FOREST_SEED[cfg_id], cfg["trees"], cfg["depth"], cfg["cols"])
     f = api.Forest.from_dense(nodes, cfg["trees"], cfg["depth"], cfg["cols"], missing=-999.0)
@@ -256,7 +258,7 @@ def measured_mean_depth(forest, data, levels, sample=4096):
     DIRECT kernel reports (held bit-exact to the oracle's by tests/test_gpu_full_size.py)."""
     import torch
     from tahoe_b200 import api
-    offs, lv = levels
+    offs, lv = levels[0], levels[1]
     n = min(sample, int(data.shape[0]))
     T = offs.shape[0] - 1
     ids = torch.zeros((n, T), dtype=torch.int32, device="cuda")
@@ -323,11 +325,15 @@ def measure_config(cfg_id, forest, n_nodes, data, peaks, hbm_gbs, steps, strateg
         rec["frac_smem"] = smem_bytes / sec / 1e9 / peaks["smem_read_gbs"]
         rec["plan"] = {"warps": info.smem_warps, "staged": info.smem_staged, "group": info.smem_group,
                        "trees_per_chunk": info.trees_per_chunk, "chunks": info.num_chunks, "cluster": info.smem_cluster}
-    rec["e2e"] = host_leg(forest, data, preds, s, rows / (step_ms * 1e-3))
+    # the sparse shared-memory path finishes its deep walks in an order that depends on the launch shape: its host
+    # slabs and its whole-batch launch may differ in the last bits; bound = the tests' 1e-6 x the L1 mass of a row's
+    # summands (<= trees x the largest |leaf|).  Every other path must match bit for bit.
+    tol = 1e-6 * cfg["trees"] * levels[2] if (info.is_sparse and levels is not None and len(levels) > 2) else None
+    rec["e2e"] = host_leg(forest, data, preds, s, rows / (step_ms * 1e-3), tol_abs=tol)
     return rec, s, preds
 
 
-def host_leg(forest, data, preds, strategy, device_rate, reps=3):
+def host_leg(forest, data, preds, strategy, device_rate, reps=3, tol_abs=None):
     """The same predict through host buffers (tahoe_predict_host: pinned rows in, scores out, copies inside the timed
     region) and the same slab copies with the kernels left out: what the end-to-end number is bounded by."""
     import torch
@@ -347,8 +353,11 @@ def host_leg(forest, data, preds, strategy, device_rate, reps=3):
     out["unit"] = "samples/s"
     out["h2d_bytes_per_step"] = int(data.numel()) * 4
     out["d2h_bytes_per_step"] = rows * 4
-    out["matches_device_path"] = bool(torch.equal(h_preds.cuda(), preds))     # bit for bit (the sparse path re-orders its sum per launch shape)
+    out["bit_identical_to_device_path"] = bool(torch.equal(h_preds.cuda(), preds))
     out["max_abs_diff_vs_device_path"] = float((h_preds.cuda().double() - preds.double()).abs().max().item())
+    out["tolerance_abs"] = tol_abs           # None: bit-identity is required (every path that sums in tree order)
+    out["matches_device_path"] = out["bit_identical_to_device_path"] or (
+        tol_abs is not None and out["max_abs_diff_vs_device_path"] <= tol_abs)
     out["frac_of_bound"] = out["value"] / min(device_rate, out["copies_only_samples_per_s"])
     return out
 

@@ -71,17 +71,18 @@ constexpr double kTeamLevel = 0.7e-6;       // SHARED_DATA: one tree level of a 
 constexpr double kSharedDataRate = 7.0e11;  // visits/s (slot-levels), SHARED_DATA
 constexpr double kTilePass = 4.6e12;        // B/s through the tile pass of the 8-byte sparse tops (read + write)
 constexpr double kRowStream = 6.0e12;       // B/s of sample rows through a TMA-fed SHARED_DATA kernel (config 1: 614 MB in 0.109 ms at 50K rows, 2.46 GB in 0.364 ms at 200K)
-// The shared-memory forest's rate is DERIVED FROM NCU COUNTERS of the unit plan (config 2, 16 warps x 5 trees staged,
-// parameter-table levels; profiles/r02_ncu_full_C2_summary.json), not fitted to wall-clock:
-//   l1tex__data_pipe_lsu_wavefronts_mem_shared.sum = 2.1175e9 over rows x trees x depth = 5M x 500 x 10 lane-visits
-//   l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed = 97.9 %; the pipe retires one wavefront per clock
+// The shared-memory forest's rate is DERIVED FROM NCU COUNTERS of the unit plan (config 2, 16 warps x 5 trees, SINGLE
+// tiles, parameter-table levels; profiles/r02_ncu_full_C2_summary.json), not fitted to wall-clock:
+//   l1tex__data_pipe_lsu_wavefronts_mem_shared.sum = 2.0294e9 over rows x trees x depth = 5M x 500 x 10 lane-visits
+//   l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed = 95.6 %; the pipe retires one wavefront per clock
 //   per SM (tahoe_measure_peaks: 37.1 TB/s = 128 B x 148 SMs x 1.965 GHz)
-// => seconds per lane-visit = wavefronts per lane-visit / (pipe rate x utilisation) = 2.97e-13 (wall-clock fit: 2.9e-13).
-// The same two counters on config 3 (1.1582e10 wavefronts over 1.2e11 lane-visits at 81.2 %) give 4.09e-13: the ratio,
-// 1.37, is smem_depth_factor(12) = 1.4 of the planner.
-constexpr double kSmemWavefrontsPerLaneVisit = 2.1175e9 / 2.5e10;
+// => seconds per lane-visit = wavefronts per lane-visit / (pipe rate x utilisation) = 2.92e-13.
+// The same two counters on config 3 (1.0898e10 wavefronts over 1.2e11 lane-visits at 89.4 %) give 3.49e-13 before the
+// parameter-table discount both share: the ratio, 1.20 in counters and 1.3 in wall-clock (46.5 ms), is the planner's
+// smem_depth_factor(12) = 1.3.
+constexpr double kSmemWavefrontsPerLaneVisit = 2.0294e9 / 2.5e10;
 constexpr double kLsuPipeRate = 148.0 * 1.965e9;   // wavefronts/s
-constexpr double kLsuPipeUtil = 0.979;
+constexpr double kLsuPipeUtil = 0.956;
 constexpr double kSmemVisit = kSmemWavefrontsPerLaneVisit / (kLsuPipeRate * kLsuPipeUtil);   // s per lane-visit, unit plan
 constexpr double kChunkFixed = 4.0e-6;      // stage one chunk + barrier + the ragged end of a pass (config 3: 0.9 ms over 167 chunks)
 constexpr double kTileLevel = 30e-9;        // one level of one traversal group of a tile: this much alone ...

@@ -873,10 +873,10 @@ double smem_visit_cost(int warps, int G, bool staged) {
   return by_chains * by_group[G];
 }
 
-// Deep trees cost more per visit: the bottom levels of a 2^12-leaf tree are random words (bank conflicts:
-// 3.3 shared-memory wavefronts per level on config 3 against 2.8 on config 2) and the pipe runs at 82 %
-// instead of 92 %.  Measured 1.4 at depth 12 relative to depth 10; applied to the visits, not to the tile passes.
-double smem_depth_factor(int depth) { return 1.0 + 0.2 * std::max(0, depth - 10); }
+// Deep trees cost more per visit: the bottom levels of a 2^12-leaf tree are random words (bank conflicts: 2.9
+// shared-memory wavefronts per warp-visit on config 3 against 2.6 on config 2) and the pipe runs at 89 % instead of
+// 96 %.  Measured 1.3 at depth 12 relative to depth 10; applied to the visits, not to the tile passes.
+double smem_depth_factor(int depth) { return 1.0 + 0.15 * std::max(0, depth - 10); }
 
 // One pass of a row's tile through a chunk, in node-visit units.  `mode` = how the warp's tile buffer is filled:
 // 1 staged: the tile moves through the LSU twice (C/4 128-bit loads + stores per lane) plus a fixed part --

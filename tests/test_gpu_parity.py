@@ -325,3 +325,31 @@ def test_quantise_from_rows_and_from_float_tiles_agree(oracle, monkeypatch, tile
     assert np.array_equal(ids.cpu().numpy(), wids)
     mass = np.abs(sp["val"][offs[:-1][None, :] + wids]).sum(1)
     assert score_close(got, want, mass)
+
+
+@pytest.mark.parametrize("plan,trees,depth,cols,rows", [
+    ("16,2,5", 203, 10, 18, 148 * 16 * 32 + 77), ("16,0,5", 203, 10, 18, 5000), ("16,1,5", 203, 10, 18, 5000),
+    ("16,2,5", 47, 12, 28, 148 * 16 * 32 * 2 + 5), ("12,2,5", 47, 12, 28, 33), ("8,2,3", 10, 11, 28, 1),
+    ("16,2,2", 7, 6, 40, 70_001), ("4,2,1", 5, 3, 64, 2049), ("16,2,6", 600, 8, 5, 300_000)])
+def test_smem_tile_modes_are_bit_exact(oracle, monkeypatch, plan, trees, depth, cols, rows):
+    """k_smem_forest under every way of filling a warp's tile buffer -- two buffers by TMA (0), one + registers (1),
+    SINGLE (2: one buffer by TMA, refilled from L2 after the walk) -- forced by TAHOE_SMEM_PLAN on dense forests of
+    several depths: scores are the CPU's bits, leaf ids the oracle's, twice in a row (mbarrier phases end clean);
+    several chunks, one tile, one row, rows with missing values and NaN."""
+    import torch
+    monkeypatch.setenv("TAHOE_SMEM_PLAN", plan)
+    nodes = synth.gen_dense_forest(5200 + trees, trees, depth, cols, leaf_prob=0.03)
+    f = api.Forest.from_dense(nodes, trees, depth, cols, missing=-999.0)
+    inf = f.info()
+    if not f.applicable(api.SPLIT_SHARED_FOREST, rows):
+        pytest.skip("plan does not fit this forest")
+    assert (inf.smem_warps, inf.smem_staged, inf.smem_group) == tuple(int(x) for x in plan.split(","))
+    x = api.gen_data_device(5300 + trees, rows, cols, miss_frac=0.004)
+    ref = f.predict(x, strategy=api.DIRECT).cpu().numpy()
+    for _ in range(2):
+        assert bits_equal(f.predict(x, strategy=api.SPLIT_SHARED_FOREST).cpu().numpy(), ref)
+    n = min(rows, 1500)
+    host = synth.gen_data(5300 + trees, n, cols, miss_frac=0.004, nan_frac=0.002)
+    want, wids = oracle.predict_dense(nodes, trees, depth, host, -999.0, want_leaf_ids=True)
+    got, ids = _run(f, host, api.SPLIT_SHARED_FOREST)
+    assert np.array_equal(ids, wids) and bits_equal(got, want)
