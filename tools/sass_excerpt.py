@@ -9,11 +9,11 @@ import collections, os, re, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 OBJ = os.path.join(ROOT, "tahoe_b200", "build")
 KERNELS = [
-    ("config 3: k_smem_forest<12, 4, ids=0, staged=0 (TMA tiles), top_levels=0>", "kernels_smem_depth_12.o", "_ZN5tahoe13k_smem_forestILi12ELi4ELb0ELb0ELi0EEEvNS_10SmemParamsENS_8TopWordsE"),
-    ("config 2: k_smem_forest<10, 5, ids=0, staged=1, top_levels=2 (levels 0-1 from kernel parameters)>", "kernels_smem_depth_10.o", "_ZN5tahoe13k_smem_forestILi10ELi5ELb0ELb1ELi2EEEvNS_10SmemParamsENS_8TopWordsE"),
+    ("config 3: k_smem_forest<12, 5, ids=0, staged=0, top_levels=2, SINGLE tiles (one TMA buffer per warp, next tile prefetched into L2)>", "kernels_smem_depth_12.o", "_ZN5tahoe13k_smem_forestILi12ELi5ELb0ELb0ELi2ELb1EEEvNS_10SmemParamsENS_8TopWordsE"),
+    ("config 2: k_smem_forest<10, 5, ids=0, staged=0, top_levels=2 (levels 0-1 from kernel parameters), SINGLE tiles>", "kernels_smem_depth_10.o", "_ZN5tahoe13k_smem_forestILi10ELi5ELb0ELb0ELi2ELb1EEEvNS_10SmemParamsENS_8TopWordsE"),
     ("config 4: k_smem_forest_deep<6, 6, ids=0, pieces=8, K=2, pair=1>", "kernels_smem_depth_6.o", "_ZN5tahoe18k_smem_forest_deepILi6ELi6ELb0ELi8ELi2ELb1EEEvNS_10SmemParamsENS_8TopWordsE"),
     ("config 1: k_shared_data<TMA=1, G=2, blocked=1>", "kernels_shared_data.cu.o", "_ZN5tahoe13k_shared_dataILb1ELi2ELb1EEEvNS_16SharedDataParamsE"),
-    ("k_quantize", "kernels_smem.cu.o", "_ZN5tahoe10k_quantizeENS_11QuantParamsE"),
+    ("k_quantize<from_tiles=1> (config 3: quantises the transposed float tiles in place)", "kernels_smem.cu.o", "_ZN5tahoe10k_quantizeILb1EEEvNS_11QuantParamsE"),
 ]
 for title, obj, sym in KERNELS:
     out = subprocess.run(["cuobjdump", "-sass", "-fun", sym, os.path.join(OBJ, obj)], capture_output=True, text=True).stdout
