@@ -9,6 +9,11 @@
 // reduction per row.  No block barrier in the row loop, no idle lanes when T < 256.
 // This is the strategy for wide rows (SVHN-like: a 12 KB row is read once, coalesced)
 // and for small batches, where trees are the only parallelism.
+//
+// Round 2 (profiles/r02_c1_walk_cycles.md): wide rows run as two-warp teams with ONE row buffer each; the team's
+// next row is prefetched into L2 while the current one is walked (cp.async.bulk.prefetch.L2), the forest's top
+// levels are one bulk-copied image without padding slots, and the blocked walk reads nodes stored the way a
+// decision uses them (kSd* in forest.h; sd_child).
 #include <cstdlib>
 
 #include "device_utils.cuh"
@@ -30,7 +35,7 @@ struct SharedDataParams {
   float* preds;
   int32_t* leaf_ids;
   Transform tf;
-  int teams_per_block;       // a team = team_warps warps sharing one row (two row buffers)
+  int teams_per_block;       // a team = team_warps warps sharing one row (row_bufs row buffers)
   int team_warps;            // 1, 2 or 4
   int top_levels;            // levels 0..top_levels-1 of the interleaved forest are copied to shared memory
   uint32_t top_off;          // byte offset of that copy ([2^top_levels - 1][top_stride] uint2)
@@ -254,10 +259,11 @@ __device__ __forceinline__ double sd_walk_row_blocked(const SharedDataParams& p,
   return acc;
 }
 
-// Shared-memory map: [teams][2][row_stride floats] row buffers | [teams][2][4] double partials |
-// [teams][2] mbarriers (TMA only).
+// Shared-memory map: [teams][row_bufs][row_stride floats] row buffers | [teams][2][4] double partials |
+// [teams][2] mbarriers (TMA only) | top levels of the forest (top_off) | the top image's mbarrier.
 // TMA = true : rows arrive by bulk copies (cp.async.bulk, row bytes a multiple of 16) completing on
-//              the buffer's mbarrier: the next row streams in from HBM while the current one is walked.
+//              the buffer's mbarrier: with two buffers the next row streams in from HBM while the current one is
+//              walked; with one it is prefetched into L2 meanwhile and copied after the walk.
 // TMA = false: the team copies its row with coalesced loads (any width / alignment).
 template <bool TMA, int G, bool BLOCKED>
 __global__ void __launch_bounds__(1024, 1) k_shared_data(SharedDataParams p) {
