@@ -125,6 +125,7 @@ struct Tuning {
   int cluster = -1;                    // TAHOE_CLUSTER: CTAs per cluster of the k_smem_forest cluster pipeline (0/1 = off, -1 = by plan)
   int quant_tiles = -1;                // TAHOE_QUANT_TILES: 1 = transpose to float tiles first, quantise them in place; 0 = from the rows; -1 = by table
   int top_levels = -1;                 // TAHOE_TOP_LEVELS: 0/1/2 tree levels from the kernel-parameter table; -1 = by plan
+  bool sd_no_l2_ahead = false;         // TAHOE_SD_NO_L2_AHEAD: k_shared_data's single-buffer teams do not prefetch their next row into L2 (ablation)
   int top_trees = 0;                   // TAHOE_TOP_TREES: cap on the trees per launch of k_smem_forest (test knob: forces the split)
   int slab_first = 0, slab_growth = 0, slab_cap = 0;   // TAHOE_HOST_SLAB="first,growth%,cap" (waves of tiles); 0 = from the model
 };

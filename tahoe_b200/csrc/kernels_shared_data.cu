@@ -424,7 +424,7 @@ int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches) {
   p.top_nodes = f->d_sd_top_image; p.top_bytes = (uint32_t)(f->host.sd_top_image.size() * sizeof(uint2)); p.blocks = f->d_sd_blocks; p.orig_bottom = f->d_sd_orig_bottom;
   p.block_levels = f->sd_blocked ? (f->depth + 1 - f->sd_top) / 2 : 0;
   p.row_bufs = f->sd_row_bufs;
-  p.l2_ahead = std::getenv("TAHOE_SD_NO_L2_AHEAD") ? 0 : 1;
+  p.l2_ahead = f->tune.sd_no_l2_ahead ? 0 : 1;
   const size_t per_team = (size_t)p.row_bufs * row_stride + 64 + 16;    // row buffers, partials, mbarriers
   p.top_off = (uint32_t)(((size_t)p.teams_per_block * per_team + 127) / 128 * 128);
   const size_t smem = f->sd_smem;

@@ -996,6 +996,7 @@ static void read_tuning(Tuning& t) {
   if (const char* e = std::getenv("TAHOE_TOP_LEVELS")) t.top_levels = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_QUANT_TILES")) t.quant_tiles = std::atoi(e);
   if (const char* e = std::getenv("TAHOE_CLUSTER")) t.cluster = std::atoi(e);
+  if (std::getenv("TAHOE_SD_NO_L2_AHEAD")) t.sd_no_l2_ahead = true;
   if (const char* e = std::getenv("TAHOE_NO_REORDER")) t.no_reorder = std::atoi(e) != 0;
   if (const char* e = std::getenv("TAHOE_NO_SIMHASH")) t.no_simhash = std::atoi(e) != 0;
   if (const char* e = std::getenv("TAHOE_HOST_SLAB")) std::sscanf(e, "%d,%d,%d", &t.slab_first, &t.slab_growth, &t.slab_cap);
