@@ -391,12 +391,17 @@ int tahoe_forest_info(const tahoe_forest_t* f, tahoe_forest_info_t* info) {
 // call recorded (stream-ordered, no host sync).  Calls on one stream are ordered by the stream itself.
 static int predict_on_ws0(tahoe_forest* f, int strategy, PredictArgs a) {
   Workspace& w = f->ws[0];
-  if (f->device >= 0) {
+  if (strategy == TAHOE_STRATEGY_AUTO && f->device >= 0) strategy = select_strategy(f, a.rows, nullptr);
+  // the one-kernel strategies keep nothing in the handle's workspace: no event traffic on their launch path
+  // (small batches are bound by the host side of the call)
+  const bool uses_ws = !(strategy == TAHOE_STRATEGY_DIRECT || strategy == TAHOE_STRATEGY_SHARED_DATA_PER_THREAD ||
+                         strategy == TAHOE_STRATEGY_SHARED_DATA);
+  if (f->device >= 0 && uses_ws) {
     if (!w.done) TAHOE_CUDA(cudaEventCreateWithFlags(&w.done, cudaEventDisableTiming));
     if (w.used && w.last_stream != a.stream) TAHOE_CUDA(cudaStreamWaitEvent(a.stream, w.done, 0));
   }
   const int rc = predict_impl(f, strategy, a);
-  if (f->device >= 0 && rc == TAHOE_OK) {
+  if (f->device >= 0 && rc == TAHOE_OK && uses_ws) {
     TAHOE_CUDA(cudaEventRecord(w.done, a.stream));
     w.used = true; w.last_stream = a.stream;
   }

@@ -183,6 +183,7 @@ struct tahoe_forest {
   int sd_top = 0;                // forest levels copied to shared memory
   bool sd_blocked = false;       // B32 two-level blocks below the top levels
   int sd_top_stride = 0;         // slots per node in the shared-memory copy of the top levels (tpad, or the tree count)
+  int sd_per_sm[2] = {0, 0};     // CTAs per SM of the forest's k_shared_data launch, asked once ([0] LSU rows, [1] TMA rows)
   size_t sd_smem = 0;
 
   // per-class outputs (tahoe_forest_create_sparse_classes): class k owns packed trees

@@ -15,6 +15,9 @@
 // levels are one bulk-copied image without padding slots, and the blocked walk reads nodes stored the way a
 // decision uses them (kSd* in forest.h; sd_child).
 #include <cstdlib>
+#include <map>
+#include <mutex>
+#include <utility>
 
 #include "device_utils.cuh"
 #include "forest.h"
@@ -430,13 +433,29 @@ int launch_shared_data(tahoe_forest* f, const PredictArgs& a, int* launches) {
   const size_t smem = f->sd_smem;
   // bulk copies need 16-byte rows at 16-byte addresses; short rows are cheaper through the LSU
   const bool tma = (row_bytes % 16 == 0) && ((reinterpret_cast<uintptr_t>(a.data) & 15) == 0) && row_bytes >= 1024;
+  // Small batches are bound by the HOST side of a launch (10 us per call measured against a 5 us kernel,
+  // tools/probe_small_batch.py), so what does not change between calls is asked once: the kernel's shared-memory
+  // limit per device (raised only when a forest needs more than any before it) and the forest's CTAs per SM.
   auto go = [&](auto kern) -> int {
-    if (smem > 48 * 1024)
-      TAHOE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // (every instantiation has the same function-pointer TYPE, so this lambda is instantiated once: the limits are
+    // keyed by the kernel's address and the device)
+    if (smem > 48 * 1024) {
+      static std::mutex mu;
+      static std::map<std::pair<const void*, int>, int> limit_set;
+      std::lock_guard<std::mutex> lock(mu);
+      int& have = limit_set[{reinterpret_cast<const void*>(kern), f->device}];
+      if ((int)smem > have) {
+        TAHOE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        have = (int)smem;
+      }
+    }
     const int threads = p.teams_per_block * p.team_warps * 32;
-    int per_sm = 1;
-    TAHOE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
-    per_sm = std::max(per_sm, 1);
+    int per_sm = f->sd_per_sm[tma ? 1 : 0];
+    if (per_sm == 0) {
+      TAHOE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
+      per_sm = std::max(per_sm, 1);
+      f->sd_per_sm[tma ? 1 : 0] = per_sm;
+    }
     const size_t want = (a.rows + p.teams_per_block - 1) / p.teams_per_block;
     const unsigned grid = (unsigned)std::min<size_t>(want, (size_t)f->sm_count * per_sm);
     kern<<<grid, threads, smem, a.stream>>>(p);
