@@ -338,8 +338,8 @@ int tahoe_predict_classes(tahoe_forest_t* f, int strategy, const float* d_data, 
     if (rc != TAHOE_OK) return rc;
     total += f->last_launches;
   }
-  if (f->device >= 0) {   // the event predict_on_ws0 recorded covered class 0 only
-    Workspace& w = f->ws[0];
+  if (f->device >= 0 && smem) {   // the event predict_on_ws0 recorded covered class 0 only (the other strategies keep
+    Workspace& w = f->ws[0];      // nothing in the workspace: no event)
     TAHOE_CUDA(cudaEventRecord(w.done, (cudaStream_t)stream));
   }
   f->last_launches = total;
